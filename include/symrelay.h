@@ -1,0 +1,194 @@
+/*
+ * symrelay.h -- C ABI of the B200-native batched secretstream relay.
+ *
+ * Drop-in boundary for the one data-parallel path of Symmetry's provider:
+ * the per-chunk body of the relay loop, /root/reference/src/provider.ts:240-257
+ * (parse -> extract delta -> `peer.write(chunk)`), and its mirror on receive,
+ * provider.ts:174 (`peer.on('data')`).  In the reference every `peer.write`
+ * ends in ONE synchronous libsodium call per frame four packages down
+ * (@hyperswarm/secret-stream `_write` -> sodium-secretstream `Push.next` ->
+ * sodium-native `crypto_secretstream_xchacha20poly1305_push`;
+ * package-lock.json:763-777, 5725-5758; state shape src/types.ts:168-177).
+ * This library does the same arithmetic, bit-exact, for the frames of MANY
+ * connections per call on a B200.  Plain C types only; no exceptions; every
+ * function returns 0 / a non-negative value on success or a negative
+ * SYMRELAY_E* code.  There is no CPU fallback: without a CUDA device
+ * symrelay_create() fails.
+ *
+ * Wire format (unchanged, so an unmodified peer decrypts it):
+ *     uint24-LE(mlen+17) ‖ tag^ks ‖ c[mlen] ‖ mac[16]      (mlen + 20 bytes)
+ */
+#ifndef SYMRELAY_H
+#define SYMRELAY_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SYMRELAY_API __attribute__((visibility("default")))
+#else
+#define SYMRELAY_API
+#endif
+
+#define SYMRELAY_ABI_VERSION 1
+
+#define SYMRELAY_KEYBYTES 32
+#define SYMRELAY_HEADERBYTES 24
+#define SYMRELAY_STATEBYTES 52  /* libsodium crypto_secretstream_xchacha20poly1305_state; src/types.ts:170,175 */
+#define SYMRELAY_WIRE_OVERHEAD 20 /* 3-byte length prefix + 17 (ABYTES) */
+#define SYMRELAY_MAX_FRAME ((1u << 24) - 1u - 17u) /* uint24 prefix caps mlen */
+
+/* error codes (negative return values) */
+#define SYMRELAY_OK 0
+#define SYMRELAY_EINVAL (-22)
+#define SYMRELAY_EAGAIN (-11) /* ring full: maps to `peer.write() === false`, provider.ts:248-252 */
+#define SYMRELAY_ENOMEM (-12)
+#define SYMRELAY_ENOENT (-2)
+#define SYMRELAY_ECUDA (-1000) /* CUDA failure: fatal for the batch, see symrelay_last_error() */
+
+/* per-frame status word written by the kernels: bits 0..7 code, bits 8..15 opened tag */
+#define SYMRELAY_ST_OK 0u
+#define SYMRELAY_ST_BAD_MAC 1u            /* pull returned -1: that slot's state is untouched */
+#define SYMRELAY_ST_TOO_SHORT 2u          /* wire frame shorter than 17 bytes after the prefix */
+#define SYMRELAY_ST_EXTRACT_THROW 3u      /* the reference would throw a TypeError here (utils.ts:38-50) */
+#define SYMRELAY_ST_EXTRACT_UNSUPPORTED 4u /* value shape outside the GPU extractor's domain: use the JS helper */
+#define SYMRELAY_ST_PENDING 0xffu
+#define SYMRELAY_STATUS_CODE(s) ((s) & 0xffu)
+#define SYMRELAY_STATUS_TAG(s) (((s) >> 8) & 0xffu)
+
+/* descriptor flags (upper byte of len_flags) */
+#define SYMRELAY_F_TAG_MASK 0x03000000u /* secretstream tag for seal: MESSAGE 0, PUSH 1, REKEY 2, FINAL 3 */
+#define SYMRELAY_F_TAG_SHIFT 24
+#define SYMRELAY_F_OPEN 0x04000000u     /* frame is an inbound wire frame to open (else: seal) */
+#define SYMRELAY_F_EXTRACT 0x08000000u  /* also run the SSE `data:` test + delta extraction on the plaintext */
+#define SYMRELAY_LEN_MASK 0x00ffffffu
+
+/* provider kinds: src/constants.ts:22-29 (lmstudio / oobabooga / unknown take the default branch) */
+enum symrelay_provider {
+    SYMRELAY_PROVIDER_DEFAULT = 0, /* litellm, lmstudio, oobabooga, anything else: utils.ts:45-50 */
+    SYMRELAY_PROVIDER_OLLAMA = 1,  /* ollama, openwebui: utils.ts:38-42 */
+    SYMRELAY_PROVIDER_LLAMACPP = 2 /* utils.ts:43-44 */
+};
+
+/*
+ * One frame of a batch ("key, nonce/state, offset, length" of the north star):
+ * the key and nonce live in the device-resident state table, addressed by slot.
+ *   seal: plaintext  = in  + in_off  (in_off  % 16 == 0),  mlen = len
+ *         wire frame -> out + out_off (out_off % 16 == 12), mlen + 20 bytes
+ *         (in place allowed with in == out and in_off == out_off + 4: the layout
+ *          secret-stream's `_write` uses, `wrapped.set(data, 4)`)
+ *   open: wire frame = in  + in_off  (in_off  % 16 == 12), mlen + 20 bytes, len = mlen
+ *         plaintext  -> out + out_off (out_off % 16 == 0)
+ * A batch holds at most ONE frame per (slot, direction): frames of one stream
+ * are MAC-chained and go into consecutive batches.
+ * Arenas must be readable up to the next 16-byte boundary past each frame.
+ */
+typedef struct symrelay_desc {
+    uint32_t slot;
+    uint32_t in_off;
+    uint32_t out_off;
+    uint32_t len_flags; /* len (24 bits) | SYMRELAY_F_* */
+} symrelay_desc;
+
+/* Work tile produced by symrelay_plan(): a warp's worth of frames. */
+typedef struct symrelay_tile {
+    uint32_t first;   /* index of the tile's first descriptor */
+    uint32_t n_kind;  /* bits 0..15 frames in the tile, bit 16: bulk tile (one frame, > 32 ChaCha blocks) */
+} symrelay_tile;
+
+/* Result of the fused extractor for one frame (see symrelay_batch_* `extract` argument). */
+typedef struct symrelay_delta {
+    uint32_t off; /* byte offset into the delta arena */
+    uint32_t len; /* WTF-8 bytes appended to `completion` (provider.ts:243) */
+} symrelay_delta;
+
+typedef struct symrelay_opts {
+    uint32_t max_streams;     /* capacity of the slot table (default 65536) */
+    uint32_t pipeline_depth;  /* host-batch pipeline stages (default 4) */
+    uint64_t stage_bytes;     /* device staging bytes per stage and direction (default 64 MiB) */
+    uint32_t max_batch_frames; /* descriptors per host batch (default 131072) */
+    uint32_t flags;
+} symrelay_opts;
+
+typedef struct symrelay_ctx symrelay_ctx;
+
+/* ---- lifetime ------------------------------------------------------------ */
+SYMRELAY_API int symrelay_abi_version(void);
+/* Creates a context on gpu_ids[0..n_gpus) (n_gpus >= 1).  Slots are sharded
+ * slot % n_gpus, no state ever crosses GPUs.  Hook:
+ * once per process, before hyperswarm's 'connection' events (provider.ts:55-58). */
+SYMRELAY_API symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opts *opts);
+SYMRELAY_API void symrelay_destroy(symrelay_ctx *ctx);
+SYMRELAY_API const char *symrelay_last_error(symrelay_ctx *ctx);
+SYMRELAY_API const char *symrelay_strerror(int code);
+/* kernels launched by this context so far (bench.py's gpu_launches) */
+SYMRELAY_API uint64_t symrelay_launch_count(symrelay_ctx *ctx);
+
+/* ---- streams: replaces sodium-secretstream's Push/Pull construction -------
+ * (`new Push(tx)` / `Pull.init(header)` in secret-stream `_setupSecretStream`;
+ * the objects typed at src/types.ts:168-177).  `*_init_len` is 24 (a header:
+ * the sub-key is derived with HChaCha20 on the GPU, libsodium init_push/_pull)
+ * or 52 (an already initialised libsodium state to adopt), or 0 with a NULL
+ * key to leave that direction closed. */
+SYMRELAY_API int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, const uint8_t *tx_init, int tx_init_len,
+                         const uint8_t *rx_key, const uint8_t *rx_init, int rx_init_len, int provider_kind,
+                         uint32_t *slot_out);
+/* Batched variant for connection churn: n streams, keys
+ * 32 B each, inits `init_len` bytes each (24 or 52), slots_out[n]. */
+SYMRELAY_API int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_keys, const uint8_t *tx_inits,
+                               const uint8_t *rx_keys, const uint8_t *rx_inits, int init_len, int provider_kind,
+                               uint32_t *slots_out);
+SYMRELAY_API int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot);
+/* Copies the live libsodium-compatible 52-byte states back (either may be NULL). */
+SYMRELAY_API int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_t tx_state[SYMRELAY_STATEBYTES],
+                           uint8_t rx_state[SYMRELAY_STATEBYTES]);
+
+/* ---- planning: pack descriptors into warp tiles (host, no GPU) ------------
+ * Writes at most max_tiles tiles -- packed tiles (several small frames that
+ * are consecutive in `desc`) first, then *n_bulk_out bulk tiles (one frame of
+ * more than 30 payload blocks each) -- and returns the total number needed
+ * (call with tiles == NULL to size), or SYMRELAY_EINVAL for a bad descriptor. */
+SYMRELAY_API int64_t symrelay_plan(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles, uint32_t max_tiles,
+                      uint32_t *n_bulk_out);
+/* Validates one descriptor's alignment and length rules; 0 or SYMRELAY_EINVAL. */
+SYMRELAY_API int symrelay_desc_check(const symrelay_desc *d);
+
+/* ---- synchronous batch: replaces N calls of push/pull ----------------------
+ * (sodium.crypto_secretstream_xchacha20poly1305_push / _pull, one frame each,
+ * reached from provider.ts:248 / :174).  Mixed seal and open frames allowed. */
+/* All pointers are DEVICE memory on the context's GPU `gpu_index`; the launch
+ * goes to `cuda_stream` (a cudaStream_t, NULL = default stream) and returns
+ * without synchronising.  d_delta / d_delta_arena may be NULL when no
+ * descriptor carries SYMRELAY_F_EXTRACT. */
+SYMRELAY_API int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
+                          const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
+                          const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, symrelay_delta *d_delta,
+                          uint8_t *d_delta_arena, void *cuda_stream);
+/* HOST buffers (pinned from symrelay_alloc_pinned for full speed, pageable
+ * accepted): plans, copies in, launches, copies out, waits.  status[n] and, if
+ * any descriptor has F_EXTRACT, delta[n] + delta_arena (delta_arena_bytes) are
+ * filled.  in_bytes/out_bytes are the arena sizes (multiples of 16). */
+SYMRELAY_API int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, const uint8_t *in,
+                        uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
+                        symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes);
+/* Pipelined form of the same call: returns a ticket (>= 0) at once; buffers
+ * must stay valid until symrelay_batch_wait(ticket) returns.  Batches execute
+ * in submission order, so consecutive batches may carry consecutive frames of
+ * the same streams. */
+SYMRELAY_API int64_t symrelay_batch_submit(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, const uint8_t *in,
+                              uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
+                              symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes);
+SYMRELAY_API int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket);
+
+/* pinned host memory for arenas (the N-API shim exposes it as an external ArrayBuffer) */
+SYMRELAY_API void *symrelay_alloc_pinned(symrelay_ctx *ctx, uint64_t bytes);
+SYMRELAY_API void symrelay_free_pinned(symrelay_ctx *ctx, void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SYMRELAY_H */

@@ -1,0 +1,80 @@
+"""ctypes binding of libsymrelay.so (include/symrelay.h).
+
+This is the only way the package computes anything: if the CUDA library is
+missing the import fails loudly -- there is no CPU fallback (BASELINE.json
+north_star)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "libsymrelay.so")
+
+# every symbol include/symrelay.h declares (tests/test_abi_symbols.py cross-checks the header)
+EXPORTS = (
+    "symrelay_abi_version", "symrelay_create", "symrelay_destroy", "symrelay_last_error", "symrelay_strerror",
+    "symrelay_launch_count", "symrelay_stream_open", "symrelay_stream_open_batch", "symrelay_stream_close",
+    "symrelay_stream_export", "symrelay_plan", "symrelay_desc_check", "symrelay_batch_device",
+    "symrelay_batch_host", "symrelay_batch_submit", "symrelay_batch_wait", "symrelay_alloc_pinned",
+    "symrelay_free_pinned",
+)
+
+
+class SymrelayOpts(C.Structure):
+    _fields_ = [("max_streams", C.c_uint32), ("pipeline_depth", C.c_uint32), ("stage_bytes", C.c_uint64),
+                ("max_batch_frames", C.c_uint32), ("flags", C.c_uint32)]
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError(
+            f"{SO_PATH} is missing: build it with `python -m symmetry_b200.build` (needs nvcc). "
+            "symmetry_b200 has no CPU fallback.")
+    L = C.CDLL(SO_PATH)
+    vp, u32, u64, i64, ci = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int64, C.c_int
+    L.symrelay_abi_version.restype = ci
+    L.symrelay_create.restype = vp
+    L.symrelay_create.argtypes = [C.POINTER(ci), ci, C.POINTER(SymrelayOpts)]
+    L.symrelay_destroy.argtypes = [vp]
+    L.symrelay_destroy.restype = None
+    L.symrelay_last_error.restype = C.c_char_p
+    L.symrelay_last_error.argtypes = [vp]
+    L.symrelay_strerror.restype = C.c_char_p
+    L.symrelay_strerror.argtypes = [ci]
+    L.symrelay_launch_count.restype = u64
+    L.symrelay_launch_count.argtypes = [vp]
+    L.symrelay_stream_open.restype = ci
+    L.symrelay_stream_open.argtypes = [vp, vp, vp, ci, vp, vp, ci, ci, C.POINTER(u32)]
+    L.symrelay_stream_open_batch.restype = ci
+    L.symrelay_stream_open_batch.argtypes = [vp, u32, vp, vp, vp, vp, ci, ci, vp]
+    L.symrelay_stream_close.restype = ci
+    L.symrelay_stream_close.argtypes = [vp, u32]
+    L.symrelay_stream_export.restype = ci
+    L.symrelay_stream_export.argtypes = [vp, u32, vp, vp]
+    L.symrelay_plan.restype = i64
+    L.symrelay_plan.argtypes = [vp, u32, vp, u32, C.POINTER(u32)]
+    L.symrelay_desc_check.restype = ci
+    L.symrelay_desc_check.argtypes = [vp]
+    L.symrelay_batch_device.restype = ci
+    L.symrelay_batch_device.argtypes = [vp, ci, vp, u32, vp, u32, u32, vp, vp, vp, vp, vp, vp]
+    L.symrelay_batch_host.restype = ci
+    L.symrelay_batch_host.argtypes = [vp, vp, u32, vp, u64, vp, u64, vp, vp, vp, u64]
+    L.symrelay_batch_submit.restype = i64
+    L.symrelay_batch_submit.argtypes = [vp, vp, u32, vp, u64, vp, u64, vp, vp, vp, u64]
+    L.symrelay_batch_wait.restype = ci
+    L.symrelay_batch_wait.argtypes = [vp, i64]
+    L.symrelay_alloc_pinned.restype = vp
+    L.symrelay_alloc_pinned.argtypes = [vp, u64]
+    L.symrelay_free_pinned.restype = None
+    L.symrelay_free_pinned.argtypes = [vp, vp]
+    if L.symrelay_abi_version() != 1:
+        raise ImportError("libsymrelay.so ABI version mismatch")
+    _lib = L
+    return L

@@ -1,0 +1,62 @@
+// plan.h -- host-side packing of frame descriptors into warp tiles.
+//
+// The reference handles one frame per `peer.write` call
+// (/root/reference/src/provider.ts:248); here a batch of frames from many
+// connections is cut into warp-sized tiles: consecutive small frames whose
+// ChaCha20 block counts (2 + ceil(mlen/64) each) sum to <= 32 share a warp,
+// a frame with more than 30 payload blocks gets a bulk tile of its own.
+#pragma once
+#include <stdint.h>
+
+#include "../../include/symrelay.h"
+
+static inline uint32_t symrelay_nblocks(uint32_t mlen) { return 2u + ((mlen + 63u) >> 6); }
+
+static inline int symrelay_desc_check_inline(const symrelay_desc *d) {
+    const uint32_t mlen = d->len_flags & SYMRELAY_LEN_MASK;
+    if (mlen > SYMRELAY_MAX_FRAME) return SYMRELAY_EINVAL;
+    if (d->len_flags & SYMRELAY_F_OPEN) {
+        if ((d->in_off & 15u) != 12u || (d->out_off & 15u) != 0u) return SYMRELAY_EINVAL;
+    } else {
+        if ((d->in_off & 15u) != 0u || (d->out_off & 15u) != 12u) return SYMRELAY_EINVAL;
+    }
+    return 0;
+}
+
+// Two passes over the descriptors: packed tiles first, bulk tiles after them.
+static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles,
+                                           uint32_t max_tiles, uint32_t *n_bulk_out) {
+    uint64_t n_tiles = 0;
+    uint32_t n_bulk = 0;
+    uint32_t run_first = 0, run_n = 0, run_blocks = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        if (symrelay_desc_check_inline(&desc[i])) return SYMRELAY_EINVAL;
+        const uint32_t nc = symrelay_nblocks(desc[i].len_flags & SYMRELAY_LEN_MASK);
+        const bool bulk = nc > 32u;
+        if (bulk || run_blocks + nc > 32u || run_n == 16u) {
+            if (run_n) {
+                if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = run_first; tiles[n_tiles].n_kind = run_n; }
+                n_tiles++;
+            }
+            run_n = 0; run_blocks = 0;
+        }
+        if (bulk) { n_bulk++; continue; }
+        if (run_n == 0) run_first = i;
+        run_n++; run_blocks += nc;
+    }
+    if (run_n) {
+        if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = run_first; tiles[n_tiles].n_kind = run_n; }
+        n_tiles++;
+    }
+    if (n_bulk) {
+        for (uint32_t i = 0; i < n; i++) {
+            const uint32_t nc = symrelay_nblocks(desc[i].len_flags & SYMRELAY_LEN_MASK);
+            if (nc > 32u) {
+                if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = 1u | (1u << 16); }
+                n_tiles++;
+            }
+        }
+    }
+    if (n_bulk_out) *n_bulk_out = n_bulk;
+    return (int64_t)n_tiles;
+}

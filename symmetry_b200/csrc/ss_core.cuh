@@ -1,0 +1,548 @@
+// ss_core.cuh -- warp-level secretstream (XChaCha20-Poly1305) seal/open for sm_100a.
+//
+// What it computes: libsodium's crypto_secretstream_xchacha20poly1305_push/_pull
+// plus @hyperswarm/secret-stream's uint24-LE framing -- the arithmetic behind
+// `peer.write(chunk)` (/root/reference/src/provider.ts:248) and `peer.on('data')`
+// (:174); spec in SURVEY.md section 8(a) rows A9/A10/A12.
+//
+// Mapping ("warp-per-stream, thread-per-block keystream"):
+//   * one lane = one 64-byte ChaCha20 block: lane b==0 makes the Poly1305 key
+//     (ic=0), b==1 the tag block (ic=1), b>=2 the payload keystream (ic=b);
+//   * a PACKED tile puts several small frames side by side in one warp
+//     (sum of block counts <= 32); a BULK tile is one frame whose lanes loop
+//     with stride 32 over its blocks;
+//   * Poly1305 runs lane-parallel: every lane Horner-reduces its own 64-byte
+//     window of the MAC input with r, the lane partials are aligned with
+//     r^E (per-lane square-and-multiply; bulk lanes first fold their strided
+//     windows with r^128) and summed with a segmented warp-shuffle tree;
+//   * the frame's leader lane finalises the tag, writes/compares it and
+//     advances the per-stream nonce chain in the HBM state table.
+//
+// The same source is compiled (a) by nvcc for sm_100a -- the product -- and
+// (b) by g++ under tests/emu/ with a 32-thread warp emulator, which exists only
+// so the lane logic can be unit-tested on a machine without a GPU.  (b) is test
+// infrastructure; nothing in the product links or loads it.
+#pragma once
+#include <stdint.h>
+
+#ifdef SS_HOST_EMU
+#include "emu_warp.h"  // SS_DEV, uint4, ss_lane(), collectives and bit intrinsics for the emulator
+#else
+#define SS_DEV __device__ __forceinline__
+#define SS_NOINLINE __device__ __noinline__
+SS_DEV uint32_t ss_lane() { return threadIdx.x & 31u; }
+SS_DEV uint32_t ss_shfl(uint32_t v, uint32_t src) { return __shfl_sync(0xffffffffu, v, (int)src); }
+SS_DEV uint32_t ss_shfl_up(uint32_t v, uint32_t d) { return __shfl_up_sync(0xffffffffu, v, d); }
+SS_DEV uint32_t ss_shfl_down(uint32_t v, uint32_t d) { return __shfl_down_sync(0xffffffffu, v, d); }
+SS_DEV uint32_t ss_reduce_or(uint32_t v) { return __reduce_or_sync(0xffffffffu, v); }
+SS_DEV uint32_t ss_reduce_max(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
+SS_DEV uint32_t ss_popc(uint32_t v) { return (uint32_t)__popc(v); }
+SS_DEV uint32_t ss_clz(uint32_t v) { return (uint32_t)__clz((int)v); }
+SS_DEV uint32_t ss_rotl16(uint32_t x) { return __byte_perm(x, 0, 0x1032); }
+SS_DEV uint32_t ss_rotl8(uint32_t x) { return __byte_perm(x, 0, 0x2103); }
+SS_DEV uint32_t ss_rotl12(uint32_t x) { return __funnelshift_l(x, x, 12); }
+SS_DEV uint32_t ss_rotl7(uint32_t x) { return __funnelshift_l(x, x, 7); }
+// (lo, hi) >> s, low 32 bits, 0 <= s < 32
+SS_DEV uint32_t ss_fsr(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
+#endif
+
+#define SS_F_OPEN 0x04000000u
+#define SS_F_EXTRACT 0x08000000u
+#define SS_ST_OK 0u
+#define SS_ST_BAD_MAC 1u
+
+struct SsDesc {
+    uint32_t slot, in_off, out_off, len_flags;
+};
+struct SsTile {
+    uint32_t first, n_kind;
+};
+struct SsArgs {
+    const SsDesc *desc;
+    const SsTile *tiles;
+    uint32_t n_tiles;
+    const uint8_t *in;
+    uint8_t *out;
+    uint4 *states;  // [slot][dir]: 3 x uint4 = k[0..3] | k[4..7] | {frame counter, inonce0, inonce1, meta}
+    uint32_t *status;
+};
+
+// ---------------------------------------------------------------- ChaCha20 --
+#define SS_QR(a, b, c, d)   \
+    a += b; d ^= a; d = ss_rotl16(d); \
+    c += d; b ^= c; b = ss_rotl12(b); \
+    a += b; d ^= a; d = ss_rotl8(d);  \
+    c += d; b ^= c; b = ss_rotl7(b);
+
+// RFC 8439 block function; x <- keystream words for block counter `ic`.
+SS_DEV void ss_chacha_block(const uint32_t k[8], uint32_t ic, uint32_t n0, uint32_t n1, uint32_t n2,
+                            uint32_t x[16]) {
+    x[0] = 0x61707865u; x[1] = 0x3320646eu; x[2] = 0x79622d32u; x[3] = 0x6b206574u;
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[4 + i] = k[i];
+    x[12] = ic; x[13] = n0; x[14] = n1; x[15] = n2;
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        SS_QR(x[0], x[4], x[8], x[12])
+        SS_QR(x[1], x[5], x[9], x[13])
+        SS_QR(x[2], x[6], x[10], x[14])
+        SS_QR(x[3], x[7], x[11], x[15])
+        SS_QR(x[0], x[5], x[10], x[15])
+        SS_QR(x[1], x[6], x[11], x[12])
+        SS_QR(x[2], x[7], x[8], x[13])
+        SS_QR(x[3], x[4], x[9], x[14])
+    }
+    x[0] += 0x61707865u; x[1] += 0x3320646eu; x[2] += 0x79622d32u; x[3] += 0x6b206574u;
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[4 + i] += k[i];
+    x[12] += ic; x[13] += n0; x[14] += n1; x[15] += n2;
+}
+
+// ---------------------------------------------------------------- Poly1305 --
+// 130-bit values in five 26-bit limbs; products with 32x32->64 multiply-adds.
+SS_DEV void ss_pmul(uint32_t h[5], const uint32_t a[5], const uint32_t b[5]) {
+    const uint32_t s1 = b[1] * 5u, s2 = b[2] * 5u, s3 = b[3] * 5u, s4 = b[4] * 5u;
+    uint64_t d0 = (uint64_t)a[0] * b[0] + (uint64_t)a[1] * s4 + (uint64_t)a[2] * s3 + (uint64_t)a[3] * s2 + (uint64_t)a[4] * s1;
+    uint64_t d1 = (uint64_t)a[0] * b[1] + (uint64_t)a[1] * b[0] + (uint64_t)a[2] * s4 + (uint64_t)a[3] * s3 + (uint64_t)a[4] * s2;
+    uint64_t d2 = (uint64_t)a[0] * b[2] + (uint64_t)a[1] * b[1] + (uint64_t)a[2] * b[0] + (uint64_t)a[3] * s4 + (uint64_t)a[4] * s3;
+    uint64_t d3 = (uint64_t)a[0] * b[3] + (uint64_t)a[1] * b[2] + (uint64_t)a[2] * b[1] + (uint64_t)a[3] * b[0] + (uint64_t)a[4] * s4;
+    uint64_t d4 = (uint64_t)a[0] * b[4] + (uint64_t)a[1] * b[3] + (uint64_t)a[2] * b[2] + (uint64_t)a[3] * b[1] + (uint64_t)a[4] * b[0];
+    uint32_t c;
+    c = (uint32_t)(d0 >> 26); h[0] = (uint32_t)d0 & 0x3ffffffu; d1 += c;
+    c = (uint32_t)(d1 >> 26); h[1] = (uint32_t)d1 & 0x3ffffffu; d2 += c;
+    c = (uint32_t)(d2 >> 26); h[2] = (uint32_t)d2 & 0x3ffffffu; d3 += c;
+    c = (uint32_t)(d3 >> 26); h[3] = (uint32_t)d3 & 0x3ffffffu; d4 += c;
+    c = (uint32_t)(d4 >> 26); h[4] = (uint32_t)d4 & 0x3ffffffu;
+    h[0] += c * 5u;
+    c = h[0] >> 26; h[0] &= 0x3ffffffu; h[1] += c;
+}
+
+// acc <- (acc + block) * r for the 16-byte block (t0..t3) with the given 2^128 bit.
+SS_DEV void ss_pblock(uint32_t acc[5], uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, uint32_t hibit,
+                      const uint32_t r[5]) {
+    uint32_t a[5];
+    a[0] = acc[0] + (t0 & 0x3ffffffu);
+    a[1] = acc[1] + (ss_fsr(t0, t1, 26) & 0x3ffffffu);
+    a[2] = acc[2] + (ss_fsr(t1, t2, 20) & 0x3ffffffu);
+    a[3] = acc[3] + (ss_fsr(t2, t3, 14) & 0x3ffffffu);
+    a[4] = acc[4] + ((t3 >> 8) | hibit);
+    ss_pmul(acc, a, r);
+}
+
+// Horner over the first `nbytes` (0..64) bytes of a 64-byte window.  Bytes past
+// nbytes must already be zero except for the 0x01 terminator of a partial block.
+SS_DEV void ss_phorner(uint32_t acc[5], const uint32_t w[16], uint32_t nbytes, const uint32_t r[5]) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if ((uint32_t)(16 * i) < nbytes) {
+            const uint32_t hibit = ((uint32_t)(16 * i + 16) <= nbytes) ? (1u << 24) : 0u;
+            ss_pblock(acc, w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3], hibit, r);
+        }
+    }
+}
+
+// OR the 4-byte little-endian value `val` into the window at byte offset `o`
+// (any alignment, may hang over either edge).
+SS_DEV void ss_insert(uint32_t w[16], int o, uint32_t val) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const int d = o - 4 * i;
+        if (d == 0) w[i] |= val;
+        else if (d > 0 && d < 4) w[i] |= val << (8 * d);
+        else if (d < 0 && d > -4) w[i] |= val >> (8 * -d);
+    }
+}
+
+// Zero the bytes of the window at offsets >= n (n may be <= 0 or >= 64).
+SS_DEV void ss_keep_bytes(uint32_t w[16], int n) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const int nb = n - 4 * i;
+        if (nb <= 0) w[i] = 0;
+        else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
+    }
+}
+
+// Full reduction mod 2^130-5, + s, -> 16-byte tag as four words.
+SS_DEV void ss_pfinal(const uint32_t hin[5], const uint32_t s[4], uint32_t mac[4]) {
+    uint32_t h0 = hin[0], h1 = hin[1], h2 = hin[2], h3 = hin[3], h4 = hin[4], c;
+    c = h0 >> 26; h0 &= 0x3ffffffu; h1 += c;
+    c = h1 >> 26; h1 &= 0x3ffffffu; h2 += c;
+    c = h2 >> 26; h2 &= 0x3ffffffu; h3 += c;
+    c = h3 >> 26; h3 &= 0x3ffffffu; h4 += c;
+    c = h4 >> 26; h4 &= 0x3ffffffu; h0 += c * 5u;
+    c = h0 >> 26; h0 &= 0x3ffffffu; h1 += c;
+    c = h1 >> 26; h1 &= 0x3ffffffu; h2 += c;
+    c = h2 >> 26; h2 &= 0x3ffffffu; h3 += c;
+    c = h3 >> 26; h3 &= 0x3ffffffu; h4 += c;
+    c = h4 >> 26; h4 &= 0x3ffffffu; h0 += c * 5u;
+    c = h0 >> 26; h0 &= 0x3ffffffu; h1 += c;
+    uint32_t g0 = h0 + 5u; c = g0 >> 26; g0 &= 0x3ffffffu;
+    uint32_t g1 = h1 + c; c = g1 >> 26; g1 &= 0x3ffffffu;
+    uint32_t g2 = h2 + c; c = g2 >> 26; g2 &= 0x3ffffffu;
+    uint32_t g3 = h3 + c; c = g3 >> 26; g3 &= 0x3ffffffu;
+    uint32_t g4 = h4 + c - (1u << 26);
+    const uint32_t m = (g4 >> 31) - 1u;  // all ones when h >= p
+    h0 = (h0 & ~m) | (g0 & m); h1 = (h1 & ~m) | (g1 & m); h2 = (h2 & ~m) | (g2 & m);
+    h3 = (h3 & ~m) | (g3 & m); h4 = (h4 & ~m) | (g4 & m);
+    const uint32_t w0 = h0 | (h1 << 26), w1 = (h1 >> 6) | (h2 << 20), w2 = (h2 >> 12) | (h3 << 14),
+                   w3 = (h3 >> 18) | (h4 << 8);
+    uint64_t f;
+    f = (uint64_t)w0 + s[0]; mac[0] = (uint32_t)f;
+    f = (uint64_t)w1 + s[1] + (f >> 32); mac[1] = (uint32_t)f;
+    f = (uint64_t)w2 + s[2] + (f >> 32); mac[2] = (uint32_t)f;
+    f = (uint64_t)w3 + s[3] + (f >> 32); mac[3] = (uint32_t)f;
+}
+
+// Clamp r (RFC 8439 2.5) and split into limbs.
+SS_DEV void ss_r_limbs(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, uint32_t r[5]) {
+    t0 &= 0x0fffffffu; t1 &= 0x0ffffffcu; t2 &= 0x0ffffffcu; t3 &= 0x0ffffffcu;
+    r[0] = t0 & 0x3ffffffu;
+    r[1] = ss_fsr(t0, t1, 26) & 0x3ffffffu;
+    r[2] = ss_fsr(t1, t2, 20) & 0x3ffffffu;
+    r[3] = ss_fsr(t2, t3, 14) & 0x3ffffffu;
+    r[4] = t3 >> 8;
+}
+
+// libsodium rekey (SURVEY 8(a) spec box): k, inonce <- (k ‖ inonce) ^ ChaCha20(k, n, ic=0)[0:40]; counter <- 1.
+#ifndef SS_HOST_EMU
+SS_NOINLINE
+#else
+static
+#endif
+void ss_rekey(uint32_t k[8], uint32_t nn[3]) {
+    uint32_t x[16];
+    ss_chacha_block(k, 0, nn[0], nn[1], nn[2], x);
+#pragma unroll
+    for (int i = 0; i < 8; i++) k[i] ^= x[i];
+    nn[1] ^= x[8];
+    nn[2] ^= x[9];
+    nn[0] = 1;
+}
+
+// ------------------------------------------------------- payload load/store --
+// Loads up to 64 bytes (16-byte pieces that start below nbytes) from a 16-aligned address.
+SS_DEV void ss_load64(const uint8_t *p, int nbytes, uint32_t m[16]) {
+    const uint4 *q = reinterpret_cast<const uint4 *>(p);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint4 v;
+        v.x = v.y = v.z = v.w = 0;
+        if (16 * i < nbytes) v = q[i];
+        m[4 * i] = v.x; m[4 * i + 1] = v.y; m[4 * i + 2] = v.z; m[4 * i + 3] = v.w;
+    }
+}
+
+// Stores exactly nbytes (1..64) bytes to a 16-aligned address: whole 16-byte
+// pieces as one vector store, the ragged tail byte by byte (the MAC or the next
+// frame's bytes may follow immediately).
+SS_DEV void ss_store64(uint8_t *p, int nbytes, const uint32_t m[16]) {
+    uint4 *q = reinterpret_cast<uint4 *>(p);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if (16 * i + 16 <= nbytes) {
+            uint4 v;
+            v.x = m[4 * i]; v.y = m[4 * i + 1]; v.z = m[4 * i + 2]; v.w = m[4 * i + 3];
+            q[i] = v;
+        } else if (16 * i < nbytes) {
+            const int rem = nbytes - 16 * i;
+#pragma unroll
+            for (int j = 0; j < 15; j++)
+                if (j < rem) p[16 * i + j] = (uint8_t)(m[4 * i + (j >> 2)] >> (8 * (j & 3)));
+        }
+    }
+}
+
+SS_DEV void ss_store_mac(uint8_t *p, const uint32_t mac[4]) {
+    if ((reinterpret_cast<uintptr_t>(p) & 3u) == 0) {
+        uint32_t *q = reinterpret_cast<uint32_t *>(p);
+        q[0] = mac[0]; q[1] = mac[1]; q[2] = mac[2]; q[3] = mac[3];
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; j++) p[j] = (uint8_t)(mac[j >> 2] >> (8 * (j & 3)));
+    }
+}
+
+SS_DEV uint32_t ss_mac_differs(const uint8_t *p, const uint32_t mac[4]) {
+    uint32_t diff = 0;
+    if ((reinterpret_cast<uintptr_t>(p) & 3u) == 0) {
+        const uint32_t *q = reinterpret_cast<const uint32_t *>(p);
+        diff = (q[0] ^ mac[0]) | (q[1] ^ mac[1]) | (q[2] ^ mac[2]) | (q[3] ^ mac[3]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; j++) diff |= (uint32_t)p[j] ^ ((mac[j >> 2] >> (8 * (j & 3))) & 0xffu);
+    }
+    return diff;
+}
+
+// --------------------------------------------------------------- the tile ---
+// One warp processes one tile.  BULK == false: up to 16 small frames packed in
+// the warp, one pass.  BULK == true: one frame of any size, lanes stride by 32.
+template <bool BULK>
+SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
+    const uint32_t lane = ss_lane();
+    const SsTile tile = a.tiles[tile_idx];
+    const uint32_t nfr = BULK ? 1u : (tile.n_kind & 0xffffu);
+
+    // ---- lane -> (frame f, first lane st of that frame) ---------------------
+    uint32_t d_slot = 0, d_in = 0, d_out = 0, d_lf = 0, my_nc = 0;
+    if (lane < nfr) {
+        const SsDesc d = a.desc[tile.first + lane];
+        d_slot = d.slot; d_in = d.in_off; d_out = d.out_off; d_lf = d.len_flags;
+        my_nc = 2u + (((d_lf & 0xffffffu) + 63u) >> 6);
+    }
+    uint32_t f = 0, st = 0;
+    bool valid = true;
+    if (!BULK) {
+        uint32_t incl = my_nc;
+#pragma unroll
+        for (uint32_t o = 1; o < 32; o <<= 1) {
+            const uint32_t t = ss_shfl_up(incl, o);
+            if (lane >= o) incl += t;
+        }
+        const uint32_t startmask = ss_reduce_or(lane < nfr ? (1u << (incl - my_nc)) : 0u);
+        const uint32_t total = ss_shfl(incl, 31);
+        const uint32_t below = startmask & (0xffffffffu >> (31u - lane));
+        f = ss_popc(below) - 1u;
+        st = 31u - ss_clz(below);
+        valid = lane < total;
+    }
+    const uint32_t slot = ss_shfl(d_slot, f);
+    const uint32_t in_off = ss_shfl(d_in, f);
+    const uint32_t out_off = ss_shfl(d_out, f);
+    const uint32_t lf = ss_shfl(d_lf, f);
+
+    const uint32_t mlen = lf & 0xffffffu;
+    const bool is_open = (lf & SS_F_OPEN) != 0;
+    const uint32_t nc = 2u + ((mlen + 63u) >> 6);          // ChaCha20 blocks of this frame
+    const uint32_t T = 80u + mlen + (mlen & 15u);          // MAC input bytes (libsodium pad quirk)
+    const uint32_t NB = (T + 15u) >> 4;                    // Poly1305 blocks
+    const uint32_t V = 64u + mlen;                         // LE64(64+mlen) sits at stream offset T-8
+    const uint8_t *src = a.in + in_off + (is_open ? 4u : 0u);   // payload in  (16-aligned)
+    uint8_t *dst = a.out + out_off + (is_open ? 0u : 4u);       // payload out (16-aligned)
+    uint4 *sp = a.states + ((size_t)slot * 2u + (is_open ? 1u : 0u)) * 3u;
+
+    uint32_t k[8], nn[3], meta = 0;
+    {
+        uint4 s0, s1, s2;
+        s0.x = s0.y = s0.z = s0.w = 0; s1 = s0; s2 = s0;
+        if (valid) { s0 = sp[0]; s1 = sp[1]; s2 = sp[2]; }
+        k[0] = s0.x; k[1] = s0.y; k[2] = s0.z; k[3] = s0.w;
+        k[4] = s1.x; k[5] = s1.y; k[6] = s1.z; k[7] = s1.w;
+        nn[0] = s2.x; nn[1] = s2.y; nn[2] = s2.z; meta = s2.w;
+    }
+
+    uint32_t A[5] = {0, 0, 0, 0, 0};   // lane partial, to be scaled by r^E
+    uint32_t HX[5] = {0, 0, 0, 0, 0};  // bulk: partial of the final window (exponent 0)
+    uint32_t E = 0;
+    uint32_t r[5] = {0, 0, 0, 0, 0}, r128[5] = {0, 0, 0, 0, 0}, sw[4] = {0, 0, 0, 0};
+    uint32_t tagval = 0;               // lane b==1: seal -> wire tag byte, open -> decrypted tag
+    uint32_t keep[16];                 // packed open: plaintext held back until the MAC verdict
+    bool have_A = false;
+    const uint32_t niter = BULK ? ((nc + 1u + 31u) >> 5) : 1u;  // bulk walks virtual blocks 0..nc
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < niter; ++it) {
+        const uint32_t b = (lane - st) + 32u * it;
+        const bool has_block = valid && b < nc;
+        const bool need_ks = has_block && (!(BULK && is_open) || b < 2u);
+        uint32_t x[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) x[i] = 0;
+        if (need_ks) ss_chacha_block(k, b, nn[0], nn[1], nn[2], x);
+
+        if (it == 0) {
+            // Poly1305 key: r to every lane of the frame, s stays on the leader.
+            const uint32_t t0 = ss_shfl(x[0], st), t1 = ss_shfl(x[1], st), t2 = ss_shfl(x[2], st),
+                           t3 = ss_shfl(x[3], st);
+            ss_r_limbs(t0, t1, t2, t3, r);
+            sw[0] = x[4]; sw[1] = x[5]; sw[2] = x[6]; sw[3] = x[7];
+            if (BULK) {
+                uint32_t t[5];
+                ss_pmul(t, r, r);        // r^2
+                ss_pmul(r128, t, t);     // r^4
+#pragma unroll 1
+                for (int i = 0; i < 5; i++) {  // r^8 .. r^128
+                    ss_pmul(t, r128, r128);
+#pragma unroll
+                    for (int j = 0; j < 5; j++) r128[j] = t[j];
+                }
+            }
+        }
+
+        // ---- this lane's 64-byte window of the MAC input --------------------
+        // stream = B(64) ‖ c(mlen) ‖ 0^(mlen%16) ‖ LE64(0) ‖ LE64(64+mlen); window q covers [64q, 64q+64)
+        bool has_win = false;
+        uint32_t q = 0;
+        if (valid) {
+            if (b == 0) {
+                if (!BULK) { has_win = true; q = nc - 1u; }       // packed: the key lane takes the overflow window
+#pragma unroll
+                for (int i = 0; i < 16; i++) x[i] = 0;
+            } else if (b == 1) {
+                has_win = true; q = 0;
+                if (!is_open) {
+                    x[0] ^= (lf >> 24) & 3u;                        // (tag ‖ 0^63) ^ keystream
+                    tagval = x[0] & 0xffu;
+                    *reinterpret_cast<uint32_t *>(a.out + out_off) = (mlen + 17u) | (tagval << 24);
+                } else {
+                    const uint32_t hw = *reinterpret_cast<const uint32_t *>(a.in + in_off);
+                    const uint32_t c0 = hw >> 24;
+                    tagval = (x[0] ^ c0) & 0xffu;                  // decrypted tag
+                    x[0] = (x[0] & 0xffffff00u) | c0;              // MAC covers the wire byte
+                }
+            } else if (b < nc) {
+                has_win = true; q = b - 1u;
+                const uint32_t j = b - 2u;
+                const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
+                uint32_t m[16];
+                ss_load64(src + 64u * (size_t)j, cbytes, m);
+                if (!is_open) {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) x[i] ^= m[i];     // ciphertext
+                    ss_store64(dst + 64u * (size_t)j, cbytes, x);
+                } else {
+                    if (!BULK) {
+#pragma unroll
+                        for (int i = 0; i < 16; i++) keep[i] = x[i] ^ m[i];
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; i++) x[i] = m[i];      // MAC is over the ciphertext
+                }
+                ss_keep_bytes(x, cbytes);
+            } else if (BULK && b == nc) {
+                has_win = true; q = nc - 1u;                        // bulk: virtual block = overflow window
+            }
+        }
+        const int so = (int)(64u * q);
+        int nbytes = has_win ? (int)T - so : 0;
+        nbytes = nbytes < 0 ? 0 : (nbytes > 64 ? 64 : nbytes);
+        if (nbytes > 0) {
+            ss_insert(x, (int)T - 8 - so, V);
+            if (T & 15u) ss_insert(x, (int)T - so, 1u);            // Poly1305 terminator of the partial last block
+            uint32_t C[5] = {0, 0, 0, 0, 0};
+            ss_phorner(C, x, (uint32_t)nbytes, r);
+            const bool final_win = (uint32_t)so + 64u >= T;
+            if (BULK && final_win) {
+#pragma unroll
+                for (int i = 0; i < 5; i++) HX[i] = C[i];
+            } else {
+                if (BULK && have_A) {
+                    uint32_t t[5];
+                    ss_pmul(t, A, r128);
+#pragma unroll
+                    for (int i = 0; i < 5; i++) A[i] = t[i] + C[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 5; i++) A[i] = C[i];
+                }
+                have_A = true;
+                E = final_win ? 0u : NB - 4u * q - 4u;             // Poly1305 blocks after this window
+            }
+        }
+    }
+
+    // ---- align lane partials: A <- A * r^E ----------------------------------
+    {
+        const uint32_t maxe = ss_reduce_max(E);
+        const uint32_t bits = 32u - ss_clz(maxe);  // clz(0) == 32
+        uint32_t base[5];
+#pragma unroll
+        for (int i = 0; i < 5; i++) base[i] = r[i];
+#pragma unroll 1
+        for (uint32_t bit = 0; bit < bits; ++bit) {
+            if ((E >> bit) & 1u) {
+                uint32_t t[5];
+                ss_pmul(t, A, base);
+#pragma unroll
+                for (int i = 0; i < 5; i++) A[i] = t[i];
+            }
+            if (bit + 1u < bits) {
+                uint32_t t[5];
+                ss_pmul(t, base, base);
+#pragma unroll
+                for (int i = 0; i < 5; i++) base[i] = t[i];
+            }
+        }
+    }
+    if (BULK) {
+#pragma unroll
+        for (int i = 0; i < 5; i++) A[i] += HX[i];
+    }
+
+    // ---- segmented sum of the limb vectors onto the leader lane -------------
+    const uint32_t endl = BULK ? 31u : st + nc - 1u;
+#pragma unroll
+    for (uint32_t o = 1; o < 32; o <<= 1) {
+#pragma unroll
+        for (int i = 0; i < 5; i++) {
+            const uint32_t t = ss_shfl_down(A[i], o);
+            if (lane + o <= endl) A[i] += t;
+        }
+    }
+    const uint32_t tag_b1 = ss_shfl(tagval, st + 1u);  // st+1 <= 31 always (every frame has >= 2 lanes)
+
+    // ---- leader: tag, verdict, nonce chain -----------------------------------
+    const bool leader = valid && lane == st;
+    uint32_t ok = 1;
+    uint32_t mac[4] = {0, 0, 0, 0};
+    if (leader) {
+        ss_pfinal(A, sw, mac);
+        if (!is_open) ss_store_mac(dst + mlen, mac);
+        else ok = ss_mac_differs(src + mlen, mac) == 0 ? 1u : 0u;
+    }
+    ok = ss_shfl(ok, st);
+
+    if (is_open && ok) {
+        if (!BULK) {
+            const uint32_t b = lane - st;
+            if (valid && b >= 2u && b < nc) {
+                const uint32_t j = b - 2u;
+                const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
+                ss_store64(dst + 64u * (size_t)j, cbytes, keep);
+            }
+        }
+    }
+    if (BULK) {
+        // verified: second pass decrypts (lanes keep striding by 32 blocks); warp-uniform branch
+        if (is_open && ok) {
+#pragma unroll 1
+            for (uint32_t it = 0; it < niter; ++it) {
+                const uint32_t b = lane + 32u * it;
+                if (b >= 2u && b < nc) {
+                    const uint32_t j = b - 2u;
+                    const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
+                    uint32_t x[16], m[16];
+                    ss_chacha_block(k, b, nn[0], nn[1], nn[2], x);
+                    ss_load64(src + 64u * (size_t)j, cbytes, m);
+#pragma unroll
+                    for (int i = 0; i < 16; i++) x[i] ^= m[i];
+                    ss_store64(dst + 64u * (size_t)j, cbytes, x);
+                }
+            }
+        }
+    }
+
+    if (leader) {
+        const uint32_t frame_idx = tile.first + f;
+        if (ok) {
+            const uint32_t tag = is_open ? tag_b1 : ((lf >> 24) & 3u);
+            nn[1] ^= mac[0];
+            nn[2] ^= mac[1];
+            nn[0] += 1u;
+            if ((tag & 2u) || nn[0] == 0u) {
+                ss_rekey(k, nn);
+                uint4 s0, s1;
+                s0.x = k[0]; s0.y = k[1]; s0.z = k[2]; s0.w = k[3];
+                s1.x = k[4]; s1.y = k[5]; s1.z = k[6]; s1.w = k[7];
+                sp[0] = s0; sp[1] = s1;
+            }
+            uint4 s2;
+            s2.x = nn[0]; s2.y = nn[1]; s2.z = nn[2]; s2.w = meta;
+            sp[2] = s2;
+            a.status[frame_idx] = SS_ST_OK | (tag << 8);
+        } else {
+            a.status[frame_idx] = SS_ST_BAD_MAC;
+        }
+    }
+}

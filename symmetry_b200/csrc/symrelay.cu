@@ -1,0 +1,559 @@
+// symrelay.cu -- kernels + C ABI of the batched secretstream relay (sm_100a).
+//
+// Replaces, for all connections at once, the per-frame work that the reference
+// does on Node's main thread for every `peer.write(chunk)`
+// (/root/reference/src/provider.ts:248) and every inbound frame (:174):
+// secret-stream framing + libsodium secretstream push/pull.  See
+// include/symrelay.h for the boundary and DESIGN.md for layouts and rooflines.
+// There is deliberately no CPU path in this file: every entry point that
+// computes needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/symrelay.h"
+#include "plan.h"
+#include "ss_core.cuh"
+
+static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) == sizeof(SsTile), "ABI layout");
+
+// ------------------------------------------------------------------ kernels --
+// One warp per tile.  Packed tiles: several small frames per warp.
+__global__ void __launch_bounds__(128) ss_packed_kernel(SsArgs a) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= a.n_tiles) return;
+    ss_process_tile<false>(a, warp);
+}
+
+// Bulk tiles: one frame per warp, lanes stride over its 64-byte blocks.
+// a.tiles already points at the first bulk tile.
+__global__ void __launch_bounds__(128) ss_bulk_kernel(SsArgs a) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= a.n_tiles) return;
+    ss_process_tile<true>(a, warp);
+}
+
+// Stream set-up (libsodium init_push/init_pull): one thread per
+// (slot, direction).  rec = key[32] ‖ init[init_len]; init_len 24 derives the
+// sub-key with HChaCha20, 52 adopts an existing libsodium state, 0 clears.
+struct SsInitRec {
+    uint32_t slot_dir;  // slot * 2 + dir
+    uint32_t init_len;
+    uint32_t meta;
+    uint32_t pad;
+    uint8_t key[32];
+    uint8_t init[64];
+};
+static_assert(sizeof(SsInitRec) == 112, "init record layout");
+
+__global__ void ss_init_kernel(const SsInitRec *recs, uint32_t n, uint4 *states) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const SsInitRec *r = recs + i;
+    const uint32_t *kw = reinterpret_cast<const uint32_t *>(r->key);
+    const uint32_t *iw = reinterpret_cast<const uint32_t *>(r->init);
+    uint32_t k[8], nn[3];
+    if (r->init_len == 24u) {
+        // HChaCha20(key, header[0:16]): ChaCha20 rounds without the feed-forward, words 0..3 and 12..15
+        uint32_t x[16];
+        x[0] = 0x61707865u; x[1] = 0x3320646eu; x[2] = 0x79622d32u; x[3] = 0x6b206574u;
+#pragma unroll
+        for (int j = 0; j < 8; j++) x[4 + j] = kw[j];
+#pragma unroll
+        for (int j = 0; j < 4; j++) x[12 + j] = iw[j];
+#pragma unroll 1
+        for (int rr = 0; rr < 10; rr++) {
+            SS_QR(x[0], x[4], x[8], x[12])
+            SS_QR(x[1], x[5], x[9], x[13])
+            SS_QR(x[2], x[6], x[10], x[14])
+            SS_QR(x[3], x[7], x[11], x[15])
+            SS_QR(x[0], x[5], x[10], x[15])
+            SS_QR(x[1], x[6], x[11], x[12])
+            SS_QR(x[2], x[7], x[8], x[13])
+            SS_QR(x[3], x[4], x[9], x[14])
+        }
+        k[0] = x[0]; k[1] = x[1]; k[2] = x[2]; k[3] = x[3];
+        k[4] = x[12]; k[5] = x[13]; k[6] = x[14]; k[7] = x[15];
+        nn[0] = 1u; nn[1] = iw[4]; nn[2] = iw[5];
+    } else if (r->init_len == 52u) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) k[j] = iw[j];
+        nn[0] = iw[8]; nn[1] = iw[9]; nn[2] = iw[10];
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; j++) k[j] = 0;
+        nn[0] = nn[1] = nn[2] = 0;
+    }
+    uint4 *sp = states + (size_t)r->slot_dir * 3u;
+    sp[0] = make_uint4(k[0], k[1], k[2], k[3]);
+    sp[1] = make_uint4(k[4], k[5], k[6], k[7]);
+    sp[2] = make_uint4(nn[0], nn[1], nn[2], r->meta);
+}
+
+// --------------------------------------------------------------- host side --
+namespace {
+
+struct Stage {
+    uint8_t *d_ctrl = nullptr;   // tiles ‖ descs
+    uint8_t *h_ctrl = nullptr;   // pinned mirror
+    uint8_t *d_in = nullptr, *d_out = nullptr;
+    uint32_t *d_status = nullptr, *h_status = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_k = nullptr, ev_out = nullptr;
+    // in-flight batch bookkeeping
+    int64_t ticket = -1;
+    uint32_t n = 0;
+    uint32_t *user_status = nullptr;
+    bool busy = false;
+};
+
+struct Shard {
+    int dev = -1;
+    uint4 *d_states = nullptr;
+    cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;
+    std::vector<Stage> stages;
+    SsInitRec *h_init = nullptr, *d_init = nullptr;  // staging for stream_open
+    uint32_t init_cap = 0;
+    int64_t next_ticket_seq = 0;
+};
+
+}  // namespace
+
+struct symrelay_ctx {
+    int n_gpus = 0;
+    Shard shard[8];
+    symrelay_opts opts{};
+    std::vector<uint8_t> slot_state;      // 0 free, 1 open
+    std::vector<uint32_t> free_slots[8];  // per GPU (slot % n_gpus == gpu)
+    std::mutex mu;
+    std::string err;
+    std::atomic<uint64_t> launches{0};
+    int64_t ticket_counter = 0;
+};
+
+static thread_local char g_err[256];
+
+static int fail(symrelay_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[256];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    snprintf(g_err, sizeof g_err, "%s", buf);
+    return code;
+}
+
+#define CU(ctx, call)                                                                                      \
+    do {                                                                                                   \
+        cudaError_t e__ = (call);                                                                          \
+        if (e__ != cudaSuccess)                                                                            \
+            return fail(ctx, SYMRELAY_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+                        __LINE__);                                                                         \
+    } while (0)
+
+static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+
+static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, const symrelay_tile *d_tiles,
+                        uint32_t n_tiles, uint32_t n_bulk, const uint8_t *d_in, uint8_t *d_out, uint4 *d_states,
+                        uint32_t *d_status, cudaStream_t stream) {
+    const uint32_t n_packed = n_tiles - n_bulk;
+    SsArgs a;
+    a.desc = reinterpret_cast<const SsDesc *>(d_desc);
+    a.in = d_in;
+    a.out = d_out;
+    a.states = d_states;
+    a.status = d_status;
+    if (n_packed) {
+        a.tiles = reinterpret_cast<const SsTile *>(d_tiles);
+        a.n_tiles = n_packed;
+        const uint32_t threads = n_packed <= 148u * 8u ? 32u : 128u;  // few tiles: one warp per SM sub-partition
+        const uint32_t wpb = threads / 32u;
+        ss_packed_kernel<<<(n_packed + wpb - 1) / wpb, threads, 0, stream>>>(a);
+        ctx->launches++;
+    }
+    if (n_bulk) {
+        a.tiles = reinterpret_cast<const SsTile *>(d_tiles) + n_packed;
+        a.n_tiles = n_bulk;
+        const uint32_t threads = n_bulk <= 148u * 8u ? 32u : 128u;
+        const uint32_t wpb = threads / 32u;
+        ss_bulk_kernel<<<(n_bulk + wpb - 1) / wpb, threads, 0, stream>>>(a);
+        ctx->launches++;
+    }
+    CU(ctx, cudaGetLastError());
+    return 0;
+}
+
+extern "C" {
+
+int symrelay_abi_version(void) { return SYMRELAY_ABI_VERSION; }
+
+const char *symrelay_strerror(int code) {
+    switch (code) {
+        case SYMRELAY_OK: return "ok";
+        case SYMRELAY_EINVAL: return "invalid argument";
+        case SYMRELAY_EAGAIN: return "ring full, try again";
+        case SYMRELAY_ENOMEM: return "out of memory / slots";
+        case SYMRELAY_ENOENT: return "no such slot or ticket";
+        case SYMRELAY_ECUDA: return "CUDA failure";
+        default: return "unknown error";
+    }
+}
+
+const char *symrelay_last_error(symrelay_ctx *ctx) { return ctx ? ctx->err.c_str() : g_err; }
+
+uint64_t symrelay_launch_count(symrelay_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
+
+static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
+    sh.dev = dev;
+    CU(ctx, cudaSetDevice(dev));
+    const size_t table_bytes = (size_t)ctx->opts.max_streams * 2u * 48u;
+    CU(ctx, cudaMalloc(&sh.d_states, table_bytes));
+    CU(ctx, cudaMemset(sh.d_states, 0, table_bytes));
+    CU(ctx, cudaStreamCreateWithFlags(&sh.s_in, cudaStreamNonBlocking));
+    CU(ctx, cudaStreamCreateWithFlags(&sh.s_k, cudaStreamNonBlocking));
+    CU(ctx, cudaStreamCreateWithFlags(&sh.s_out, cudaStreamNonBlocking));
+    sh.init_cap = 4096;
+    CU(ctx, cudaHostAlloc(&sh.h_init, sizeof(SsInitRec) * sh.init_cap, cudaHostAllocDefault));
+    CU(ctx, cudaMalloc(&sh.d_init, sizeof(SsInitRec) * sh.init_cap));
+    sh.stages.resize(ctx->opts.pipeline_depth);
+    const size_t ctrl_bytes = (size_t)ctx->opts.max_batch_frames * (sizeof(symrelay_desc) + sizeof(symrelay_tile));
+    for (Stage &st : sh.stages) {
+        CU(ctx, cudaMalloc(&st.d_ctrl, ctrl_bytes));
+        CU(ctx, cudaHostAlloc(&st.h_ctrl, ctrl_bytes, cudaHostAllocDefault));
+        CU(ctx, cudaMalloc(&st.d_in, ctx->opts.stage_bytes));
+        CU(ctx, cudaMalloc(&st.d_out, ctx->opts.stage_bytes));
+        CU(ctx, cudaMalloc(&st.d_status, (size_t)ctx->opts.max_batch_frames * 4u));
+        CU(ctx, cudaHostAlloc(&st.h_status, (size_t)ctx->opts.max_batch_frames * 4u, cudaHostAllocDefault));
+        CU(ctx, cudaEventCreateWithFlags(&st.ev_in, cudaEventDisableTiming));
+        CU(ctx, cudaEventCreateWithFlags(&st.ev_k, cudaEventDisableTiming));
+        CU(ctx, cudaEventCreateWithFlags(&st.ev_out, cudaEventDisableTiming));
+    }
+    return 0;
+}
+
+static void shard_free(Shard &sh) {
+    if (sh.dev < 0) return;
+    cudaSetDevice(sh.dev);
+    if (sh.s_k) cudaStreamSynchronize(sh.s_k);
+    if (sh.s_out) cudaStreamSynchronize(sh.s_out);
+    for (Stage &st : sh.stages) {
+        cudaFree(st.d_ctrl); cudaFreeHost(st.h_ctrl); cudaFree(st.d_in); cudaFree(st.d_out);
+        cudaFree(st.d_status); cudaFreeHost(st.h_status);
+        if (st.ev_in) cudaEventDestroy(st.ev_in);
+        if (st.ev_k) cudaEventDestroy(st.ev_k);
+        if (st.ev_out) cudaEventDestroy(st.ev_out);
+    }
+    cudaFree(sh.d_states); cudaFreeHost(sh.h_init); cudaFree(sh.d_init);
+    if (sh.s_in) cudaStreamDestroy(sh.s_in);
+    if (sh.s_k) cudaStreamDestroy(sh.s_k);
+    if (sh.s_out) cudaStreamDestroy(sh.s_out);
+}
+
+symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opts *opts) {
+    if (n_gpus < 1 || n_gpus > 8 || !gpu_ids) {
+        fail(nullptr, SYMRELAY_EINVAL, "symrelay_create: n_gpus must be 1..8");
+        return nullptr;
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count < 1) {
+        fail(nullptr, SYMRELAY_ECUDA, "symrelay_create: no CUDA device (%s); this library has no CPU path",
+             e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+        return nullptr;
+    }
+    symrelay_ctx *ctx = new (std::nothrow) symrelay_ctx();
+    if (!ctx) return nullptr;
+    if (opts) ctx->opts = *opts;
+    if (!ctx->opts.max_streams) ctx->opts.max_streams = 65536;
+    if (!ctx->opts.pipeline_depth) ctx->opts.pipeline_depth = 4;
+    if (!ctx->opts.stage_bytes) ctx->opts.stage_bytes = 64ull << 20;
+    if (!ctx->opts.max_batch_frames) ctx->opts.max_batch_frames = 131072;
+    ctx->opts.stage_bytes = align_up(ctx->opts.stage_bytes, 256);
+    ctx->n_gpus = n_gpus;
+    for (int g = 0; g < n_gpus; g++) {
+        if (gpu_ids[g] < 0 || gpu_ids[g] >= count) {
+            fail(nullptr, SYMRELAY_EINVAL, "symrelay_create: gpu id %d out of range (have %d)", gpu_ids[g], count);
+            symrelay_destroy(ctx);
+            return nullptr;
+        }
+        if (shard_init(ctx, ctx->shard[g], gpu_ids[g]) != 0) {
+            snprintf(g_err, sizeof g_err, "%s", ctx->err.c_str());
+            symrelay_destroy(ctx);
+            return nullptr;
+        }
+    }
+    ctx->slot_state.assign(ctx->opts.max_streams, 0);
+    for (uint32_t s = ctx->opts.max_streams; s-- > 0;) ctx->free_slots[s % (uint32_t)n_gpus].push_back(s);
+    return ctx;
+}
+
+void symrelay_destroy(symrelay_ctx *ctx) {
+    if (!ctx) return;
+    for (int g = 0; g < ctx->n_gpus; g++) shard_free(ctx->shard[g]);
+    delete ctx;
+}
+
+// ---- streams ------------------------------------------------------------------
+static int push_init_recs(symrelay_ctx *ctx, Shard &sh, uint32_t n) {
+    CU(ctx, cudaSetDevice(sh.dev));
+    CU(ctx, cudaMemcpyAsync(sh.d_init, sh.h_init, sizeof(SsInitRec) * n, cudaMemcpyHostToDevice, sh.s_k));
+    ss_init_kernel<<<(n + 127) / 128, 128, 0, sh.s_k>>>(sh.d_init, n, sh.d_states);
+    ctx->launches++;
+    CU(ctx, cudaGetLastError());
+    CU(ctx, cudaStreamSynchronize(sh.s_k));  // h_init is reused by the next call
+    return 0;
+}
+
+static void fill_rec(SsInitRec *r, uint32_t slot, uint32_t dir, const uint8_t *key, const uint8_t *init, int init_len,
+                     uint32_t meta) {
+    memset(r, 0, sizeof *r);
+    r->slot_dir = slot * 2u + dir;
+    r->init_len = key ? (uint32_t)init_len : 0u;
+    r->meta = meta;
+    if (key) {
+        memcpy(r->key, key, 32);
+        memcpy(r->init, init, (size_t)init_len);
+    }
+}
+
+int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_keys, const uint8_t *tx_inits,
+                               const uint8_t *rx_keys, const uint8_t *rx_inits, int init_len, int provider_kind,
+                               uint32_t *slots_out) {
+    if (!ctx || !slots_out) return SYMRELAY_EINVAL;
+    if (init_len != 24 && init_len != 52) return fail(ctx, SYMRELAY_EINVAL, "init_len must be 24 or 52");
+    if ((tx_keys && !tx_inits) || (rx_keys && !rx_inits)) return fail(ctx, SYMRELAY_EINVAL, "key without init");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    // allocate slots round-robin over the GPUs
+    uint32_t avail = 0;
+    for (int g = 0; g < ctx->n_gpus; g++) avail += (uint32_t)ctx->free_slots[g].size();
+    if (avail < n) return fail(ctx, SYMRELAY_ENOMEM, "slot table full (%u free, %u wanted)", avail, n);
+    int g = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        while (ctx->free_slots[g].empty()) g = (g + 1) % ctx->n_gpus;
+        slots_out[i] = ctx->free_slots[g].back();
+        ctx->free_slots[g].pop_back();
+        ctx->slot_state[slots_out[i]] = 1;
+        g = (g + 1) % ctx->n_gpus;
+    }
+    for (int gi = 0; gi < ctx->n_gpus; gi++) {
+        Shard &sh = ctx->shard[gi];
+        uint32_t fill = 0;
+        for (uint32_t i = 0; i < n; i++) {
+            if ((int)(slots_out[i] % (uint32_t)ctx->n_gpus) != gi) continue;
+            fill_rec(&sh.h_init[fill++], slots_out[i], 0, tx_keys ? tx_keys + 32ull * i : nullptr,
+                     tx_inits ? tx_inits + (size_t)init_len * i : nullptr, init_len, (uint32_t)provider_kind);
+            fill_rec(&sh.h_init[fill++], slots_out[i], 1, rx_keys ? rx_keys + 32ull * i : nullptr,
+                     rx_inits ? rx_inits + (size_t)init_len * i : nullptr, init_len, (uint32_t)provider_kind);
+            if (fill + 2 > sh.init_cap) {
+                int rc = push_init_recs(ctx, sh, fill);
+                if (rc) return rc;
+                fill = 0;
+            }
+        }
+        if (fill) {
+            int rc = push_init_recs(ctx, sh, fill);
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
+int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, const uint8_t *tx_init, int tx_init_len,
+                         const uint8_t *rx_key, const uint8_t *rx_init, int rx_init_len, int provider_kind,
+                         uint32_t *slot_out) {
+    if (!ctx || !slot_out) return SYMRELAY_EINVAL;
+    if (tx_key && tx_init_len != 24 && tx_init_len != 52) return fail(ctx, SYMRELAY_EINVAL, "tx_init_len must be 24 or 52");
+    if (rx_key && rx_init_len != 24 && rx_init_len != 52) return fail(ctx, SYMRELAY_EINVAL, "rx_init_len must be 24 or 52");
+    if ((tx_key && !tx_init) || (rx_key && !rx_init)) return fail(ctx, SYMRELAY_EINVAL, "key without init");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int g = -1;
+    size_t best = 0;
+    for (int i = 0; i < ctx->n_gpus; i++)
+        if (ctx->free_slots[i].size() > best) { best = ctx->free_slots[i].size(); g = i; }
+    if (g < 0) return fail(ctx, SYMRELAY_ENOMEM, "slot table full");
+    const uint32_t slot = ctx->free_slots[g].back();
+    ctx->free_slots[g].pop_back();
+    ctx->slot_state[slot] = 1;
+    Shard &sh = ctx->shard[g];
+    fill_rec(&sh.h_init[0], slot, 0, tx_key, tx_init, tx_init_len, (uint32_t)provider_kind);
+    fill_rec(&sh.h_init[1], slot, 1, rx_key, rx_init, rx_init_len, (uint32_t)provider_kind);
+    int rc = push_init_recs(ctx, sh, 2);
+    if (rc) return rc;
+    *slot_out = slot;
+    return 0;
+}
+
+int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot) {
+    if (!ctx) return SYMRELAY_EINVAL;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (slot >= ctx->opts.max_streams || !ctx->slot_state[slot]) return fail(ctx, SYMRELAY_ENOENT, "slot %u not open", slot);
+    Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
+    fill_rec(&sh.h_init[0], slot, 0, nullptr, nullptr, 0, 0);
+    fill_rec(&sh.h_init[1], slot, 1, nullptr, nullptr, 0, 0);
+    int rc = push_init_recs(ctx, sh, 2);  // wipes the key material on the device
+    if (rc) return rc;
+    ctx->slot_state[slot] = 0;
+    ctx->free_slots[slot % (uint32_t)ctx->n_gpus].push_back(slot);
+    return 0;
+}
+
+int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_t tx_state[SYMRELAY_STATEBYTES],
+                           uint8_t rx_state[SYMRELAY_STATEBYTES]) {
+    if (!ctx) return SYMRELAY_EINVAL;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (slot >= ctx->opts.max_streams || !ctx->slot_state[slot]) return fail(ctx, SYMRELAY_ENOENT, "slot %u not open", slot);
+    Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
+    CU(ctx, cudaSetDevice(sh.dev));
+    uint8_t buf[96];
+    CU(ctx, cudaMemcpyAsync(buf, sh.d_states + (size_t)slot * 6u, 96, cudaMemcpyDeviceToHost, sh.s_k));
+    CU(ctx, cudaStreamSynchronize(sh.s_k));
+    if (tx_state) { memcpy(tx_state, buf, 44); memset(tx_state + 44, 0, 8); }
+    if (rx_state) { memcpy(rx_state, buf + 48, 44); memset(rx_state + 44, 0, 8); }
+    return 0;
+}
+
+// ---- planning -------------------------------------------------------------------
+int64_t symrelay_plan(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles, uint32_t max_tiles,
+                      uint32_t *n_bulk_out) {
+    if (!desc && n) return SYMRELAY_EINVAL;
+    return symrelay_plan_inline(desc, n, tiles, max_tiles, n_bulk_out);
+}
+
+int symrelay_desc_check(const symrelay_desc *d) { return d ? symrelay_desc_check_inline(d) : SYMRELAY_EINVAL; }
+
+// ---- batches --------------------------------------------------------------------
+int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
+                          const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
+                          const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, symrelay_delta *d_delta,
+                          uint8_t *d_delta_arena, void *cuda_stream) {
+    (void)d_delta; (void)d_delta_arena;
+    if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
+    if (n == 0 || n_tiles == 0) return 0;
+    if (!d_desc || !d_tiles || !d_in || !d_out || !d_status || n_bulk_tiles > n_tiles)
+        return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_device: null pointer or bad tile counts");
+    Shard &sh = ctx->shard[gpu_index];
+    CU(ctx, cudaSetDevice(sh.dev));
+    return launch_tiles(ctx, d_desc, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status,
+                        (cudaStream_t)cuda_stream);
+}
+
+static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st) {
+    if (!st.busy) return 0;
+    CU(ctx, cudaSetDevice(sh.dev));
+    CU(ctx, cudaEventSynchronize(st.ev_out));
+    if (st.user_status) memcpy(st.user_status, st.h_status, (size_t)st.n * 4u);
+    st.busy = false;
+    return 0;
+}
+
+static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *desc, uint32_t n,
+                             const uint8_t *in, uint64_t in_bytes, uint8_t *out, uint64_t out_bytes,
+                             uint32_t *status) {
+    Shard &sh = ctx->shard[gpu_index];
+    if (n > ctx->opts.max_batch_frames) return fail(ctx, SYMRELAY_EINVAL, "batch of %u frames exceeds max_batch_frames %u", n, ctx->opts.max_batch_frames);
+    if (in_bytes > ctx->opts.stage_bytes || out_bytes > ctx->opts.stage_bytes)
+        return fail(ctx, SYMRELAY_EINVAL, "arena (%llu in / %llu out bytes) exceeds stage_bytes %llu",
+                    (unsigned long long)in_bytes, (unsigned long long)out_bytes, (unsigned long long)ctx->opts.stage_bytes);
+    if ((in_bytes & 15u) || (out_bytes & 15u)) return fail(ctx, SYMRELAY_EINVAL, "arena sizes must be multiples of 16");
+    CU(ctx, cudaSetDevice(sh.dev));
+    const int64_t seq = sh.next_ticket_seq++;
+    Stage &st = sh.stages[(size_t)(seq % (int64_t)sh.stages.size())];
+    int rc = finish_stage(ctx, sh, st);  // recycle: the batch that used this stage P submissions ago
+    if (rc) return rc;
+
+    // control block: tiles ‖ descs, planned straight into pinned memory
+    symrelay_tile *h_tiles = reinterpret_cast<symrelay_tile *>(st.h_ctrl);
+    uint32_t n_bulk = 0;
+    const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk);
+    if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t mlen = desc[i].len_flags & SYMRELAY_LEN_MASK;
+        const bool op = desc[i].len_flags & SYMRELAY_F_OPEN;
+        const uint64_t in_end = (uint64_t)desc[i].in_off + mlen + (op ? 20u : 0u);
+        const uint64_t out_end = (uint64_t)desc[i].out_off + mlen + (op ? 0u : 20u);
+        if (in_end > in_bytes || out_end > out_bytes || desc[i].slot >= ctx->opts.max_streams ||
+            (int)(desc[i].slot % (uint32_t)ctx->n_gpus) != gpu_index)
+            return fail(ctx, SYMRELAY_EINVAL, "descriptor %u: frame outside its arena or slot not on gpu %d", i, gpu_index);
+    }
+    const size_t tiles_bytes = align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
+    memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
+    const size_t ctrl_bytes = tiles_bytes + (size_t)n * sizeof(symrelay_desc);
+
+    CU(ctx, cudaMemcpyAsync(st.d_ctrl, st.h_ctrl, ctrl_bytes, cudaMemcpyHostToDevice, sh.s_in));
+    if (in_bytes) CU(ctx, cudaMemcpyAsync(st.d_in, in, in_bytes, cudaMemcpyHostToDevice, sh.s_in));
+    CU(ctx, cudaEventRecord(st.ev_in, sh.s_in));
+    CU(ctx, cudaStreamWaitEvent(sh.s_k, st.ev_in, 0));
+    rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(st.d_ctrl + tiles_bytes),
+                      reinterpret_cast<const symrelay_tile *>(st.d_ctrl), (uint32_t)n_tiles, n_bulk, st.d_in, st.d_out,
+                      sh.d_states, st.d_status, sh.s_k);
+    if (rc) return rc;
+    CU(ctx, cudaEventRecord(st.ev_k, sh.s_k));
+    CU(ctx, cudaStreamWaitEvent(sh.s_out, st.ev_k, 0));
+    if (out_bytes) CU(ctx, cudaMemcpyAsync(out, st.d_out, out_bytes, cudaMemcpyDeviceToHost, sh.s_out));
+    CU(ctx, cudaMemcpyAsync(st.h_status, st.d_status, (size_t)n * 4u, cudaMemcpyDeviceToHost, sh.s_out));
+    CU(ctx, cudaEventRecord(st.ev_out, sh.s_out));
+    st.busy = true;
+    st.n = n;
+    st.user_status = status;
+    st.ticket = (seq << 3) | gpu_index;
+    return st.ticket;
+}
+
+int64_t symrelay_batch_submit(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, const uint8_t *in,
+                              uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
+                              symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes) {
+    (void)delta; (void)delta_arena; (void)delta_arena_bytes;
+    if (!ctx || !desc || n == 0 || !in || !out) return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_submit: null/empty argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    const int gpu_index = (int)(desc[0].slot % (uint32_t)ctx->n_gpus);
+    return submit_locked(ctx, gpu_index, desc, n, in, in_bytes, out, out_bytes, status);
+}
+
+int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket) {
+    if (!ctx || ticket < 0) return SYMRELAY_EINVAL;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    const int gpu_index = (int)(ticket & 7);
+    if (gpu_index >= ctx->n_gpus) return fail(ctx, SYMRELAY_ENOENT, "bad ticket");
+    Shard &sh = ctx->shard[gpu_index];
+    const int64_t seq = ticket >> 3;
+    if (seq >= sh.next_ticket_seq) return fail(ctx, SYMRELAY_ENOENT, "ticket not issued");
+    Stage &st = sh.stages[(size_t)(seq % (int64_t)sh.stages.size())];
+    if (st.busy && st.ticket == ticket) return finish_stage(ctx, sh, st);
+    return 0;  // already recycled => already finished
+}
+
+int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, const uint8_t *in,
+                        uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
+                        symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes) {
+    if (n == 0) return 0;
+    const int64_t t = symrelay_batch_submit(ctx, desc, n, in, in_bytes, out, out_bytes, status, delta, delta_arena,
+                                            delta_arena_bytes);
+    if (t < 0) return (int)t;
+    return symrelay_batch_wait(ctx, t);
+}
+
+void *symrelay_alloc_pinned(symrelay_ctx *ctx, uint64_t bytes) {
+    void *p = nullptr;
+    if (!ctx || bytes == 0) return nullptr;
+    cudaSetDevice(ctx->shard[0].dev);
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        fail(ctx, SYMRELAY_ENOMEM, "cudaHostAlloc(%llu) failed", (unsigned long long)bytes);
+        return nullptr;
+    }
+    return p;
+}
+
+void symrelay_free_pinned(symrelay_ctx *ctx, void *p) {
+    (void)ctx;
+    if (p) cudaFreeHost(p);
+}
+
+}  // extern "C"

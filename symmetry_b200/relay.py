@@ -1,0 +1,172 @@
+"""Host-side front end of the C ABI (ctypes), in the reference's vocabulary.
+
+The reference's seal/open path is `peer.write(chunk)` / `peer.on('data')`
+(/root/reference/src/provider.ts:248, :174) on a hyperswarm secret-stream whose
+crypto state is typed at /root/reference/src/types.ts:168-177.  `SymRelay` owns
+the device-resident table of those states (one slot per connection) and runs
+batches of frames from many connections through the CUDA kernels.  No Node.js
+exists in this image, so this module is also the only runnable caller of the
+library; the N-API shim a maintainer would add is in INTEGRATION.md.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+DESC_DTYPE = np.dtype([("slot", "<u4"), ("in_off", "<u4"), ("out_off", "<u4"), ("len_flags", "<u4")])
+TILE_DTYPE = np.dtype([("first", "<u4"), ("n_kind", "<u4")])
+DELTA_DTYPE = np.dtype([("off", "<u4"), ("len", "<u4")])
+
+F_OPEN = 0x04000000
+F_EXTRACT = 0x08000000
+LEN_MASK = 0x00FFFFFF
+ST_OK, ST_BAD_MAC, ST_TOO_SHORT, ST_EXTRACT_THROW, ST_EXTRACT_UNSUPPORTED = 0, 1, 2, 3, 4
+PROVIDER_DEFAULT, PROVIDER_OLLAMA, PROVIDER_LLAMACPP = 0, 1, 2
+STATEBYTES, HEADERBYTES, KEYBYTES, WIRE_OVERHEAD = 52, 24, 32, 20
+
+# src/constants.ts:22-29 -> extractor branch (utils.ts:36-50)
+PROVIDER_KIND = {"ollama": PROVIDER_OLLAMA, "openwebui": PROVIDER_OLLAMA, "llamacpp": PROVIDER_LLAMACPP,
+                 "litellm": PROVIDER_DEFAULT, "lmstudio": PROVIDER_DEFAULT, "oobabooga": PROVIDER_DEFAULT}
+
+
+def provider_kind(api_provider: str) -> int:
+    return PROVIDER_KIND.get(api_provider, PROVIDER_DEFAULT)
+
+
+class RelayError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"symrelay error {code}: {msg}")
+        self.code = code
+
+
+def _ptr(a) -> int:
+    if a is None:
+        return 0
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return int(a)
+
+
+def _bytes_ptr(b):
+    return None if b is None else bytes(b)  # ctypes passes bytes to a void* parameter as-is
+
+
+class SymRelay:
+    """One context = one state table per GPU + the batch pipeline."""
+
+    def __init__(self, gpu_ids=(0,), max_streams: int = 65536, pipeline_depth: int = 4,
+                 stage_bytes: int = 64 << 20, max_batch_frames: int = 131072):
+        self.lib = _lib.load()
+        ids = (C.c_int * len(gpu_ids))(*gpu_ids)
+        opts = _lib.SymrelayOpts(max_streams, pipeline_depth, stage_bytes, max_batch_frames, 0)
+        self.n_gpus = len(gpu_ids)
+        self.ctx = self.lib.symrelay_create(ids, len(gpu_ids), C.byref(opts))
+        if not self.ctx:
+            raise RelayError(-1000, self.lib.symrelay_last_error(None).decode())
+        self._pinned = []
+
+    # -- lifetime ----------------------------------------------------------------
+    def close(self):
+        if getattr(self, "ctx", None):
+            for p in self._pinned:
+                self.lib.symrelay_free_pinned(self.ctx, p)
+            self._pinned = []
+            self.lib.symrelay_destroy(self.ctx)
+            self.ctx = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int) -> int:
+        if rc < 0:
+            raise RelayError(rc, self.lib.symrelay_last_error(self.ctx).decode())
+        return rc
+
+    @property
+    def launches(self) -> int:
+        return int(self.lib.symrelay_launch_count(self.ctx))
+
+    # -- streams -----------------------------------------------------------------
+    def open_stream(self, tx_key=None, tx_init=None, rx_key=None, rx_init=None, provider: int = 0) -> int:
+        """`new Push(tx)` + `Pull.init(header)` for one connection; init is a 24-byte header or a
+        52-byte libsodium state.  Returns the slot."""
+        slot = C.c_uint32(0)
+        self._check(self.lib.symrelay_stream_open(
+            self.ctx, _bytes_ptr(tx_key), _bytes_ptr(tx_init), len(tx_init) if tx_init else 0,
+            _bytes_ptr(rx_key), _bytes_ptr(rx_init), len(rx_init) if rx_init else 0, provider, C.byref(slot)))
+        return slot.value
+
+    def open_streams(self, tx_keys, tx_inits, rx_keys, rx_inits, provider: int = 0) -> np.ndarray:
+        """Batched open: arrays [n,32] and [n,24|52] (uint8); either direction may be None."""
+        ref = tx_keys if tx_keys is not None else rx_keys
+        n = len(ref)
+        inits = tx_inits if tx_inits is not None else rx_inits
+        init_len = inits.shape[1]
+        arrs = [None if a is None else np.ascontiguousarray(a, dtype=np.uint8)
+                for a in (tx_keys, tx_inits, rx_keys, rx_inits)]
+        slots = np.zeros(n, dtype=np.uint32)
+        self._check(self.lib.symrelay_stream_open_batch(self.ctx, n, _ptr(arrs[0]), _ptr(arrs[1]), _ptr(arrs[2]),
+                                                        _ptr(arrs[3]), init_len, provider, _ptr(slots)))
+        return slots
+
+    def close_stream(self, slot: int) -> None:
+        self._check(self.lib.symrelay_stream_close(self.ctx, int(slot)))
+
+    def export(self, slot: int):
+        """(tx_state, rx_state): the live 52-byte libsodium states of a slot."""
+        tx = C.create_string_buffer(STATEBYTES)
+        rx = C.create_string_buffer(STATEBYTES)
+        self._check(self.lib.symrelay_stream_export(self.ctx, int(slot), tx, rx))
+        return tx.raw, rx.raw
+
+    # -- batches -----------------------------------------------------------------
+    def plan(self, descs: np.ndarray):
+        nb = C.c_uint32(0)
+        need = self._check(self.lib.symrelay_plan(_ptr(descs), len(descs), None, 0, C.byref(nb)))
+        tiles = np.zeros(max(1, need), dtype=TILE_DTYPE)
+        self._check(self.lib.symrelay_plan(_ptr(descs), len(descs), _ptr(tiles), need, C.byref(nb)))
+        return tiles[:need], nb.value
+
+    def batch_host(self, descs: np.ndarray, arena_in: np.ndarray, arena_out: np.ndarray,
+                   status: np.ndarray | None = None) -> np.ndarray:
+        """Synchronous mixed seal/open batch on HOST arenas (N x push/pull in one call)."""
+        if status is None:
+            status = np.full(len(descs), 0xFF, dtype=np.uint32)
+        self._check(self.lib.symrelay_batch_host(self.ctx, _ptr(descs), len(descs), _ptr(arena_in), arena_in.nbytes,
+                                                 _ptr(arena_out), arena_out.nbytes, _ptr(status), None, None, 0))
+        return status
+
+    def submit(self, descs: np.ndarray, arena_in, in_bytes: int, arena_out, out_bytes: int, status) -> int:
+        """Pipelined batch; buffers must stay alive until wait(ticket)."""
+        return self._check(self.lib.symrelay_batch_submit(self.ctx, _ptr(descs), len(descs), _ptr(arena_in), in_bytes,
+                                                          _ptr(arena_out), out_bytes, _ptr(status), None, None, 0))
+
+    def wait(self, ticket: int) -> None:
+        self._check(self.lib.symrelay_batch_wait(self.ctx, ticket))
+
+    def batch_device(self, d_desc: int, n: int, d_tiles: int, n_tiles: int, n_bulk: int, d_in: int, d_out: int,
+                     d_status: int, stream: int = 0, gpu_index: int = 0) -> None:
+        """One launch on device-resident buffers (raw device pointers), asynchronous on `stream`."""
+        self._check(self.lib.symrelay_batch_device(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk, d_in,
+                                                   d_out, d_status, None, None, stream))
+
+    def alloc_pinned(self, nbytes: int) -> np.ndarray:
+        """Pinned host arena as a uint8 numpy view (freed with the context)."""
+        p = self.lib.symrelay_alloc_pinned(self.ctx, nbytes)
+        if not p:
+            raise RelayError(-12, self.lib.symrelay_last_error(self.ctx).decode())
+        self._pinned.append(p)
+        buf = (C.c_uint8 * nbytes).from_address(p)
+        return np.frombuffer(buf, dtype=np.uint8)

@@ -1,0 +1,52 @@
+// emu_main.cpp -- TEST INFRASTRUCTURE ONLY (see emu_warp.h).
+// Runs the product's tile code (ss_core.cuh) and host planner (plan.h) on CPU
+// threads so tests/test_emu_kernel_logic.py can compare them with the oracle
+// without a GPU.
+#define SS_HOST_EMU 1
+#include "emu_warp.h"
+
+#include "../../symmetry_b200/csrc/plan.h"
+#include "../../symmetry_b200/csrc/ss_core.cuh"
+
+thread_local uint32_t emu_lane_id;
+thread_local EmuWarp *emu_warp;
+
+struct Job {
+    EmuWarp *warp;
+    SsArgs args;
+    uint32_t n_packed, n_bulk;
+    uint32_t lane;
+};
+
+static void *lane_main(void *p) {
+    Job *j = (Job *)p;
+    emu_lane_id = j->lane;
+    emu_warp = j->warp;
+    for (uint32_t t = 0; t < j->n_packed; t++) ss_process_tile<false>(j->args, t);
+    for (uint32_t t = 0; t < j->n_bulk; t++) ss_process_tile<true>(j->args, j->n_packed + t);
+    return nullptr;
+}
+
+extern "C" int64_t emu_plan(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles, uint32_t max_tiles,
+                            uint32_t *n_bulk) {
+    return symrelay_plan_inline(desc, n, tiles, max_tiles, n_bulk);
+}
+
+extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *tiles, uint32_t n_tiles, uint32_t n_bulk,
+                             const uint8_t *in, uint8_t *out, void *states, uint32_t *status) {
+    EmuWarp warp;
+    pthread_barrier_init(&warp.bar, nullptr, 32);
+    Job jobs[32];
+    pthread_t th[32];
+    for (uint32_t l = 0; l < 32; l++) {
+        jobs[l].warp = &warp;
+        jobs[l].args = SsArgs{(const SsDesc *)desc, (const SsTile *)tiles, n_tiles, in, out, (uint4 *)states, status};
+        jobs[l].n_packed = n_tiles - n_bulk;
+        jobs[l].n_bulk = n_bulk;
+        jobs[l].lane = l;
+        pthread_create(&th[l], nullptr, lane_main, &jobs[l]);
+    }
+    for (uint32_t l = 0; l < 32; l++) pthread_join(th[l], nullptr);
+    pthread_barrier_destroy(&warp.bar);
+    return 0;
+}

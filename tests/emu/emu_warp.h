@@ -1,0 +1,71 @@
+// emu_warp.h -- TEST INFRASTRUCTURE ONLY.
+// A 32-thread, barrier-synchronised stand-in for a CUDA warp so that
+// symmetry_b200/csrc/ss_core.cuh (the product's device code) can be compiled with
+// g++ and its lane logic unit-tested on a machine without a GPU.  Slow by design;
+// never linked into, loaded by, or used as a fallback for the product library.
+#pragma once
+#include <pthread.h>
+#include <stdint.h>
+
+#define SS_DEV static inline
+
+struct alignas(16) uint4 {
+    uint32_t x, y, z, w;
+};
+
+struct EmuWarp {
+    pthread_barrier_t bar;
+    volatile uint32_t slot[32];
+};
+extern thread_local uint32_t emu_lane_id;
+extern thread_local EmuWarp *emu_warp;
+
+static inline uint32_t ss_lane() { return emu_lane_id; }
+static inline void emu_sync() { pthread_barrier_wait(&emu_warp->bar); }
+static inline uint32_t ss_shfl(uint32_t v, uint32_t src) {
+    emu_warp->slot[emu_lane_id] = v;
+    emu_sync();
+    const uint32_t r = emu_warp->slot[src & 31u];
+    emu_sync();
+    return r;
+}
+static inline uint32_t ss_shfl_up(uint32_t v, uint32_t d) {
+    emu_warp->slot[emu_lane_id] = v;
+    emu_sync();
+    const uint32_t r = emu_lane_id >= d ? emu_warp->slot[emu_lane_id - d] : v;
+    emu_sync();
+    return r;
+}
+static inline uint32_t ss_shfl_down(uint32_t v, uint32_t d) {
+    emu_warp->slot[emu_lane_id] = v;
+    emu_sync();
+    const uint32_t r = emu_lane_id + d < 32u ? emu_warp->slot[emu_lane_id + d] : v;
+    emu_sync();
+    return r;
+}
+static inline uint32_t ss_reduce_or(uint32_t v) {
+    emu_warp->slot[emu_lane_id] = v;
+    emu_sync();
+    uint32_t r = 0;
+    for (int i = 0; i < 32; i++) r |= emu_warp->slot[i];
+    emu_sync();
+    return r;
+}
+static inline uint32_t ss_reduce_max(uint32_t v) {
+    emu_warp->slot[emu_lane_id] = v;
+    emu_sync();
+    uint32_t r = 0;
+    for (int i = 0; i < 32; i++) r = emu_warp->slot[i] > r ? emu_warp->slot[i] : r;
+    emu_sync();
+    return r;
+}
+static inline uint32_t ss_popc(uint32_t v) { return (uint32_t)__builtin_popcount(v); }
+static inline uint32_t ss_clz(uint32_t v) { return v ? (uint32_t)__builtin_clz(v) : 32u; }
+static inline uint32_t emu_rotl(uint32_t x, int n) { return (x << n) | (x >> (32 - n)); }
+static inline uint32_t ss_rotl16(uint32_t x) { return emu_rotl(x, 16); }
+static inline uint32_t ss_rotl8(uint32_t x) { return emu_rotl(x, 8); }
+static inline uint32_t ss_rotl12(uint32_t x) { return emu_rotl(x, 12); }
+static inline uint32_t ss_rotl7(uint32_t x) { return emu_rotl(x, 7); }
+static inline uint32_t ss_fsr(uint32_t lo, uint32_t hi, uint32_t s) {
+    return (uint32_t)((((uint64_t)hi << 32) | lo) >> (s & 31u));
+}

@@ -1,0 +1,70 @@
+"""The C-ABI library loads on a machine without a GPU and exports every symbol
+include/symrelay.h declares; computing entry points refuse to run without a device."""
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    with open(os.path.join(ROOT, "include", "symrelay.h")) as f:
+        text = f.read()
+    return sorted(set(re.findall(r"SYMRELAY_API[^;(]*?\b(symrelay_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from symmetry_b200 import _lib, build
+
+    build.build()
+    L = _lib.load()
+    decl = declared_symbols()
+    assert len(decl) >= 18
+    for name in decl:
+        assert hasattr(L, name), f"{name} declared in include/symrelay.h but not exported"
+    assert sorted(_lib.EXPORTS) == decl, "symmetry_b200/_lib.py EXPORTS out of sync with the header"
+    assert L.symrelay_abi_version() == 1
+    assert L.symrelay_strerror(-22) == b"invalid argument"
+
+
+def test_planner_and_desc_check_are_host_only():
+    import numpy as np
+
+    import batch_util as bu
+    from symmetry_b200 import _lib
+
+    L = _lib.load()
+    lens = [64] * 20 + [5000]
+    p, _ = bu.plain_layout(lens)
+    w, _ = bu.wire_layout(lens)
+    d = bu.make_descs(np.arange(len(lens)), lens, p, w)
+    import ctypes as C
+
+    nb = C.c_uint32(0)
+    assert L.symrelay_plan(d.ctypes.data, len(d), None, 0, C.byref(nb)) == 3 and nb.value == 1
+    assert L.symrelay_desc_check(d[:1].ctypes.data) == 0
+    d["out_off"][0] = 16
+    assert L.symrelay_desc_check(d[:1].ctypes.data) == -22
+
+
+def test_no_cpu_fallback_without_a_device():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    import symmetry_b200 as sb
+
+    with pytest.raises(sb.RelayError, match="no CPU path"):
+        sb.SymRelay()
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "symmetry_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                with open(os.path.join(dirpath, fn)) as f:
+                    src = f.read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), fn
+                assert "ssref_" not in src and "libss_emu" not in src and "nacl" not in src, fn

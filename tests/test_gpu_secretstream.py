@@ -1,0 +1,243 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against
+the real libsodium on the same seeded inputs, the libsodium-generated golden
+chains, and -- at BASELINE.json's full sizes -- size-independent properties
+(seal -> open round trip, state chain equality on a sample, forged frames
+rejected).  Bit-exact: bytes, tags, statuses and 52-byte states."""
+import random
+
+import numpy as np
+import pytest
+
+import batch_util as bu
+import parity_cases as pc
+from oracle import libsodium as ls
+
+pytestmark = pytest.mark.gpu
+
+
+class GpuBackend:
+    def __init__(self, relay):
+        self.relay = relay
+
+    def open_streams(self, tx_states, rx_states):
+        n = len(tx_states)
+        keys = np.zeros((n, 32), dtype=np.uint8)
+        tx = np.frombuffer(b"".join(tx_states), dtype=np.uint8).reshape(n, 52)
+        rx = np.frombuffer(b"".join(rx_states), dtype=np.uint8).reshape(n, 52)
+        return [int(s) for s in self.relay.open_streams(keys, tx, keys, rx)]
+
+    def run(self, descs, arena_in, arena_out):
+        return self.relay.batch_host(descs, arena_in, arena_out)
+
+    def export(self, slot):
+        return self.relay.export(slot)
+
+
+@pytest.fixture(scope="module")
+def relay():
+    import symmetry_b200 as sb
+
+    r = sb.SymRelay(gpu_ids=(0,), max_streams=1 << 17, stage_bytes=96 << 20)
+    yield r
+    r.close()
+
+
+@pytest.fixture()
+def be(relay):
+    return GpuBackend(relay)
+
+
+def test_header_init_matches_libsodium(relay):
+    rng = random.Random(3)
+    for _ in range(8):
+        tk, th, rk, rh = rng.randbytes(32), rng.randbytes(24), rng.randbytes(32), rng.randbytes(24)
+        slot = relay.open_stream(tk, th, rk, rh)
+        tx, rx = relay.export(slot)
+        assert tx == ls.State(tk, th).raw and rx == ls.State(rk, rh).raw
+        relay.close_stream(slot)
+    n = 300
+    tks = np.frombuffer(rng.randbytes(32 * n), dtype=np.uint8).reshape(n, 32)
+    ths = np.frombuffer(rng.randbytes(24 * n), dtype=np.uint8).reshape(n, 24)
+    slots = relay.open_streams(tks, ths, tks, ths)
+    assert len(set(int(s) for s in slots)) == n
+    for i in (0, 1, 150, 299):
+        want = ls.State(bytes(tks[i]), bytes(ths[i])).raw
+        assert relay.export(int(slots[i])) == (want, want)
+
+
+def test_golden_chains(be, ss_vectors):
+    assert pc.golden_chains(be, ss_vectors) >= 200
+
+
+def test_packed_every_small_length(be):
+    lens = list(range(0, 260))
+    pc.seal_open_roundtrip(be, lens, [0] * len(lens), seed=1, chain=3)
+
+
+def test_packed_tags_and_rekey(be):
+    rng = random.Random(5)
+    lens = [rng.choice([0, 1, 15, 16, 17, 63, 64, 65, 100, 200, 500, 1000, 1919, 1920]) for _ in range(400)]
+    pc.seal_open_roundtrip(be, lens, [i % 4 for i in range(400)], seed=2, chain=4)
+
+
+def test_bulk_lengths(be):
+    lens = [1921, 1984, 2048, 4095, 4096, 4097, 16383, 16384, 65535, 65536, 65537, 64 * 1022, 64 * 1023 + 1,
+            1 << 20, (1 << 20) + 3]
+    pc.seal_open_roundtrip(be, lens, [0, 1, 2, 3, 0, 0, 0, 0, 2, 0, 0, 1, 0, 0, 3], seed=3, chain=2)
+
+
+def test_config3_ragged_power_law_with_forgeries(be):
+    lens = pc.power_law_lens(random.Random(11), 3000) + [3000, 0, 0, 64]
+    pc.seal_open_roundtrip(be, lens, [0] * len(lens), seed=4, chain=2, corrupt=(0, 5, 17, 1000, 2999, 3000, 3001, 3003))
+
+
+def test_config2_1024_streams_x64B_chain(be):
+    pc.seal_open_roundtrip(be, [64] * 1024, [0] * 1024, seed=6, chain=8)
+
+
+def test_counter_wrap_rekeys(be):
+    key, hdr = bytes(range(32)), bytes(24)
+    raw = bytearray(ls.State(key, hdr).raw)
+    raw[32:36] = (0xFFFFFFFF).to_bytes(4, "little")
+    ref = ls.State(key, hdr)
+    ref.st.statebuf[0:52] = bytes(raw)
+    (slot,) = be.open_streams([bytes(raw)], [bytes(raw)])
+    plain = bu.aligned_zeros(16)
+    plain[:4] = np.frombuffer(b"wrap", dtype=np.uint8)
+    wire = bu.aligned_zeros(48)
+    be.run(bu.make_descs([slot], [4], [0], [12]), plain, wire)
+    assert bytes(wire[12:36]) == ref.seal_frame(b"wrap")
+    assert be.export(slot)[0] == ref.raw and ref.raw[32:36] == (1).to_bytes(4, "little")
+
+
+def _full_size_roundtrip(relay, lens, seed, sample):
+    """Seal then open n frames through host arenas; check every plaintext comes back, and a
+    sample of frames/states against libsodium."""
+    rng = np.random.default_rng(seed)
+    n = len(lens)
+    keys = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    hdrs = rng.integers(0, 256, (n, 24), dtype=np.uint8)
+    slots = relay.open_streams(keys, hdrs, keys, hdrs)
+    p_offs, p_bytes = bu.plain_layout(lens)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    plain = relay.alloc_pinned(p_bytes)
+    plain[:] = rng.integers(0, 256, p_bytes, dtype=np.uint8)
+    wire = relay.alloc_pinned(w_bytes)
+    back = relay.alloc_pinned(p_bytes)
+    st = relay.batch_host(bu.make_descs(slots, lens, p_offs, w_offs), plain, wire)
+    assert (st == 0).all()
+    for i in sample:
+        ref = ls.State(bytes(keys[i]), bytes(hdrs[i]))
+        want = ref.seal_frame(bytes(plain[p_offs[i] : p_offs[i] + lens[i]]))
+        assert bytes(wire[w_offs[i] : w_offs[i] + lens[i] + 20]) == want, (i, lens[i])
+        assert relay.export(int(slots[i]))[0] == ref.raw
+    st = relay.batch_host(bu.make_descs(slots, lens, w_offs, p_offs, open_=True), wire, back)
+    assert (st == 0).all()
+    ok = True
+    for o, L in zip(p_offs, lens):
+        ok &= bool((back[o : o + L] == plain[o : o + L]).all())
+    assert ok
+    for i in sample:
+        assert relay.export(int(slots[i]))[0] == relay.export(int(slots[i]))[1]
+    return slots
+
+
+def test_config3_full_size_65536_streams(relay):
+    lens = pc.power_law_lens(random.Random(0x5EED0001), 65536)
+    _full_size_roundtrip(relay, lens, seed=7, sample=[0, 1, 2, 100, 4097, 30000, 65535] +
+                         [int(i) for i in np.argsort(lens)[-4:]])
+
+
+def test_config4_bulk_64KiB_frames(relay):
+    _full_size_roundtrip(relay, [65536] * 512, seed=8, sample=[0, 255, 511])
+
+
+def test_device_resident_batch_on_torch_stream(relay):
+    """symrelay_batch_device: buffers in HBM (torch tensors), launch on torch's current stream."""
+    import torch
+
+    rng = random.Random(9)
+    lens = [64] * 1024 + pc.power_law_lens(rng, 500) + [65536, 5000]
+    n = len(lens)
+    keys = [rng.randbytes(32) for _ in range(n)]
+    hdrs = [rng.randbytes(24) for _ in range(n)]
+    karr = np.frombuffer(b"".join(keys), dtype=np.uint8).reshape(n, 32)
+    harr = np.frombuffer(b"".join(hdrs), dtype=np.uint8).reshape(n, 24)
+    slots = relay.open_streams(karr, harr, karr, harr)
+    p_offs, p_bytes = bu.plain_layout(lens)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    plain = np.frombuffer(rng.randbytes(p_bytes), dtype=np.uint8).copy()
+    descs = bu.make_descs(slots, lens, p_offs, w_offs)
+    tiles, n_bulk = relay.plan(descs)
+    dev = torch.device("cuda:0")
+    t_desc = torch.from_numpy(descs.view(np.uint8).copy()).to(dev)
+    t_tiles = torch.from_numpy(tiles.view(np.uint8).copy()).to(dev)
+    t_in = torch.from_numpy(plain).to(dev)
+    t_out = torch.zeros(w_bytes, dtype=torch.uint8, device=dev)
+    t_status = torch.full((n,), 0xFF, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    relay.batch_device(t_desc.data_ptr(), n, t_tiles.data_ptr(), len(tiles), n_bulk, t_in.data_ptr(),
+                       t_out.data_ptr(), t_status.data_ptr(), stream=stream)
+    torch.cuda.synchronize()
+    wire = t_out.cpu().numpy()
+    assert (t_status.cpu().numpy() == 0).all()
+    for i in list(range(0, n, 97)) + [n - 2, n - 1]:
+        want = ls.State(keys[i], hdrs[i]).seal_frame(bytes(plain[p_offs[i] : p_offs[i] + lens[i]]))
+        assert bytes(wire[w_offs[i] : w_offs[i] + lens[i] + 20]) == want
+    # open in place on the device: wire arena -> plaintext written into a second arena
+    d2 = bu.make_descs(slots, lens, w_offs, p_offs, open_=True)
+    tiles2, n_bulk2 = relay.plan(d2)
+    t_desc2 = torch.from_numpy(d2.view(np.uint8).copy()).to(dev)
+    t_tiles2 = torch.from_numpy(tiles2.view(np.uint8).copy()).to(dev)
+    t_back = torch.zeros(p_bytes, dtype=torch.uint8, device=dev)
+    relay.batch_device(t_desc2.data_ptr(), n, t_tiles2.data_ptr(), len(tiles2), n_bulk2, t_out.data_ptr(),
+                       t_back.data_ptr(), t_status.data_ptr(), stream=stream)
+    torch.cuda.synchronize()
+    back = t_back.cpu().numpy()
+    assert (t_status.cpu().numpy() == 0).all()
+    for o, L in zip(p_offs, lens):
+        assert (back[o : o + L] == plain[o : o + L]).all()
+
+
+def test_pipelined_submit_keeps_chain_order(relay):
+    """Consecutive batches carry consecutive frames of the same streams (MAC chain)."""
+    rng = random.Random(10)
+    n, depth = 256, 12
+    keys = [rng.randbytes(32) for _ in range(n)]
+    hdrs = [rng.randbytes(24) for _ in range(n)]
+    karr = np.frombuffer(b"".join(keys), dtype=np.uint8).reshape(n, 32)
+    harr = np.frombuffer(b"".join(hdrs), dtype=np.uint8).reshape(n, 24)
+    slots = relay.open_streams(karr, harr, None, None)
+    lens = [rng.choice([0, 17, 64, 200, 3000]) for _ in range(n)]
+    p_offs, p_bytes = bu.plain_layout(lens)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    descs = bu.make_descs(slots, lens, p_offs, w_offs)
+    plains = [relay.alloc_pinned(p_bytes) for _ in range(depth)]
+    wires = [relay.alloc_pinned(w_bytes) for _ in range(depth)]
+    stats = [np.full(n, 0xFF, dtype=np.uint32) for _ in range(depth)]
+    tickets = []
+    for k in range(depth):
+        plains[k][:] = np.frombuffer(rng.randbytes(p_bytes), dtype=np.uint8)
+        tickets.append(relay.submit(descs, plains[k], p_bytes, wires[k], w_bytes, stats[k]))
+    for t in tickets:
+        relay.wait(t)
+    refs = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+    for k in range(depth):
+        assert (stats[k] == 0).all()
+        for i in range(0, n, 5):
+            want = refs[i].seal_frame(bytes(plains[k][p_offs[i] : p_offs[i] + lens[i]]))
+            assert bytes(wires[k][w_offs[i] : w_offs[i] + lens[i] + 20]) == want, (k, i)
+
+
+def test_bad_arguments_are_rejected(relay):
+    import symmetry_b200 as sb
+
+    d = bu.make_descs([0], [64], [0], [12])
+    small = bu.aligned_zeros(64)
+    with pytest.raises(sb.RelayError):
+        relay.batch_host(d, small, small)  # wire frame does not fit the out arena
+    d = bu.make_descs([0], [64], [4], [12])
+    with pytest.raises(sb.RelayError):
+        relay.batch_host(d, bu.aligned_zeros(128), bu.aligned_zeros(128))  # misaligned plaintext
+    with pytest.raises(sb.RelayError):
+        relay.export(99999)  # not open
