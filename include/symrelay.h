@@ -184,6 +184,12 @@ SYMRELAY_API int64_t symrelay_batch_submit(symrelay_ctx *ctx, const symrelay_des
                               symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes);
 SYMRELAY_API int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket);
 
+/* Measurement aid (bench.py): sustained integer throughput of this GPU in
+ * Tera-ops/s for ChaCha20's ADD:XOR:ROTATE 1:1:1 mix and for 32x32->64
+ * multiply-adds -- the integer roofline denominators.
+ * No counterpart in the reference. */
+SYMRELAY_API int symrelay_probe_int_peak(symrelay_ctx *ctx, int gpu_index, double *arx_tops, double *imad_tops);
+
 /* pinned host memory for arenas (the N-API shim exposes it as an external ArrayBuffer) */
 SYMRELAY_API void *symrelay_alloc_pinned(symrelay_ctx *ctx, uint64_t bytes);
 SYMRELAY_API void symrelay_free_pinned(symrelay_ctx *ctx, void *p);

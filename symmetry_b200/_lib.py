@@ -17,7 +17,7 @@ EXPORTS = (
     "symrelay_launch_count", "symrelay_stream_open", "symrelay_stream_open_batch", "symrelay_stream_close",
     "symrelay_stream_export", "symrelay_plan", "symrelay_desc_check", "symrelay_batch_device",
     "symrelay_batch_host", "symrelay_batch_submit", "symrelay_batch_wait", "symrelay_alloc_pinned",
-    "symrelay_free_pinned",
+    "symrelay_free_pinned", "symrelay_probe_int_peak",
 )
 
 
@@ -74,6 +74,8 @@ def load() -> C.CDLL:
     L.symrelay_alloc_pinned.argtypes = [vp, u64]
     L.symrelay_free_pinned.restype = None
     L.symrelay_free_pinned.argtypes = [vp, vp]
+    L.symrelay_probe_int_peak.restype = ci
+    L.symrelay_probe_int_peak.argtypes = [vp, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     if L.symrelay_abi_version() != 1:
         raise ImportError("libsymrelay.so ABI version mismatch")
     _lib = L

@@ -98,6 +98,48 @@ __global__ void ss_init_kernel(const SsInitRec *recs, uint32_t n, uint4 *states)
     sp[2] = make_uint4(nn[0], nn[1], nn[2], r->meta);
 }
 
+// Integer-throughput probes: the roofline denominator MEASURED_PEAKS.json lacks
+// (SURVEY.md section 8(d)).  ARX: ChaCha20's own ADD : XOR : ROTATE = 1:1:1 mix
+// on 16 register words with no memory traffic (4 independent quarter-rounds
+// in flight per thread); IMAD: independent 32x32->64 multiply-add chains as in
+// the Poly1305 limb products.
+__global__ void __launch_bounds__(256) ss_probe_arx_kernel(uint32_t *out, int double_rounds) {
+    uint32_t x[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) x[i] = threadIdx.x * 0x9e3779b9u + blockIdx.x + i;
+#pragma unroll 1
+    for (int r = 0; r < double_rounds; r++) {
+        SS_QR(x[0], x[4], x[8], x[12])
+        SS_QR(x[1], x[5], x[9], x[13])
+        SS_QR(x[2], x[6], x[10], x[14])
+        SS_QR(x[3], x[7], x[11], x[15])
+        SS_QR(x[0], x[5], x[10], x[15])
+        SS_QR(x[1], x[6], x[11], x[12])
+        SS_QR(x[2], x[7], x[8], x[13])
+        SS_QR(x[3], x[4], x[9], x[14])
+    }
+    uint32_t acc = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc ^= x[i];
+    if (acc == 0x12345u) out[0] = acc;  // keep the work alive
+}
+
+__global__ void __launch_bounds__(256) ss_probe_imad_kernel(uint32_t *out, int iters) {
+    uint64_t d[8];
+    uint32_t a = threadIdx.x * 2654435761u + 1u, b = blockIdx.x * 40503u + 7u;
+#pragma unroll
+    for (int i = 0; i < 8; i++) d[i] = i;
+#pragma unroll 1
+    for (int r = 0; r < iters; r++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) d[i] += (uint64_t)(a + i) * (uint32_t)(b ^ (uint32_t)d[(i + 1) & 7]);
+    }
+    uint64_t acc = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) acc ^= d[i];
+    if (acc == 0x12345ull) out[0] = (uint32_t)acc;
+}
+
 // --------------------------------------------------------------- host side --
 namespace {
 
@@ -538,6 +580,42 @@ int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n
                                             delta_arena_bytes);
     if (t < 0) return (int)t;
     return symrelay_batch_wait(ctx, t);
+}
+
+int symrelay_probe_int_peak(symrelay_ctx *ctx, int gpu_index, double *arx_tops, double *imad_tops) {
+    if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Shard &sh = ctx->shard[gpu_index];
+    CU(ctx, cudaSetDevice(sh.dev));
+    uint32_t *d_out = reinterpret_cast<uint32_t *>(sh.d_init);  // never written in practice
+    cudaEvent_t e0, e1;
+    CU(ctx, cudaEventCreate(&e0));
+    CU(ctx, cudaEventCreate(&e1));
+    const int blocks = 148 * 8, threads = 256;
+    float best_arx = 1e30f, best_imad = 1e30f;
+    const int dr = 4000, it = 8000;
+    for (int rep = 0; rep < 4; rep++) {
+        CU(ctx, cudaEventRecord(e0, sh.s_k));
+        ss_probe_arx_kernel<<<blocks, threads, 0, sh.s_k>>>(d_out, dr);
+        CU(ctx, cudaEventRecord(e1, sh.s_k));
+        CU(ctx, cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(ctx, cudaEventElapsedTime(&ms, e0, e1));
+        if (rep && ms < best_arx) best_arx = ms;
+        CU(ctx, cudaEventRecord(e0, sh.s_k));
+        ss_probe_imad_kernel<<<blocks, threads, 0, sh.s_k>>>(d_out, it);
+        CU(ctx, cudaEventRecord(e1, sh.s_k));
+        CU(ctx, cudaEventSynchronize(e1));
+        CU(ctx, cudaEventElapsedTime(&ms, e0, e1));
+        if (rep && ms < best_imad) best_imad = ms;
+        ctx->launches += 2;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    const double nthreads = (double)blocks * threads;
+    if (arx_tops) *arx_tops = nthreads * dr * 96.0 / (best_arx * 1e-3) / 1e12;   // 8 quarter-rounds x 12 ops
+    if (imad_tops) *imad_tops = nthreads * it * 8.0 / (best_imad * 1e-3) / 1e12;  // multiply-adds only
+    return 0;
 }
 
 void *symrelay_alloc_pinned(symrelay_ctx *ctx, uint64_t bytes) {

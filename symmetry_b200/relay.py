@@ -162,6 +162,12 @@ class SymRelay:
         self._check(self.lib.symrelay_batch_device(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk, d_in,
                                                    d_out, d_status, None, None, stream))
 
+    def probe_int_peak(self, gpu_index: int = 0):
+        """(arx_tops, imad_tops): measured integer throughput, the ALU roofline denominators."""
+        a, m = C.c_double(0), C.c_double(0)
+        self._check(self.lib.symrelay_probe_int_peak(self.ctx, gpu_index, C.byref(a), C.byref(m)))
+        return a.value, m.value
+
     def alloc_pinned(self, nbytes: int) -> np.ndarray:
         """Pinned host arena as a uint8 numpy view (freed with the context)."""
         p = self.lib.symrelay_alloc_pinned(self.ctx, nbytes)

@@ -16,6 +16,12 @@ pytestmark = pytest.mark.gpu
 
 
 class GpuBackend:
+    """Host-arena batches through symrelay_batch_host.  The whole out arena is copied back from
+    the device staging buffer, so bytes between frames are unspecified (preserves_gaps False);
+    GpuDeviceBackend below checks the exact-footprint property on device buffers."""
+
+    preserves_gaps = False
+
     def __init__(self, relay):
         self.relay = relay
 
@@ -31,6 +37,30 @@ class GpuBackend:
 
     def export(self, slot):
         return self.relay.export(slot)
+
+
+class GpuDeviceBackend(GpuBackend):
+    """Same scenarios through symrelay_batch_device on torch tensors: the kernels must touch
+    nothing outside the frames they write."""
+
+    preserves_gaps = True
+
+    def run(self, descs, arena_in, arena_out):
+        import torch
+
+        dev = torch.device("cuda:0")
+        tiles, n_bulk = self.relay.plan(descs)
+        t_desc = torch.from_numpy(descs.view(np.uint8).copy()).to(dev)
+        t_tiles = torch.from_numpy(tiles.view(np.uint8).copy()).to(dev)
+        t_in = torch.from_numpy(np.ascontiguousarray(arena_in)).to(dev)
+        t_out = torch.from_numpy(np.ascontiguousarray(arena_out)).to(dev)
+        t_status = torch.full((len(descs),), 0xFF, dtype=torch.int32, device=dev)
+        self.relay.batch_device(t_desc.data_ptr(), len(descs), t_tiles.data_ptr(), len(tiles), n_bulk,
+                                t_in.data_ptr(), t_out.data_ptr(), t_status.data_ptr(),
+                                stream=torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        arena_out[:] = t_out.cpu().numpy()
+        return t_status.cpu().numpy().astype(np.uint32)
 
 
 @pytest.fixture(scope="module")
@@ -63,6 +93,16 @@ def test_header_init_matches_libsodium(relay):
     for i in (0, 1, 150, 299):
         want = ls.State(bytes(tks[i]), bytes(ths[i])).raw
         assert relay.export(int(slots[i])) == (want, want)
+
+
+@pytest.fixture()
+def dbe(relay):
+    return GpuDeviceBackend(relay)
+
+
+def test_device_path_touches_only_its_frames(dbe):
+    lens = list(range(0, 200)) + [1919, 1920, 1921, 2048, 4097, 65537]
+    pc.seal_open_roundtrip(dbe, lens, [i % 4 for i in range(len(lens))], seed=12, chain=2, corrupt=(3, 64, 200, 205))
 
 
 def test_golden_chains(be, ss_vectors):
