@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, "libsymrelay.so")
+# SYMRELAY_SO lets A/B experiments load another build of the same library (never a different implementation)
+SO_PATH = os.environ.get("SYMRELAY_SO") or os.path.join(HERE, "libsymrelay.so")
 
 # every symbol include/symrelay.h declares (tests/test_abi_symbols.py cross-checks the header)
 EXPORTS = (

@@ -68,6 +68,14 @@ struct SsArgs {
 };
 
 // ---------------------------------------------------------------- ChaCha20 --
+// Double rounds unrolled per loop trip.  1 keeps the kernels' code inside the
+// instruction caches (the fully unrolled kernels were 64 KB and stalled on
+// instruction fetch with one warp per SM sub-partition); see DESIGN.md.
+#ifndef SS_CHACHA_UNROLL
+#define SS_CHACHA_UNROLL 1
+#endif
+#define SS_PRAGMA_(x) _Pragma(#x)
+#define SS_UNROLL(n) SS_PRAGMA_(unroll n)
 #define SS_QR(a, b, c, d)   \
     a += b; d ^= a; d = ss_rotl16(d); \
     c += d; b ^= c; b = ss_rotl12(b); \
@@ -81,7 +89,7 @@ SS_DEV void ss_chacha_block(const uint32_t k[8], uint32_t ic, uint32_t n0, uint3
 #pragma unroll
     for (int i = 0; i < 8; i++) x[4 + i] = k[i];
     x[12] = ic; x[13] = n0; x[14] = n1; x[15] = n2;
-#pragma unroll
+    SS_UNROLL(SS_CHACHA_UNROLL)
     for (int r = 0; r < 10; r++) {
         SS_QR(x[0], x[4], x[8], x[12])
         SS_QR(x[1], x[5], x[9], x[13])
