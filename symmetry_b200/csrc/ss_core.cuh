@@ -293,11 +293,14 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
     const uint32_t nfr = BULK ? 1u : (tile.n_kind & 0xffffu);
 
     // ---- lane -> (frame f, first lane st of that frame) ---------------------
-    uint32_t d_slot = 0, d_in = 0, d_out = 0, d_lf = 0, my_nc = 0;
+    uint32_t d_slot = 0, d_in = 0, d_out = 0, d_lf = 0, my_nc = 0, d_skip = 0;
     if (lane < nfr) {
         const SsDesc d = a.desc[tile.first + lane];
         d_slot = d.slot; d_in = d.in_off; d_out = d.out_off; d_lf = d.len_flags;
         my_nc = 2u + (((d_lf & 0xffffffu) + 63u) >> 6);
+        // A frame the extractor refused (TypeError in the reference, or a shape it leaves to the
+        // host) is not sealed: provider.ts:243-248 throws before peer.write(chunk).
+        if ((d_lf & SS_F_EXTRACT) && !(d_lf & SS_F_OPEN)) d_skip = a.status[tile.first + lane] != SS_ST_OK;
     }
     uint32_t f = 0, st = 0;
     bool valid = true;
@@ -319,6 +322,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
     const uint32_t in_off = ss_shfl(d_in, f);
     const uint32_t out_off = ss_shfl(d_out, f);
     const uint32_t lf = ss_shfl(d_lf, f);
+    if (ss_shfl(d_skip, f)) valid = false;
 
     const uint32_t mlen = lf & 0xffffffu;
     const bool is_open = (lf & SS_F_OPEN) != 0;

@@ -22,6 +22,7 @@
 #include "../../include/symrelay.h"
 #include "plan.h"
 #include "ss_core.cuh"
+#include "ss_extract.cuh"
 
 static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) == sizeof(SsTile), "ABI layout");
 
@@ -39,6 +40,27 @@ __global__ void __launch_bounds__(128) ss_bulk_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
     ss_process_tile<true>(a, warp);
+}
+
+// Delta extraction, one thread per frame that carries
+// SYMRELAY_F_EXTRACT.  Runs before the seal kernel of the same batch: it leaves
+// its verdict in status[i] (the seal kernel skips frames whose verdict is not
+// OK) and the delta bytes at delta_arena + in_off (the plaintext layout, so no
+// allocation or scratch is needed: every frame slot holds >= max(16, mlen) bytes).
+__global__ void __launch_bounds__(128) ss_extract_kernel(const SsDesc *desc, uint32_t n, const uint8_t *in,
+                                                         const uint4 *states, uint32_t *status,
+                                                         symrelay_delta *delta, uint8_t *delta_arena) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const SsDesc d = desc[i];
+    if (!(d.len_flags & SS_F_EXTRACT) || (d.len_flags & SS_F_OPEN)) return;
+    const uint32_t mlen = d.len_flags & 0xffffffu;
+    const uint32_t kind = states[((size_t)d.slot * 2u) * 3u + 2u].w;   // provider kind lives in the tx state's meta word
+    const uint32_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
+    const sx::Result r = sx::extract_chunk(in + d.in_off, mlen, kind, delta_arena + d.in_off, cap);
+    status[i] = r.status;
+    delta[i].off = d.in_off;
+    delta[i].len = r.len;
 }
 
 // Stream set-up (libsodium init_push/init_pull): one thread per
@@ -148,6 +170,9 @@ struct Stage {
     uint8_t *h_ctrl = nullptr;   // pinned mirror
     uint8_t *d_in = nullptr, *d_out = nullptr;
     uint32_t *d_status = nullptr, *h_status = nullptr;
+    symrelay_delta *d_delta = nullptr, *h_delta = nullptr;
+    uint8_t *d_delta_arena = nullptr;   // allocated on first use (extraction batches only)
+    symrelay_delta *user_delta = nullptr;
     cudaEvent_t ev_in = nullptr, ev_k = nullptr, ev_out = nullptr;
     // in-flight batch bookkeeping
     int64_t ticket = -1;
@@ -203,10 +228,15 @@ static int fail(symrelay_ctx *ctx, int code, const char *fmt, ...) {
 
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
-static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, const symrelay_tile *d_tiles,
+static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t n, const symrelay_tile *d_tiles,
                         uint32_t n_tiles, uint32_t n_bulk, const uint8_t *d_in, uint8_t *d_out, uint4 *d_states,
-                        uint32_t *d_status, cudaStream_t stream) {
+                        uint32_t *d_status, symrelay_delta *d_delta, uint8_t *d_delta_arena, cudaStream_t stream) {
     const uint32_t n_packed = n_tiles - n_bulk;
+    if (d_delta && d_delta_arena) {
+        ss_extract_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
+                                                               d_states, d_status, d_delta, d_delta_arena);
+        ctx->launches++;
+    }
     SsArgs a;
     a.desc = reinterpret_cast<const SsDesc *>(d_desc);
     a.in = d_in;
@@ -274,6 +304,8 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
         CU(ctx, cudaMalloc(&st.d_out, ctx->opts.stage_bytes));
         CU(ctx, cudaMalloc(&st.d_status, (size_t)ctx->opts.max_batch_frames * 4u));
         CU(ctx, cudaHostAlloc(&st.h_status, (size_t)ctx->opts.max_batch_frames * 4u, cudaHostAllocDefault));
+        CU(ctx, cudaMalloc(&st.d_delta, (size_t)ctx->opts.max_batch_frames * sizeof(symrelay_delta)));
+        CU(ctx, cudaHostAlloc(&st.h_delta, (size_t)ctx->opts.max_batch_frames * sizeof(symrelay_delta), cudaHostAllocDefault));
         CU(ctx, cudaEventCreateWithFlags(&st.ev_in, cudaEventDisableTiming));
         CU(ctx, cudaEventCreateWithFlags(&st.ev_k, cudaEventDisableTiming));
         CU(ctx, cudaEventCreateWithFlags(&st.ev_out, cudaEventDisableTiming));
@@ -289,6 +321,7 @@ static void shard_free(Shard &sh) {
     for (Stage &st : sh.stages) {
         cudaFree(st.d_ctrl); cudaFreeHost(st.h_ctrl); cudaFree(st.d_in); cudaFree(st.d_out);
         cudaFree(st.d_status); cudaFreeHost(st.h_status);
+        cudaFree(st.d_delta); cudaFreeHost(st.h_delta); cudaFree(st.d_delta_arena);
         if (st.ev_in) cudaEventDestroy(st.ev_in);
         if (st.ev_k) cudaEventDestroy(st.ev_k);
         if (st.ev_out) cudaEventDestroy(st.ev_out);
@@ -476,15 +509,14 @@ int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const symrelay_desc 
                           const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
                           const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, symrelay_delta *d_delta,
                           uint8_t *d_delta_arena, void *cuda_stream) {
-    (void)d_delta; (void)d_delta_arena;
     if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
     if (n == 0 || n_tiles == 0) return 0;
     if (!d_desc || !d_tiles || !d_in || !d_out || !d_status || n_bulk_tiles > n_tiles)
         return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_device: null pointer or bad tile counts");
     Shard &sh = ctx->shard[gpu_index];
     CU(ctx, cudaSetDevice(sh.dev));
-    return launch_tiles(ctx, d_desc, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status,
-                        (cudaStream_t)cuda_stream);
+    return launch_tiles(ctx, d_desc, n, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status, d_delta,
+                        d_delta_arena, (cudaStream_t)cuda_stream);
 }
 
 static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st) {
@@ -492,13 +524,15 @@ static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st) {
     CU(ctx, cudaSetDevice(sh.dev));
     CU(ctx, cudaEventSynchronize(st.ev_out));
     if (st.user_status) memcpy(st.user_status, st.h_status, (size_t)st.n * 4u);
+    if (st.user_delta) memcpy(st.user_delta, st.h_delta, (size_t)st.n * sizeof(symrelay_delta));
     st.busy = false;
     return 0;
 }
 
 static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *desc, uint32_t n,
                              const uint8_t *in, uint64_t in_bytes, uint8_t *out, uint64_t out_bytes,
-                             uint32_t *status) {
+                             uint32_t *status, symrelay_delta *delta, uint8_t *delta_arena,
+                             uint64_t delta_arena_bytes) {
     Shard &sh = ctx->shard[gpu_index];
     if (n > ctx->opts.max_batch_frames) return fail(ctx, SYMRELAY_EINVAL, "batch of %u frames exceeds max_batch_frames %u", n, ctx->opts.max_batch_frames);
     if (in_bytes > ctx->opts.stage_bytes || out_bytes > ctx->opts.stage_bytes)
@@ -516,15 +550,25 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     uint32_t n_bulk = 0;
     const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk);
     if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
+    bool extract = false;
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t mlen = desc[i].len_flags & SYMRELAY_LEN_MASK;
         const bool op = desc[i].len_flags & SYMRELAY_F_OPEN;
+        if ((desc[i].len_flags & SYMRELAY_F_EXTRACT) && !op) {
+            extract = true;
+            const uint64_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
+            if ((uint64_t)desc[i].in_off + cap > delta_arena_bytes || (uint64_t)desc[i].in_off + cap > in_bytes)
+                return fail(ctx, SYMRELAY_EINVAL, "descriptor %u: delta slot (in_off + max(16, align16(len))) outside the arenas", i);
+        }
         const uint64_t in_end = (uint64_t)desc[i].in_off + mlen + (op ? 20u : 0u);
         const uint64_t out_end = (uint64_t)desc[i].out_off + mlen + (op ? 0u : 20u);
         if (in_end > in_bytes || out_end > out_bytes || desc[i].slot >= ctx->opts.max_streams ||
             (int)(desc[i].slot % (uint32_t)ctx->n_gpus) != gpu_index)
             return fail(ctx, SYMRELAY_EINVAL, "descriptor %u: frame outside its arena or slot not on gpu %d", i, gpu_index);
     }
+    if (extract && (!delta || !delta_arena))
+        return fail(ctx, SYMRELAY_EINVAL, "SYMRELAY_F_EXTRACT needs delta and delta_arena");
+    if (extract && !st.d_delta_arena) CU(ctx, cudaMalloc(&st.d_delta_arena, ctx->opts.stage_bytes));
     const size_t tiles_bytes = align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
     memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
     const size_t ctrl_bytes = tiles_bytes + (size_t)n * sizeof(symrelay_desc);
@@ -533,18 +577,25 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (in_bytes) CU(ctx, cudaMemcpyAsync(st.d_in, in, in_bytes, cudaMemcpyHostToDevice, sh.s_in));
     CU(ctx, cudaEventRecord(st.ev_in, sh.s_in));
     CU(ctx, cudaStreamWaitEvent(sh.s_k, st.ev_in, 0));
-    rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(st.d_ctrl + tiles_bytes),
+    rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(st.d_ctrl + tiles_bytes), n,
                       reinterpret_cast<const symrelay_tile *>(st.d_ctrl), (uint32_t)n_tiles, n_bulk, st.d_in, st.d_out,
-                      sh.d_states, st.d_status, sh.s_k);
+                      sh.d_states, st.d_status, extract ? st.d_delta : nullptr, extract ? st.d_delta_arena : nullptr,
+                      sh.s_k);
     if (rc) return rc;
     CU(ctx, cudaEventRecord(st.ev_k, sh.s_k));
     CU(ctx, cudaStreamWaitEvent(sh.s_out, st.ev_k, 0));
     if (out_bytes) CU(ctx, cudaMemcpyAsync(out, st.d_out, out_bytes, cudaMemcpyDeviceToHost, sh.s_out));
     CU(ctx, cudaMemcpyAsync(st.h_status, st.d_status, (size_t)n * 4u, cudaMemcpyDeviceToHost, sh.s_out));
+    if (extract) {
+        CU(ctx, cudaMemcpyAsync(st.h_delta, st.d_delta, (size_t)n * sizeof(symrelay_delta), cudaMemcpyDeviceToHost, sh.s_out));
+        CU(ctx, cudaMemcpyAsync(delta_arena, st.d_delta_arena, in_bytes < delta_arena_bytes ? in_bytes : delta_arena_bytes,
+                                cudaMemcpyDeviceToHost, sh.s_out));
+    }
     CU(ctx, cudaEventRecord(st.ev_out, sh.s_out));
     st.busy = true;
     st.n = n;
     st.user_status = status;
+    st.user_delta = extract ? delta : nullptr;
     st.ticket = (seq << 3) | gpu_index;
     return st.ticket;
 }
@@ -552,11 +603,11 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
 int64_t symrelay_batch_submit(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, const uint8_t *in,
                               uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
                               symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes) {
-    (void)delta; (void)delta_arena; (void)delta_arena_bytes;
     if (!ctx || !desc || n == 0 || !in || !out) return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_submit: null/empty argument");
     std::lock_guard<std::mutex> lk(ctx->mu);
     const int gpu_index = (int)(desc[0].slot % (uint32_t)ctx->n_gpus);
-    return submit_locked(ctx, gpu_index, desc, n, in, in_bytes, out, out_bytes, status);
+    return submit_locked(ctx, gpu_index, desc, n, in, in_bytes, out, out_bytes, status, delta, delta_arena,
+                         delta_arena_bytes);
 }
 
 int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket) {

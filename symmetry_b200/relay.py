@@ -140,27 +140,35 @@ class SymRelay:
         return tiles[:need], nb.value
 
     def batch_host(self, descs: np.ndarray, arena_in: np.ndarray, arena_out: np.ndarray,
-                   status: np.ndarray | None = None) -> np.ndarray:
-        """Synchronous mixed seal/open batch on HOST arenas (N x push/pull in one call)."""
+                   status: np.ndarray | None = None, delta: np.ndarray | None = None,
+                   delta_arena: np.ndarray | None = None) -> np.ndarray:
+        """Synchronous mixed seal/open batch on HOST arenas (N x push/pull in one call).  Frames with
+        F_EXTRACT also fill delta[i] = (off, len) and the delta bytes in delta_arena."""
         if status is None:
             status = np.full(len(descs), 0xFF, dtype=np.uint32)
-        self._check(self.lib.symrelay_batch_host(self.ctx, _ptr(descs), len(descs), _ptr(arena_in), arena_in.nbytes,
-                                                 _ptr(arena_out), arena_out.nbytes, _ptr(status), None, None, 0))
+        self._check(self.lib.symrelay_batch_host(
+            self.ctx, _ptr(descs), len(descs), _ptr(arena_in), arena_in.nbytes, _ptr(arena_out), arena_out.nbytes,
+            _ptr(status), _ptr(delta) or None, _ptr(delta_arena) or None,
+            0 if delta_arena is None else delta_arena.nbytes))
         return status
 
-    def submit(self, descs: np.ndarray, arena_in, in_bytes: int, arena_out, out_bytes: int, status) -> int:
+    def submit(self, descs: np.ndarray, arena_in, in_bytes: int, arena_out, out_bytes: int, status,
+               delta=None, delta_arena=None, delta_arena_bytes: int = 0) -> int:
         """Pipelined batch; buffers must stay alive until wait(ticket)."""
-        return self._check(self.lib.symrelay_batch_submit(self.ctx, _ptr(descs), len(descs), _ptr(arena_in), in_bytes,
-                                                          _ptr(arena_out), out_bytes, _ptr(status), None, None, 0))
+        return self._check(self.lib.symrelay_batch_submit(
+            self.ctx, _ptr(descs), len(descs), _ptr(arena_in), in_bytes, _ptr(arena_out), out_bytes, _ptr(status),
+            _ptr(delta) or None, _ptr(delta_arena) or None, delta_arena_bytes))
 
     def wait(self, ticket: int) -> None:
         self._check(self.lib.symrelay_batch_wait(self.ctx, ticket))
 
     def batch_device(self, d_desc: int, n: int, d_tiles: int, n_tiles: int, n_bulk: int, d_in: int, d_out: int,
-                     d_status: int, stream: int = 0, gpu_index: int = 0) -> None:
-        """One launch on device-resident buffers (raw device pointers), asynchronous on `stream`."""
+                     d_status: int, stream: int = 0, gpu_index: int = 0, d_delta: int = 0,
+                     d_delta_arena: int = 0) -> None:
+        """One launch per tile class (plus the extractor when d_delta is given) on device-resident
+        buffers (raw device pointers), asynchronous on `stream`."""
         self._check(self.lib.symrelay_batch_device(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk, d_in,
-                                                   d_out, d_status, None, None, stream))
+                                                   d_out, d_status, d_delta or None, d_delta_arena or None, stream))
 
     def probe_int_peak(self, gpu_index: int = 0):
         """(arx_tops, imad_tops): measured integer throughput, the ALU roofline denominators."""

@@ -7,6 +7,7 @@
 
 #include "../../symmetry_b200/csrc/plan.h"
 #include "../../symmetry_b200/csrc/ss_core.cuh"
+#include "../../symmetry_b200/csrc/ss_extract.cuh"
 
 thread_local uint32_t emu_lane_id;
 thread_local EmuWarp *emu_warp;
@@ -49,4 +50,12 @@ extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *til
     for (uint32_t l = 0; l < 32; l++) pthread_join(th[l], nullptr);
     pthread_barrier_destroy(&warp.bar);
     return 0;
+}
+
+// The extractor is thread-local code (no warp collectives): call it directly.
+extern "C" uint32_t emu_extract(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap,
+                                uint32_t *len_out) {
+    const sx::Result r = sx::extract_chunk(text, n, kind, out, cap);
+    *len_out = r.len;
+    return r.status;
 }

@@ -1,0 +1,114 @@
+"""GPU parity for the fused extractor: SYMRELAY_F_EXTRACT frames through the
+C ABI.  Deltas and THROW verdicts must equal oracle/extract.py; frames the reference would not have
+written (TypeError) or that the GPU hands back (UNSUPPORTED) must leave the stream state untouched,
+all others must be sealed bit-exactly (libsodium)."""
+import numpy as np
+import pytest
+
+import batch_util as bu
+from oracle import extract as ex
+from oracle import libsodium as ls
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def relay():
+    import symmetry_b200 as sb
+
+    r = sb.SymRelay(gpu_ids=(0,), max_streams=1 << 16)
+    yield r
+    r.close()
+
+
+def run_extract_batch(relay, slots, chunks):
+    import symmetry_b200 as sb
+
+    lens = [len(c) for c in chunks]
+    p_offs, p_bytes = bu.plain_layout(lens)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    plain = relay.alloc_pinned(p_bytes)
+    plain[:] = 0
+    for c, o in zip(chunks, p_offs):
+        plain[o : o + len(c)] = np.frombuffer(c, dtype=np.uint8)
+    wire = relay.alloc_pinned(w_bytes)
+    wire[:] = 0
+    darena = relay.alloc_pinned(p_bytes)
+    delta = np.zeros(len(chunks), dtype=sb.DELTA_DTYPE)
+    d = bu.make_descs(slots, lens, p_offs, w_offs, extract=True)
+    st = relay.batch_host(d, plain, wire, delta=delta, delta_arena=darena)
+    deltas = [bytes(darena[int(x["off"]) : int(x["off"]) + int(x["len"])]) for x in delta]
+    return st, deltas, wire, w_offs
+
+
+def test_quirk_matrix_through_the_abi(relay, extract_cases):
+    import symmetry_b200 as sb
+
+    rng = np.random.default_rng(5)
+    by_provider = {}
+    for c in extract_cases:
+        by_provider.setdefault(c["provider"], []).append(c)
+    for prov, cases in by_provider.items():
+        n = len(cases)
+        keys = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        hdrs = rng.integers(0, 256, (n, 24), dtype=np.uint8)
+        slots = relay.open_streams(keys, hdrs, None, None, provider=sb.provider_kind(prov))
+        chunks = [bytes.fromhex(c["chunk"]) for c in cases]
+        st, deltas, wire, w_offs = run_extract_batch(relay, slots, chunks)
+        n_uns = 0
+        for i, c in enumerate(cases):
+            code = int(st[i]) & 0xFF
+            ref = ls.State(bytes(keys[i]), bytes(hdrs[i]))
+            if code == sb.relay.ST_EXTRACT_UNSUPPORTED:
+                n_uns += 1
+                assert relay.export(int(slots[i]))[0] == ref.raw, "unsupported frame must not be sealed"
+                continue
+            if c["status"] == ex.THROW:
+                assert code == sb.relay.ST_EXTRACT_THROW, (prov, chunks[i])
+                assert relay.export(int(slots[i]))[0] == ref.raw, "TypeError chunk must not be sealed"
+                continue
+            assert code == 0, (prov, chunks[i], code)
+            assert deltas[i].hex() == c["delta"], (prov, chunks[i])
+            want = ref.seal_frame(chunks[i])
+            assert bytes(wire[w_offs[i] : w_offs[i] + len(want)]) == want
+            assert relay.export(int(slots[i]))[0] == ref.raw
+        assert n_uns <= 2, (prov, n_uns)
+        for s in slots:
+            relay.close_stream(int(s))
+
+
+def test_config5_chat_completions_accumulate(relay):
+    """BASELINE config 5 in miniature: many streams of synthetic llama3:8b completions, apiProvider
+    ollama; per batch one chunk per stream; wire frames and per-stream `completion` strings."""
+    import symmetry_b200 as sb
+    from symmetry_b200 import synth
+
+    n, n_chunks = 2048, 6
+    keys, hdrs = synth.stream_keys(n)
+    slots = relay.open_streams(keys, hdrs, None, None, provider=sb.PROVIDER_OLLAMA)
+    streams = [synth.chat_chunks(n_chunks, seed=77, stream_id=i) for i in range(n)]
+    completion = [b""] * n
+    want_completion = [b""] * n
+    refs = {i: ls.State(bytes(keys[i]), bytes(hdrs[i])) for i in range(0, n, 97)}
+    for step in range(n_chunks + 2):
+        chunks = [s[step] for s in streams]
+        st, deltas, wire, w_offs = run_extract_batch(relay, slots, chunks)
+        assert (st == 0).all()
+        for i in range(n):
+            completion[i] += deltas[i]
+            code, dl = ex.extract("ollama", chunks[i])
+            assert code == ex.OK
+            want_completion[i] += dl
+        for i, ref in refs.items():
+            want = ref.seal_frame(chunks[i])
+            assert bytes(wire[w_offs[i] : w_offs[i] + len(want)]) == want
+    assert completion == want_completion
+    assert all(len(c) > 0 for c in completion)
+
+
+def test_extract_flag_needs_delta_buffers(relay):
+    import symmetry_b200 as sb
+
+    d = bu.make_descs([0], [16], [0], [12], extract=True)
+    with pytest.raises(sb.RelayError):
+        relay.batch_host(d, bu.aligned_zeros(64), bu.aligned_zeros(64))
