@@ -428,13 +428,34 @@ def run_ours(args):
         i2 += 1
     e2e_drain()
     barrier()
+    # The timed loop is driven from C (tools/e2e_driver.c, a plain caller of the public C ABI, as the
+    # N-API addon would be): per batch it calls symrelay_batch_wait(ticket[i-4]) then
+    # symrelay_batch_submit(...) on the same ring -- the calls e2e_step() makes, minus the interpreter.
+    e2e_driver = "python"
     t0 = time.perf_counter()
-    for _ in range(K2):
-        e2e_step(i2)
-        i2 += 1
-    e2e_drain()
-    torch.cuda.synchronize()
-    t1 = time.perf_counter()
+    if K2 and not args.py_e2e:
+        from symmetry_b200 import build as sbuild
+
+        drv = C.CDLL(sbuild.build_driver())
+        drv.e2e_ring_run.restype = C.c_double
+        drv.e2e_ring_run.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64,
+                                     C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
+        stat_all = np.full(R2 * 2 * n, 0xFF, dtype=np.uint32)
+        secs = drv.e2e_ring_run(relay.ctx, e_full.ctypes.data, 2 * n, hbase, lay.slot_bytes, lay.in_bytes, lay.P,
+                                lay.out_bytes, R2, D_E2E, i2, K2, stat_all.ctypes.data, None)
+        assert secs > 0, f"e2e driver failed: {secs}"
+        i2 += K2
+        for j in range(min(R2, K2)):
+            hstat[j][:] = stat_all[j * 2 * n:(j + 1) * 2 * n]
+        e2e_driver = "tools/e2e_driver.c"
+        t1 = t0 + secs
+    else:
+        for _ in range(K2):
+            e2e_step(i2)
+            i2 += 1
+        e2e_drain()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
     e2e_sec = max_over_ranks(t1 - t0)
     clk = clocks.stop([(t_w0, t_w1), (t0, t1)])
     for j in range(R2 if K2 else 0):
@@ -516,7 +537,7 @@ def run_ours(args):
                 "h2d_bytes_per_step": lay.in_bytes + 2 * n * 16 + len(tiles_full) * 8,
                 "d2h_bytes_per_step": lay.out_bytes + 2 * n * 4, "steps": K2,
                 "ms_per_step": (e2e_sec / K2 * 1e3) if K2 else None,
-                "path": "symrelay_batch_submit/wait on pinned host arenas, pipeline depth 4, host clock"},
+                "path": "symrelay_batch_submit/wait on pinned host arenas, pipeline depth 4, host clock; loop driver: " + e2e_driver},
         "gpu_launches": int(gpu_launches),
         "launches_per_step": launches_per_step,
         "clocks": clk,
@@ -530,6 +551,127 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------- c5 --
+def run_c5(args):
+    """configs[4]: fused relay -- per batch one synthetic chat-completion chunk per stream:
+    prefix test + JSON validation + delta extraction + seal (device-resident)."""
+    import torch
+
+    import batch_util as bu
+    import symmetry_b200 as sb
+    from oracle import extract as ex
+    from oracle import libsodium as ls
+    from symmetry_b200 import synth
+
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda:0")
+    n, n_kinds = 16384, 16
+    K, W = args.steps, args.warmup
+    relay = sb.SymRelay(gpu_ids=(0,), max_streams=2 * n)
+    keys, hdrs = synth.stream_keys(n)
+    slots = relay.open_streams(keys, hdrs, None, None, provider=sb.PROVIDER_OLLAMA)
+    # 64 distinct completions cycled over the streams; ring slot j holds chunk j of each stream
+    base_streams = [synth.chat_chunks(n_kinds, seed=5, stream_id=i) for i in range(64)]
+    R = n_kinds + 2
+    slot_chunks = [[base_streams[s % 64][j] for s in range(n)] for j in range(R)]
+    lays = []
+    for j in range(R):
+        lens = [len(c) for c in slot_chunks[j]]
+        p_offs, P = bu.plain_layout(lens)
+        w_offs, Wb = bu.wire_layout(lens)
+        lays.append((lens, p_offs, P, w_offs, Wb))
+    Pmax = max(l[2] for l in lays)
+    Wmax = max(l[4] for l in lays)
+    t_in = torch.zeros(R, Pmax, dtype=torch.uint8, device=dev)
+    t_out = torch.zeros(R, Wmax, dtype=torch.uint8, device=dev)
+    t_darena = torch.zeros(R, Pmax, dtype=torch.uint8, device=dev)
+    t_delta = torch.zeros(R, n, 2, dtype=torch.int32, device=dev)
+    t_status = torch.zeros(R, n, dtype=torch.int32, device=dev)
+    t_desc, t_tiles, meta = [], [], []
+    for j, (lens, p_offs, P, w_offs, Wb) in enumerate(lays):
+        host = np.zeros(Pmax, dtype=np.uint8)
+        for c, o in zip(slot_chunks[j], p_offs):
+            host[o:o + len(c)] = np.frombuffer(c, dtype=np.uint8)
+        t_in[j].copy_(torch.from_numpy(host))
+        d = bu.make_descs(slots, lens, p_offs, w_offs, extract=True)
+        tiles, nb = relay.plan(d)
+        t_desc.append(torch.from_numpy(d.view(np.uint8).copy()).to(dev))
+        t_tiles.append(torch.from_numpy(tiles.view(np.uint8).copy()).to(dev))
+        meta.append((len(tiles), nb))
+
+    def step(i):
+        j = i % R
+        relay.batch_device(t_desc[j].data_ptr(), n, t_tiles[j].data_ptr(), meta[j][0], meta[j][1], t_in[j].data_ptr(),
+                           t_out[j].data_ptr(), t_status[j].data_ptr(), stream=torch.cuda.current_stream().cuda_stream,
+                           d_delta=t_delta[j].data_ptr(), d_delta_arena=t_darena[j].data_ptr())
+
+    i = 0
+    for _ in range(W):
+        step(i); i += 1
+    while i % R:
+        step(i); i += 1
+    torch.cuda.synchronize()
+    l0 = relay.launches
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for j in range(R):
+            step(i + j)
+    per_lap = relay.launches - l0
+    reps = max(1, K // R)
+    clocks = ClockSampler(0)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tw0 = time.perf_counter()
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+        i += R
+    e1.record()
+    torch.cuda.synchronize()
+    tw1 = time.perf_counter()
+    ms = e0.elapsed_time(e1)
+    steps = reps * R
+    # parity: statuses OK, deltas == oracle for the last lap, chains == libsodium on sampled streams
+    assert (t_status.cpu().numpy() == 0).all()
+    dl = t_delta.cpu().numpy()
+    da = t_darena.cpu().numpy()
+    for j in range(R):
+        for s in range(0, n, 1021):
+            off, ln = int(dl[j, s, 0]), int(dl[j, s, 1])
+            code, want = ex.extract("ollama", slot_chunks[j][s])
+            assert code == ex.OK and bytes(da[j, off:off + ln]) == want, (j, s)
+    for s in (0, 1, n - 1):
+        ref = ls.State(bytes(keys[s]), bytes(hdrs[s]))
+        for k in range(i):
+            w = ref.seal_frame(slot_chunks[k % R][s])
+        assert relay.export(int(slots[s]))[0] == ref.raw, "c5 tx chain differs from libsodium"
+        jl = (i - 1) % R
+        o = lays[jl][3][s]
+        assert bytes(t_out[jl, o:o + len(w)].cpu().numpy()) == w
+    arx, imad = relay.probe_int_peak(0)
+    clk = clocks.stop([(tw0, tw1)])
+    all_lens = [x for l in lays for x in l[0]]
+    mean_len = sum(all_lens) / len(all_lens)
+    ops = sum(int_ops(l[0]) + 4 * sum(l[0]) for l in lays) / R          # +4 ops/byte for the extractor (SURVEY 8(d))
+    per_step = ms / steps
+    line = {
+        "metric": METRIC, "value": n * steps / (ms * 1e-3), "unit": "frames/s", "n_gpus": 1, "steps": steps,
+        "warmup": W, "ms_per_step": per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "configs[4]: fused SSE data: test + JSON validate + delta extract + seal, 16,384 streams "
+                               "of synthetic llama3:8b chat completions, apiProvider ollama",
+                   "streams_per_gpu": n, "mean_chunk_bytes": mean_len, "launch": f"{reps} replays of a CUDA graph of {R} steps",
+                   "l2": f"ring of {R} distinct batches ({(R * (2 * Pmax + Wmax)) >> 20} MiB) visited round-robin"},
+        "gb_per_s": mean_len * n * steps / (ms * 1e-3) / 1e9,
+        "alu_roofline": {"bound": "int_alu", "achieved": ops / (per_step * 1e-3) / 1e12, "peak": arx, "unit": "Tint-op/s",
+                         "frac": ops / (per_step * 1e-3) / 1e12 / arx},
+        "gpu_launches": reps * per_lap, "launches_per_step": per_lap / R, "clocks": clk,
+        "parity": "deltas == oracle/extract.py on sampled frames of every ring slot; chains == libsodium",
+    }
+    print(json.dumps(line), flush=True)
+    relay.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -539,6 +681,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--py-e2e", action="store_true", help="drive the e2e loop from Python instead of tools/e2e_driver.c")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (huge workloads)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step directly (no CUDA graph)")
     args = ap.parse_args()
@@ -546,6 +689,8 @@ def main():
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "c5":
+        run_c5(args)
     else:
         run_ours(args)
 

@@ -106,6 +106,8 @@ typedef struct symrelay_delta {
     uint32_t len; /* WTF-8 bytes appended to `completion` (provider.ts:243) */
 } symrelay_delta;
 
+#define SYMRELAY_OPT_NO_ZERO_COPY 1u /* opts.flags: always stage host batches through device buffers */
+
 typedef struct symrelay_opts {
     uint32_t max_streams;     /* capacity of the slot table (default 65536) */
     uint32_t pipeline_depth;  /* host-batch pipeline stages (default 4) */
@@ -169,7 +171,9 @@ SYMRELAY_API int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const s
                           const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, symrelay_delta *d_delta,
                           uint8_t *d_delta_arena, void *cuda_stream);
 /* HOST buffers (pinned from symrelay_alloc_pinned for full speed, pageable
- * accepted): plans, copies in, launches, copies out, waits.  status[n] and, if
+ * accepted): plans, copies in, launches, copies out, waits.  Batches of up to
+ * 1 MiB (in + out) whose arenas came from symrelay_alloc_pinned skip the copies:
+ * the kernels read and write the pinned host arenas directly over PCIe.  status[n] and, if
  * any descriptor has F_EXTRACT, delta[n] + delta_arena (delta_arena_bytes) are
  * filled.  in_bytes/out_bytes are the arena sizes (multiples of 16). */
 SYMRELAY_API int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, const uint8_t *in,

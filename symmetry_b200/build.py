@@ -57,6 +57,19 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = SO) -
     return out
 
 
+DRIVER_SO = os.path.join(os.path.dirname(HERE), "tools", "libe2e_driver.so")
+
+
+def build_driver(force: bool = False) -> str:
+    """tools/e2e_driver.c: a plain-C caller of the public ABI (no CUDA in it), linked against libsymrelay.so."""
+    src = os.path.join(os.path.dirname(HERE), "tools", "e2e_driver.c")
+    if force or not os.path.exists(DRIVER_SO) or os.path.getmtime(src) > os.path.getmtime(DRIVER_SO):
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", DRIVER_SO, src, "-L" + HERE, "-lsymrelay",
+                        "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/../symmetry_b200"], check=True)
+    return DRIVER_SO
+
+
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose=True)
+    build_driver(force=True)
     print(SO)

@@ -58,10 +58,10 @@ class SymRelay:
     """One context = one state table per GPU + the batch pipeline."""
 
     def __init__(self, gpu_ids=(0,), max_streams: int = 65536, pipeline_depth: int = 4,
-                 stage_bytes: int = 64 << 20, max_batch_frames: int = 131072):
+                 stage_bytes: int = 64 << 20, max_batch_frames: int = 131072, zero_copy: bool = True):
         self.lib = _lib.load()
         ids = (C.c_int * len(gpu_ids))(*gpu_ids)
-        opts = _lib.SymrelayOpts(max_streams, pipeline_depth, stage_bytes, max_batch_frames, 0)
+        opts = _lib.SymrelayOpts(max_streams, pipeline_depth, stage_bytes, max_batch_frames, 0 if zero_copy else 1)
         self.n_gpus = len(gpu_ids)
         self.ctx = self.lib.symrelay_create(ids, len(gpu_ids), C.byref(opts))
         if not self.ctx:

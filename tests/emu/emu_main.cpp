@@ -41,7 +41,7 @@ extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *til
     pthread_t th[32];
     for (uint32_t l = 0; l < 32; l++) {
         jobs[l].warp = &warp;
-        jobs[l].args = SsArgs{(const SsDesc *)desc, (const SsTile *)tiles, n_tiles, in, out, (uint4 *)states, status};
+        jobs[l].args = SsArgs{(const SsDesc *)desc, (const SsTile *)tiles, n_tiles, in, out, (uint4 *)states, status, 0u};
         jobs[l].n_packed = n_tiles - n_bulk;
         jobs[l].n_bulk = n_bulk;
         jobs[l].lane = l;

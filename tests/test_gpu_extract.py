@@ -12,11 +12,13 @@ from oracle import libsodium as ls
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def relay():
+@pytest.fixture(scope="module", params=["zero_copy", "staged"])
+def relay(request):
+    """Both host paths: small pinned batches run zero-copy (kernels read/write the pinned host
+    arenas over PCIe); with zero_copy off the same batches go through the staged DMA pipeline."""
     import symmetry_b200 as sb
 
-    r = sb.SymRelay(gpu_ids=(0,), max_streams=1 << 16)
+    r = sb.SymRelay(gpu_ids=(0,), max_streams=1 << 16, zero_copy=request.param == "zero_copy")
     yield r
     r.close()
 

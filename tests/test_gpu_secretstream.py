@@ -269,6 +269,42 @@ def test_pipelined_submit_keeps_chain_order(relay):
             assert bytes(wires[k][w_offs[i] : w_offs[i] + lens[i] + 20]) == want, (k, i)
 
 
+def test_zero_copy_and_staged_paths_agree():
+    """The same pinned-arena batches through both host paths give identical wire bytes and states."""
+    import symmetry_b200 as sb
+
+    rng = random.Random(21)
+    lens = [64] * 300 + [rng.choice([0, 1, 17, 200, 1000, 1920, 1921, 5000]) for _ in range(200)]
+    n = len(lens)
+    keys = np.frombuffer(rng.randbytes(32 * n), dtype=np.uint8).reshape(n, 32)
+    hdrs = np.frombuffer(rng.randbytes(24 * n), dtype=np.uint8).reshape(n, 24)
+    p_offs, p_bytes = bu.plain_layout(lens)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    assert p_bytes + w_bytes < (1 << 20)
+    payload = [np.frombuffer(rng.randbytes(p_bytes), dtype=np.uint8) for _ in range(3)]
+    results = []
+    for zc in (True, False):
+        with sb.SymRelay(gpu_ids=(0,), max_streams=4096, zero_copy=zc) as r:
+            slots = r.open_streams(keys, hdrs, keys, hdrs)
+            plain, wire, back = r.alloc_pinned(p_bytes), r.alloc_pinned(w_bytes), r.alloc_pinned(p_bytes)
+            wires = []
+            for k in range(3):
+                plain[:] = payload[k]
+                st = r.batch_host(bu.make_descs(slots, lens, p_offs, w_offs), plain, wire)
+                assert (st == 0).all()
+                wires.append(bytes(b"".join(bytes(wire[o : o + L + 20]) for o, L in zip(w_offs, lens))))
+                st = r.batch_host(bu.make_descs(slots, lens, w_offs, p_offs, open_=True), wire, back)
+                assert (st == 0).all()
+                for o, L in zip(p_offs, lens):
+                    assert (back[o : o + L] == plain[o : o + L]).all()
+            results.append((wires, [r.export(int(s)) for s in slots[::37]]))
+    assert results[0] == results[1]
+    ref = ls.State(bytes(keys[0]), bytes(hdrs[0]))
+    for k in range(3):
+        w = ref.seal_frame(bytes(payload[k][p_offs[0] : p_offs[0] + lens[0]]))
+        assert results[0][0][k][: len(w)] == w
+
+
 def test_bad_arguments_are_rejected(relay):
     import symmetry_b200 as sb
 
