@@ -114,7 +114,34 @@ typedef struct symrelay_opts {
     uint64_t stage_bytes;     /* device staging bytes per stage and direction (default 64 MiB) */
     uint32_t max_batch_frames; /* descriptors per host batch (default 131072) */
     uint32_t flags;
+    /* per-frame front end (symrelay_submit_* / poll): */
+    uint32_t sched_flush_us;     /* deadline after a batch's first frame; 0 = flush on size / request only */
+    uint32_t sched_batches;      /* batch buffers per GPU (default pipeline_depth + 4) */
+    uint32_t sched_batch_frames; /* frames per batch (default 16384) */
+    uint32_t reserved;
+    uint64_t sched_arena_bytes;  /* pinned bytes per batch and direction (default 4 MiB) */
 } symrelay_opts;
+
+/* One finished frame, delivered by symrelay_poll in per-stream submit order.  `data` points into a
+ * pinned library arena that stays valid until symrelay_release(ticket): the wire frame (len = mlen+20)
+ * for a seal, the plaintext (len = mlen) for an open; NULL/0 when status is not OK. */
+typedef struct symrelay_completion {
+    int64_t ticket;
+    uint32_t slot;
+    uint32_t status;      /* SYMRELAY_ST_* | opened tag << 8 */
+    const uint8_t *data;
+    uint32_t len;
+    uint32_t flags;       /* SYMRELAY_F_OPEN / _EXTRACT as submitted */
+    const uint8_t *delta; /* extracted delta (F_EXTRACT seals), WTF-8 */
+    uint32_t delta_len;
+    uint32_t pad;
+    uint64_t latency_ns;  /* delivery time - submit time: the relay latency this library adds */
+} symrelay_completion;
+
+typedef struct symrelay_sched_stats_t {
+    uint64_t frames, batches, zero_copy_batches, staged_batches;
+    double mean_batch_fill, p50_us, p99_us, p999_us;
+} symrelay_sched_stats_t;
 
 typedef struct symrelay_ctx symrelay_ctx;
 
@@ -187,6 +214,28 @@ SYMRELAY_API int64_t symrelay_batch_submit(symrelay_ctx *ctx, const symrelay_des
                               uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
                               symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes);
 SYMRELAY_API int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket);
+
+/* ---- per-frame asynchronous front end: the shape of the reference's own calls ----
+ * symrelay_submit_seal  <-  `peer.write(chunk)` (src/provider.ts:97,103,125,234,248,260): copies the
+ *     chunk into the pinned ring and returns a ticket at once; SYMRELAY_EAGAIN when the ring is full
+ *     (= `write()` returned false: retry after a completion, the reference's 'drain', :250-252).
+ *     flags: SYMRELAY_F_EXTRACT and/or a tag in SYMRELAY_F_TAG_MASK.
+ * symrelay_submit_open  <-  secret-stream `_incoming` feeding `peer.on('data')` (:110,:174): `wire` is
+ *     one whole frame including its uint24-LE prefix; frames shorter than 17 bytes after the prefix or
+ *     with a wrong prefix complete with SYMRELAY_ST_TOO_SHORT (secret-stream destroys the stream).
+ * symrelay_flush closes the batch being filled; batches also close on size and on opts.sched_flush_us.
+ * symrelay_poll never blocks; symrelay_poll_wait blocks until the oldest in-flight batch is done.
+ * Completions of one stream arrive in submit order.  Every delivered completion must be released. */
+SYMRELAY_API int64_t symrelay_submit_seal(symrelay_ctx *ctx, uint32_t slot, const uint8_t *plain, uint32_t len,
+                                          uint32_t flags);
+SYMRELAY_API int64_t symrelay_submit_open(symrelay_ctx *ctx, uint32_t slot, const uint8_t *wire, uint32_t wire_len);
+SYMRELAY_API int symrelay_flush(symrelay_ctx *ctx);
+SYMRELAY_API int symrelay_poll(symrelay_ctx *ctx, symrelay_completion *out, int max);
+SYMRELAY_API int symrelay_poll_wait(symrelay_ctx *ctx, symrelay_completion *out, int max);
+SYMRELAY_API int symrelay_release(symrelay_ctx *ctx, int64_t ticket);
+/* frames/batches handled by the front end and the p50/p99/p99.9 of their added latency */
+SYMRELAY_API int symrelay_sched_stats(symrelay_ctx *ctx, symrelay_sched_stats_t *out);
+SYMRELAY_API int symrelay_sched_reset_stats(symrelay_ctx *ctx);
 
 /* Measurement aid (bench.py): sustained integer throughput of this GPU in
  * Tera-ops/s for ChaCha20's ADD:XOR:ROTATE 1:1:1 mix and for 32x32->64

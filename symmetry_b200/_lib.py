@@ -18,13 +18,29 @@ EXPORTS = (
     "symrelay_launch_count", "symrelay_stream_open", "symrelay_stream_open_batch", "symrelay_stream_close",
     "symrelay_stream_export", "symrelay_plan", "symrelay_desc_check", "symrelay_batch_device",
     "symrelay_batch_host", "symrelay_batch_submit", "symrelay_batch_wait", "symrelay_alloc_pinned",
-    "symrelay_free_pinned", "symrelay_probe_int_peak",
+    "symrelay_free_pinned", "symrelay_probe_int_peak", "symrelay_submit_seal", "symrelay_submit_open",
+    "symrelay_flush", "symrelay_poll", "symrelay_poll_wait", "symrelay_release", "symrelay_sched_stats",
+    "symrelay_sched_reset_stats",
 )
 
 
 class SymrelayOpts(C.Structure):
     _fields_ = [("max_streams", C.c_uint32), ("pipeline_depth", C.c_uint32), ("stage_bytes", C.c_uint64),
-                ("max_batch_frames", C.c_uint32), ("flags", C.c_uint32)]
+                ("max_batch_frames", C.c_uint32), ("flags", C.c_uint32), ("sched_flush_us", C.c_uint32),
+                ("sched_batches", C.c_uint32), ("sched_batch_frames", C.c_uint32), ("reserved", C.c_uint32),
+                ("sched_arena_bytes", C.c_uint64)]
+
+
+class SymrelayCompletion(C.Structure):
+    _fields_ = [("ticket", C.c_int64), ("slot", C.c_uint32), ("status", C.c_uint32), ("data", C.c_void_p),
+                ("len", C.c_uint32), ("flags", C.c_uint32), ("delta", C.c_void_p), ("delta_len", C.c_uint32),
+                ("pad", C.c_uint32), ("latency_ns", C.c_uint64)]
+
+
+class SymrelaySchedStats(C.Structure):
+    _fields_ = [("frames", C.c_uint64), ("batches", C.c_uint64), ("zero_copy_batches", C.c_uint64),
+                ("staged_batches", C.c_uint64), ("mean_batch_fill", C.c_double), ("p50_us", C.c_double),
+                ("p99_us", C.c_double), ("p999_us", C.c_double)]
 
 
 _lib = None
@@ -77,6 +93,21 @@ def load() -> C.CDLL:
     L.symrelay_free_pinned.argtypes = [vp, vp]
     L.symrelay_probe_int_peak.restype = ci
     L.symrelay_probe_int_peak.argtypes = [vp, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.symrelay_submit_seal.restype = i64
+    L.symrelay_submit_seal.argtypes = [vp, u32, vp, u32, u32]
+    L.symrelay_submit_open.restype = i64
+    L.symrelay_submit_open.argtypes = [vp, u32, vp, u32]
+    L.symrelay_flush.restype = ci
+    L.symrelay_flush.argtypes = [vp]
+    for name in ("symrelay_poll", "symrelay_poll_wait"):
+        getattr(L, name).restype = ci
+        getattr(L, name).argtypes = [vp, C.POINTER(SymrelayCompletion), ci]
+    L.symrelay_release.restype = ci
+    L.symrelay_release.argtypes = [vp, i64]
+    L.symrelay_sched_stats.restype = ci
+    L.symrelay_sched_stats.argtypes = [vp, C.POINTER(SymrelaySchedStats)]
+    L.symrelay_sched_reset_stats.restype = ci
+    L.symrelay_sched_reset_stats.argtypes = [vp]
     if L.symrelay_abi_version() != 1:
         raise ImportError("libsymrelay.so ABI version mismatch")
     _lib = L

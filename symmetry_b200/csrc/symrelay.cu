@@ -14,6 +14,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
+#include <deque>
 #include <mutex>
 #include <new>
 #include <string>
@@ -196,9 +198,12 @@ struct Shard {
 
 }  // namespace
 
+#include "scheduler.inc"
+
 struct symrelay_ctx {
     int n_gpus = 0;
     Shard shard[8];
+    Sched sched[8];
     symrelay_opts opts{};
     std::vector<uint8_t> slot_state;      // 0 free, 1 open
     std::vector<uint32_t> free_slots[8];  // per GPU (slot % n_gpus == gpu)
@@ -419,9 +424,11 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     return ctx;
 }
 
+static void sched_free(symrelay_ctx *ctx, int g);
+
 void symrelay_destroy(symrelay_ctx *ctx) {
     if (!ctx) return;
-    for (int g = 0; g < ctx->n_gpus; g++) shard_free(ctx->shard[g]);
+    for (int g = 0; g < ctx->n_gpus; g++) { shard_free(ctx->shard[g]); sched_free(ctx, g); }
     delete ctx;
 }
 
@@ -714,6 +721,8 @@ int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n
     if (t < 0) return (int)t;
     return symrelay_batch_wait(ctx, t);
 }
+
+#include "scheduler_impl.inc"
 
 int symrelay_probe_int_peak(symrelay_ctx *ctx, int gpu_index, double *arx_tops, double *imad_tops) {
     if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;

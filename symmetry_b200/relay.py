@@ -24,6 +24,7 @@ F_OPEN = 0x04000000
 F_EXTRACT = 0x08000000
 LEN_MASK = 0x00FFFFFF
 ST_OK, ST_BAD_MAC, ST_TOO_SHORT, ST_EXTRACT_THROW, ST_EXTRACT_UNSUPPORTED = 0, 1, 2, 3, 4
+EAGAIN = -11
 PROVIDER_DEFAULT, PROVIDER_OLLAMA, PROVIDER_LLAMACPP = 0, 1, 2
 STATEBYTES, HEADERBYTES, KEYBYTES, WIRE_OVERHEAD = 52, 24, 32, 20
 
@@ -58,10 +59,13 @@ class SymRelay:
     """One context = one state table per GPU + the batch pipeline."""
 
     def __init__(self, gpu_ids=(0,), max_streams: int = 65536, pipeline_depth: int = 4,
-                 stage_bytes: int = 64 << 20, max_batch_frames: int = 131072, zero_copy: bool = True):
+                 stage_bytes: int = 64 << 20, max_batch_frames: int = 131072, zero_copy: bool = True,
+                 flush_us: int = 0, sched_batches: int = 0, sched_batch_frames: int = 0, sched_arena_bytes: int = 0):
         self.lib = _lib.load()
         ids = (C.c_int * len(gpu_ids))(*gpu_ids)
-        opts = _lib.SymrelayOpts(max_streams, pipeline_depth, stage_bytes, max_batch_frames, 0 if zero_copy else 1)
+        opts = _lib.SymrelayOpts(max_streams, pipeline_depth, stage_bytes, max_batch_frames, 0 if zero_copy else 1,
+                                 flush_us, sched_batches, sched_batch_frames, 0, sched_arena_bytes)
+        self._cbuf = (_lib.SymrelayCompletion * 4096)()
         self.n_gpus = len(gpu_ids)
         self.ctx = self.lib.symrelay_create(ids, len(gpu_ids), C.byref(opts))
         if not self.ctx:
@@ -169,6 +173,43 @@ class SymRelay:
         buffers (raw device pointers), asynchronous on `stream`."""
         self._check(self.lib.symrelay_batch_device(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk, d_in,
                                                    d_out, d_status, d_delta or None, d_delta_arena or None, stream))
+
+    # -- per-frame front end (the shape of peer.write / peer.on('data')) ----------
+    def submit_seal(self, slot: int, chunk: bytes, extract: bool = False, tag: int = 0) -> int:
+        """`peer.write(chunk)`: returns a ticket, or raises RelayError(EAGAIN) when the ring is full."""
+        flags = (F_EXTRACT if extract else 0) | ((tag & 3) << 24)
+        return self._check(self.lib.symrelay_submit_seal(self.ctx, int(slot), bytes(chunk), len(chunk), flags))
+
+    def submit_open(self, slot: int, wire: bytes) -> int:
+        """One whole inbound wire frame (uint24-LE prefix included)."""
+        return self._check(self.lib.symrelay_submit_open(self.ctx, int(slot), bytes(wire), len(wire)))
+
+    def flush(self) -> None:
+        self._check(self.lib.symrelay_flush(self.ctx))
+
+    def poll(self, wait: bool = False, release: bool = True):
+        """Finished frames as dicts (data/delta copied out); releases them unless told otherwise."""
+        fn = self.lib.symrelay_poll_wait if wait else self.lib.symrelay_poll
+        n = self._check(fn(self.ctx, self._cbuf, len(self._cbuf)))
+        out = []
+        for i in range(n):
+            c = self._cbuf[i]
+            out.append({"ticket": c.ticket, "slot": c.slot, "status": c.status & 0xFF, "tag": (c.status >> 8) & 0xFF,
+                        "open": bool(c.flags & F_OPEN),
+                        "data": C.string_at(c.data, c.len) if c.data else b"",
+                        "delta": C.string_at(c.delta, c.delta_len) if c.delta else b"",
+                        "latency_ns": c.latency_ns})
+            if release:
+                self._check(self.lib.symrelay_release(self.ctx, c.ticket))
+        return out
+
+    def release(self, ticket: int) -> None:
+        self._check(self.lib.symrelay_release(self.ctx, ticket))
+
+    def sched_stats(self) -> dict:
+        st = _lib.SymrelaySchedStats()
+        self._check(self.lib.symrelay_sched_stats(self.ctx, C.byref(st)))
+        return {f: getattr(st, f) for f, _ in st._fields_}
 
     def probe_int_peak(self, gpu_index: int = 0):
         """(arx_tops, imad_tops): measured integer throughput, the ALU roofline denominators."""

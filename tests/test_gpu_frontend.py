@@ -1,0 +1,200 @@
+"""GPU tests of the per-frame front end (symrelay_submit_seal/_open/flush/poll/release) and of the
+host mirror of the reference's relay loop (provider.ts:195-275).  An "unmodified reference client"
+is modelled by a plain libsodium init_pull + pull loop with uint24 de-framing."""
+import json
+import random
+
+import numpy as np
+import pytest
+
+from oracle import extract as ex
+from oracle import libsodium as ls
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def relay():
+    import symmetry_b200 as sb
+
+    r = sb.SymRelay(gpu_ids=(0,), max_streams=8192, flush_us=0)
+    yield r
+    r.close()
+
+
+def test_per_stream_fifo_and_chain_with_interleaved_submits(relay):
+    rng = random.Random(1)
+    n = 200
+    keys = [rng.randbytes(32) for _ in range(n)]
+    hdrs = [rng.randbytes(24) for _ in range(n)]
+    slots = [relay.open_stream(k, h, k, h) for k, h in zip(keys, hdrs)]
+    refs = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+    import symmetry_b200 as sb
+
+    want = {}
+    got_order = {i: [] for i in range(n)}
+    n_eagain = 0
+
+    def collect(wait):
+        for c in relay.poll(wait=wait):
+            i, m = want.pop(c["ticket"])
+            assert c["status"] == 0 and not c["open"]
+            got_order[i].append((m, c["data"]))
+
+    def write(i, m):
+        nonlocal n_eagain
+        while True:
+            try:
+                want[relay.submit_seal(slots[i], m)] = (i, m)
+                return
+            except sb.RelayError as e:      # `peer.write()` returned false: await 'drain' (provider.ts:250-252)
+                assert e.code == sb.relay.EAGAIN
+                n_eagain += 1
+                collect(wait=True)
+
+    # several frames per stream submitted back to back: the front end must split them over batches
+    for rnd in range(5):
+        for i in rng.sample(range(n), n):
+            write(i, rng.randbytes(rng.choice([0, 1, 64, 200, 3000])))
+            if rng.random() < 0.3:
+                write(i, rng.randbytes(rng.choice([5, 64])))
+    relay.flush()
+    while want:
+        collect(wait=True)
+        relay.flush()
+    assert n_eagain > 0   # this pattern closes a batch per repeated stream and must hit back-pressure
+    for i in range(n):
+        for m, wire in got_order[i]:          # completions of a stream come in submit order = chain order
+            assert wire == refs[i].seal_frame(m)
+    st = relay.sched_stats()
+    assert st["frames"] >= 1000 and st["batches"] >= 2
+
+
+def test_open_side_and_host_rejections(relay):
+    rng = random.Random(2)
+    k, h = rng.randbytes(32), rng.randbytes(24)
+    slot = relay.open_stream(k, h, k, h)
+    peer = ls.State(k, h)   # the remote end's push state (same key/header as our rx)
+    frames = [peer.seal_frame(rng.randbytes(L)) for L in (0, 1, 63, 64, 500)]
+    msgs = []
+    mirror = ls.State(k, h)
+    for f in frames:
+        msgs.append(mirror.open_frame(f)[0])
+    tickets = []
+    for f in frames:
+        tickets.append(relay.submit_open(slot, f))
+        relay.flush()
+    tickets.append(relay.submit_open(slot, b"\x05\x00\x00abcde"))            # < 17 bytes after the prefix
+    tickets.append(relay.submit_open(slot, b"\x30\x00\x00" + bytes(30)))      # prefix disagrees with the length
+    forged = bytearray(peer.seal_frame(b"forged?"))
+    forged[10] ^= 1
+    tickets.append(relay.submit_open(slot, bytes(forged)))
+    relay.flush()
+    res = {}
+    while len(res) < len(tickets):
+        for c in relay.poll(wait=True):
+            res[c["ticket"]] = c
+    for t, m in zip(tickets[:5], msgs):
+        assert res[t]["status"] == 0 and res[t]["open"] and res[t]["data"] == m
+    assert res[tickets[5]]["status"] == 2 and res[tickets[6]]["status"] == 2
+    assert res[tickets[7]]["status"] == 1 and res[tickets[7]]["data"] == b""
+    assert relay.export(slot)[1] == mirror.raw   # rejected and forged frames left the rx state alone
+
+
+def test_ring_full_returns_eagain_then_drains():
+    import symmetry_b200 as sb
+
+    with sb.SymRelay(gpu_ids=(0,), max_streams=64, sched_batches=2, sched_batch_frames=4) as r:
+        k, h = bytes(range(32)), bytes(24)
+        slots = [r.open_stream(k, h, None, None) for _ in range(16)]
+        accepted, refused = [], 0
+        for s in slots:
+            try:
+                accepted.append(r.submit_seal(s, b"x" * 40))
+            except sb.RelayError as e:
+                assert e.code == sb.relay.EAGAIN
+                refused += 1
+        assert refused > 0 and len(accepted) >= 4     # `write()` false: the loop must await 'drain'
+        r.flush()
+        done = 0
+        while done < len(accepted):
+            done += len(r.poll(wait=True))
+            r.flush()
+        t = r.submit_seal(slots[-1], b"after drain")   # space again
+        r.flush()
+        assert [c["status"] for c in r.poll(wait=True)] == [0] and t > 0
+
+
+def test_relay_loop_mirror_against_reference_semantics(relay):
+    """provider.ts:195-275 for many connections: preamble, chunks (+delta), trailer; a TypeError chunk
+    ends that connection's relay without a trailer; an unmodified client decrypts what was sent."""
+    import symmetry_b200 as sb
+    from symmetry_b200 import provider, synth
+
+    rng = random.Random(3)
+    n = 300
+    keys = [rng.randbytes(32) for _ in range(n)]
+    hdrs = [rng.randbytes(24) for _ in range(n)]
+    peers = []
+    for i in range(n):
+        slot = relay.open_stream(keys[i], hdrs[i], None, None, provider=sb.PROVIDER_OLLAMA)
+        chunks = synth.chat_chunks(rng.randrange(1, 9), seed=9, stream_id=i)
+        if i % 10 == 3:   # OpenAI usage chunk mid-stream: `"choices":[]` -> TypeError in the reference
+            chunks.insert(rng.randrange(len(chunks)), b'data: {"choices":[],"usage":{"total_tokens":3}}\n\n')
+        if i % 10 == 5:   # a value shape the GPU hands back to the host helper
+            chunks.insert(1, b'data: {"choices":[{"delta":{"content":1e21}}]}\n\n')
+        peers.append(provider.PeerRelayState(slot, f"key-{i}", chunks))
+
+    def host_extract(p, chunk):   # stands in for the reference's own JS helper
+        code, delta = ex.extract("ollama", chunk)
+        return code == ex.OK, delta
+
+    provider.handle_inference_requests(relay, peers, host_extract=host_extract)
+    for i, p in enumerate(peers):
+        client = ls.State(keys[i], hdrs[i])                  # unmodified client: init_pull + pull loop
+        got = [client.open_frame(w) for w in p.wire]
+        assert all(g is not None and g[1] == 0 for g in got)
+        plain = [g[0] for g in got]
+        # what the reference would have done, restated with the oracle
+        want_frames = [json.dumps({"symmetryEmitterKey": f"key-{i}"}, separators=(",", ":")).encode()]
+        want_completion, aborted = b"", False
+        for ch in p.frames[1:-1]:
+            code, delta = ex.extract("ollama", ch)
+            if code == ex.THROW:
+                aborted = True
+                break
+            want_completion += delta
+            want_frames.append(ch)
+        if not aborted:
+            want_frames.append(provider.createMessage("inferenceEnded", f"key-{i}").encode())
+        assert p.aborted == aborted
+        assert plain == want_frames
+        assert p.completion == want_completion
+        if i % 10 == 5 and not aborted:
+            assert p.unsupported == [2]
+    assert any(p.aborted for p in peers) and any(not p.aborted for p in peers)
+
+
+def test_deadline_flush_and_latency_stats():
+    import time
+
+    import symmetry_b200 as sb
+
+    with sb.SymRelay(gpu_ids=(0,), max_streams=4096, flush_us=100) as r:
+        k, h = bytes(range(32)), bytes(24)
+        slots = [r.open_stream(k, h, None, None) for _ in range(1000)]
+        got = 0
+        for s in slots:
+            while True:
+                try:
+                    r.submit_seal(s, b"tok " * 16)
+                    break
+                except sb.RelayError as e:
+                    assert e.code == sb.relay.EAGAIN
+                    got += len(r.poll())
+        deadline = time.time() + 5
+        while got < 1000 and time.time() < deadline:   # no explicit flush: the deadline closes batches
+            got += len(r.poll())
+        assert got == 1000
+        st = r.sched_stats()
+        assert st["frames"] == 1000 and 0 < st["p50_us"] < 50000 and st["p99_us"] >= st["p50_us"]
