@@ -489,6 +489,19 @@ def run_ours(args):
                          f"oracle/cpu_bench.c; {cpu_model()}",
                "single_core_value": n * max(1, cpu_steps // threads) / sec1}
 
+    # ---------------- p50 added relay latency (the metric's third figure), rank 0 at N=1 ----------
+    latency = None
+    if world == 1 and not args.no_latency:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import latency_bench
+
+            relay.close()
+            relay = None
+            latency = latency_bench.run(streams=65536, rate=2e6, nbytes=200, seconds=1.0, flush_us=100)
+        except Exception as e:  # the headline numbers do not depend on it
+            latency = {"error": repr(e)}
+
     frames_per_step = n                                  # sealed frames; each step also opens n frames
     dev_s = dev_ms * 1e-3
     value = n_gpus * frames_per_step * K / dev_s
@@ -545,8 +558,11 @@ def run_ours(args):
     }
     if cpu:
         line["cpu_baseline"] = cpu
+    if latency:
+        line["latency"] = latency
     print(json.dumps(line), flush=True)
-    relay.close()
+    if relay is not None:
+        relay.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -681,6 +697,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-latency", action="store_true", help="skip the p50 added-latency leg (64k streams, Poisson)")
     ap.add_argument("--py-e2e", action="store_true", help="drive the e2e loop from Python instead of tools/e2e_driver.c")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (huge workloads)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step directly (no CUDA graph)")

@@ -62,9 +62,10 @@ DRIVER_SO = os.path.join(os.path.dirname(HERE), "tools", "libe2e_driver.so")
 
 def build_driver(force: bool = False) -> str:
     """tools/e2e_driver.c: a plain-C caller of the public ABI (no CUDA in it), linked against libsymrelay.so."""
-    src = os.path.join(os.path.dirname(HERE), "tools", "e2e_driver.c")
-    if force or not os.path.exists(DRIVER_SO) or os.path.getmtime(src) > os.path.getmtime(DRIVER_SO):
-        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", DRIVER_SO, src, "-L" + HERE, "-lsymrelay",
+    tools = os.path.join(os.path.dirname(HERE), "tools")
+    srcs = [os.path.join(tools, "e2e_driver.c"), os.path.join(tools, "latency_driver.c")]
+    if force or not os.path.exists(DRIVER_SO) or any(os.path.getmtime(s) > os.path.getmtime(DRIVER_SO) for s in srcs):
+        subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", DRIVER_SO] + srcs + ["-L" + HERE, "-lsymrelay", "-lm",
                         "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/../symmetry_b200"], check=True)
     return DRIVER_SO
 
