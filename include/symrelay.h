@@ -56,6 +56,7 @@ extern "C" {
 #define SYMRELAY_ST_TOO_SHORT 2u          /* wire frame shorter than 17 bytes after the prefix */
 #define SYMRELAY_ST_EXTRACT_THROW 3u      /* the reference would throw a TypeError here (utils.ts:38-50) */
 #define SYMRELAY_ST_EXTRACT_UNSUPPORTED 4u /* value shape outside the GPU extractor's domain: use the JS helper */
+#define SYMRELAY_ST_RETRY 5u /* frame of a run behind a failed or REKEY frame: not processed, resubmit it */
 #define SYMRELAY_ST_PENDING 0xffu
 #define SYMRELAY_STATUS_CODE(s) ((s) & 0xffu)
 #define SYMRELAY_STATUS_TAG(s) (((s) >> 8) & 0xffu)
@@ -65,6 +66,9 @@ extern "C" {
 #define SYMRELAY_F_TAG_SHIFT 24
 #define SYMRELAY_F_OPEN 0x04000000u     /* frame is an inbound wire frame to open (else: seal) */
 #define SYMRELAY_F_EXTRACT 0x08000000u  /* also run the SSE `data:` test + delta extraction on the plaintext */
+#define SYMRELAY_F_RUN 0x10000000u      /* open frame that belongs to a run: consecutive descriptors of one slot, all
+                                          F_OPEN|F_RUN, are frames queued behind each other on that stream (at most
+                                          64); they are opened in parallel from the MACs on the wire */
 #define SYMRELAY_LEN_MASK 0x00ffffffu
 
 /* provider kinds: src/constants.ts:22-29 (lmstudio / oobabooga / unknown take the default branch) */
@@ -84,7 +88,8 @@ enum symrelay_provider {
  *   open: wire frame = in  + in_off  (in_off  % 16 == 12), mlen + 20 bytes, len = mlen
  *         plaintext  -> out + out_off (out_off % 16 == 0)
  * A batch holds at most ONE frame per (slot, direction): frames of one stream
- * are MAC-chained and go into consecutive batches.
+ * are MAC-chained and go into consecutive batches
+ * -- except inbound runs marked SYMRELAY_F_RUN, whose chain is on the wire.
  * Arenas must be readable up to the next 16-byte boundary past each frame.
  */
 typedef struct symrelay_desc {
@@ -197,6 +202,15 @@ SYMRELAY_API int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const s
                           const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
                           const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, symrelay_delta *d_delta,
                           uint8_t *d_delta_arena, void *cuda_stream);
+/* symrelay_batch_device for batches that contain SYMRELAY_F_RUN frames: the caller also passes
+ * SCRATCH device memory (16-byte aligned, 16 bytes per descriptor) that the nonce pre-pass fills
+ * and the tile kernels read; its contents are meaningless afterwards.  Replaces a loop of
+ * `Pull.next` calls over the frames secret-stream's `_onrawdata` split out of one UDX segment. */
+SYMRELAY_API int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
+                                            const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
+                                            const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, void *d_scratch,
+                                            uint64_t scratch_bytes, void *cuda_stream);
+
 /* HOST buffers (pinned from symrelay_alloc_pinned for full speed, pageable
  * accepted): plans, copies in, launches, copies out, waits.  Batches of up to
  * 1 MiB (in + out) whose arenas came from symrelay_alloc_pinned skip the copies:

@@ -61,8 +61,10 @@ SS_DEV void ss_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 #define SS_F_OPEN 0x04000000u
 #define SS_F_EXTRACT 0x08000000u
+#define SS_F_RUN 0x10000000u   // open frame that is part of a run of queued frames of one stream (see ss_runs.cuh)
 #define SS_ST_OK 0u
 #define SS_ST_BAD_MAC 1u
+#define SS_ST_RETRY 5u
 
 struct SsDesc {
     uint32_t slot, in_off, out_off, len_flags;
@@ -79,6 +81,7 @@ struct SsArgs {
     uint4 *states;  // [slot][dir]: 3 x uint4 = k[0..3] | k[4..7] | {frame counter, inonce0, inonce1, meta}
     uint32_t *status;
     uint32_t flags;
+    const uint4 *run_nonce;   // scratch: per-descriptor nonce for SS_F_RUN frames (written by ss_run_nonce_kernel)
 };
 
 // ---------------------------------------------------------------- ChaCha20 --
@@ -377,6 +380,13 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
         k[4] = s1.x; k[5] = s1.y; k[6] = s1.z; k[7] = s1.w;
         nn[0] = s2.x; nn[1] = s2.y; nn[2] = s2.z; meta = s2.w;
     }
+    // A frame of a run uses the nonce the pre-pass derived from the MACs of the frames queued before
+    // it (SURVEY 8(a) "parallel open"); the stream state itself is advanced later by the commit pass.
+    const bool in_run = (lf & SS_F_RUN) != 0 && is_open;
+    if (valid && in_run) {
+        const uint4 o = a.run_nonce[tile.first + f];
+        nn[0] = o.x; nn[1] = o.y; nn[2] = o.z;
+    }
 
     if (!early) {
         if (!BULK) {
@@ -586,7 +596,9 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
 
     if (leader) {
         const uint32_t frame_idx = tile.first + f;
-        if (ok) {
+        if (ok && in_run) {
+            a.status[frame_idx] = SS_ST_OK | (tag_b1 << 8);   // state untouched: ss_run_commit_kernel owns it
+        } else if (ok) {
             const uint32_t tag = is_open ? tag_b1 : ((lf >> 24) & 3u);
             nn[1] ^= mac[0];
             nn[2] ^= mac[1];

@@ -25,6 +25,7 @@
 #include "plan.h"
 #include "ss_core.cuh"
 #include "ss_extract.cuh"
+#include "ss_runs.cuh"
 
 static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) == sizeof(SsTile), "ABI layout");
 
@@ -45,6 +46,17 @@ __global__ void __launch_bounds__(128, SS_BULK_MIN_BLOCKS) ss_bulk_kernel(SsArgs
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
     ss_process_tile<true>(a, warp);
+}
+
+// Runs of queued frames of one stream (see ss_runs.cuh): nonce pre-pass and state commit.
+// run_nonce is SCRATCH memory: 16 bytes per descriptor of the batch, valid only between these passes.
+__global__ void __launch_bounds__(128) ss_run_nonce_kernel(const SsDesc *desc, uint32_t n, const uint8_t *in,
+                                                           const uint4 *states, uint4 *run_nonce) {
+    ss_run_nonce(desc, n, in, states, run_nonce, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__global__ void __launch_bounds__(128) ss_run_commit_kernel(const SsDesc *desc, uint32_t n, const uint8_t *in,
+                                                            uint4 *states, uint32_t *status) {
+    ss_run_commit(desc, n, in, states, status, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // Delta extraction, one thread per frame that carries
@@ -177,6 +189,7 @@ struct Stage {
     uint32_t *d_status = nullptr, *h_status = nullptr;
     symrelay_delta *d_delta = nullptr, *h_delta = nullptr;
     uint8_t *d_delta_arena = nullptr;   // allocated on first use (extraction batches only)
+    uint4 *d_run_nonce = nullptr;       // scratch for runs, allocated on first use
     symrelay_delta *user_delta = nullptr;
     cudaEvent_t ev_in = nullptr, ev_k = nullptr, ev_out = nullptr;
     // in-flight batch bookkeeping
@@ -277,8 +290,14 @@ static cudaError_t launch_pdl(K kernel, uint32_t grid, uint32_t threads, cudaStr
 static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t n, const symrelay_tile *d_tiles,
                         uint32_t n_tiles, uint32_t n_bulk, const uint8_t *d_in, uint8_t *d_out, uint4 *d_states,
                         uint32_t *d_status, symrelay_delta *d_delta, uint8_t *d_delta_arena, cudaStream_t stream,
-                        uint32_t arg_flags = 0) {
+                        uint32_t arg_flags = 0, uint4 *d_run_nonce = nullptr) {
     const uint32_t n_packed = n_tiles - n_bulk;
+    if (d_run_nonce) {
+        ss_run_nonce_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
+                                                                 d_states, d_run_nonce);
+        ctx->launches++;
+        arg_flags &= ~SS_ARG_INPUT_INDEPENDENT;   // the tile kernel now depends on the pre-pass
+    }
     if (d_delta && d_delta_arena) {
         ss_extract_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
                                                                d_states, d_status, d_delta, d_delta_arena);
@@ -291,6 +310,7 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     a.states = d_states;
     a.status = d_status;
     a.flags = arg_flags;
+    a.run_nonce = d_run_nonce;
     // PDL only where it was measured to help: the host zero-copy path (16.2 -> 10.9 us per C2 batch).
     // Device-resident launches replayed from a CUDA graph got slower with it (6.3 -> 10.3 us).
     const bool pdl = ctx->pdl && (arg_flags & SS_ARG_INPUT_INDEPENDENT);
@@ -308,6 +328,11 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
         const uint32_t threads = n_bulk <= 148u * 8u ? 32u : 128u;
         const uint32_t wpb = threads / 32u;
         CU(ctx, launch_pdl(ss_bulk_kernel, (n_bulk + wpb - 1) / wpb, threads, stream, pdl, a));
+        ctx->launches++;
+    }
+    if (d_run_nonce) {
+        ss_run_commit_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
+                                                                  d_states, d_status);
         ctx->launches++;
     }
     CU(ctx, cudaGetLastError());
@@ -372,7 +397,7 @@ static void shard_free(Shard &sh) {
     for (Stage &st : sh.stages) {
         cudaFree(st.d_ctrl); cudaFreeHost(st.h_ctrl); cudaFree(st.d_in); cudaFree(st.d_out);
         cudaFree(st.d_status); cudaFreeHost(st.h_status);
-        cudaFree(st.d_delta); cudaFreeHost(st.h_delta); cudaFree(st.d_delta_arena);
+        cudaFree(st.d_delta); cudaFreeHost(st.h_delta); cudaFree(st.d_delta_arena); cudaFree(st.d_run_nonce);
         if (st.ev_in) cudaEventDestroy(st.ev_in);
         if (st.ev_k) cudaEventDestroy(st.ev_k);
         if (st.ev_out) cudaEventDestroy(st.ev_out);
@@ -575,6 +600,22 @@ int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const symrelay_desc 
                         d_delta_arena, (cudaStream_t)cuda_stream);
 }
 
+int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
+                               const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
+                               const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, void *d_scratch,
+                               uint64_t scratch_bytes, void *cuda_stream) {
+    if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
+    if (n == 0 || n_tiles == 0) return 0;
+    if (!d_desc || !d_tiles || !d_in || !d_out || !d_status || !d_scratch || n_bulk_tiles > n_tiles)
+        return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_device_runs: null pointer or bad tile counts");
+    if (scratch_bytes < (uint64_t)n * 16u || (reinterpret_cast<uintptr_t>(d_scratch) & 15u))
+        return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_device_runs: scratch must be 16-byte aligned and hold 16 bytes per descriptor");
+    Shard &sh = ctx->shard[gpu_index];
+    CU(ctx, set_device(sh.dev));
+    return launch_tiles(ctx, d_desc, n, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status, nullptr,
+                        nullptr, (cudaStream_t)cuda_stream, 0u, reinterpret_cast<uint4 *>(d_scratch));
+}
+
 static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st) {
     if (!st.busy) return 0;
     CU(ctx, set_device(sh.dev));
@@ -606,10 +647,11 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     uint32_t n_bulk = 0;
     const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk);
     if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
-    bool extract = false;
+    bool extract = false, runs = false;
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t mlen = desc[i].len_flags & SYMRELAY_LEN_MASK;
         const bool op = desc[i].len_flags & SYMRELAY_F_OPEN;
+        if (op && (desc[i].len_flags & SYMRELAY_F_RUN)) runs = true;
         if ((desc[i].len_flags & SYMRELAY_F_EXTRACT) && !op) {
             extract = true;
             const uint64_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
@@ -625,6 +667,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (extract && (!delta || !delta_arena))
         return fail(ctx, SYMRELAY_EINVAL, "SYMRELAY_F_EXTRACT needs delta and delta_arena");
     if (extract && !st.d_delta_arena) CU(ctx, cudaMalloc(&st.d_delta_arena, ctx->opts.stage_bytes));
+    if (runs && !st.d_run_nonce) CU(ctx, cudaMalloc(&st.d_run_nonce, (size_t)ctx->opts.max_batch_frames * sizeof(uint4)));
     const size_t tiles_bytes = align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
     memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
     const size_t ctrl_bytes = tiles_bytes + (size_t)n * sizeof(symrelay_desc);
@@ -650,7 +693,8 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(k_ctrl + tiles_bytes), n,
                           reinterpret_cast<const symrelay_tile *>(k_ctrl), (uint32_t)n_tiles, n_bulk, k_in, out,
                           sh.d_states, st.h_status, extract ? st.h_delta : nullptr, extract ? delta_arena : nullptr,
-                          sh.s_k, (ctx->zc_mode == 1 && !extract) ? SS_ARG_INPUT_INDEPENDENT : 0u);
+                          sh.s_k, (ctx->zc_mode == 1 && !extract) ? SS_ARG_INPUT_INDEPENDENT : 0u,
+                          runs ? st.d_run_nonce : nullptr);
         if (rc) return rc;
         CU(ctx, cudaEventRecord(st.ev_out, sh.s_k));
         ctx->zero_copy_batches++;
@@ -669,7 +713,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(st.d_ctrl + tiles_bytes), n,
                       reinterpret_cast<const symrelay_tile *>(st.d_ctrl), (uint32_t)n_tiles, n_bulk, st.d_in, st.d_out,
                       sh.d_states, st.d_status, extract ? st.d_delta : nullptr, extract ? st.d_delta_arena : nullptr,
-                      sh.s_k);
+                      sh.s_k, 0u, runs ? st.d_run_nonce : nullptr);
     if (rc) return rc;
     CU(ctx, cudaEventRecord(st.ev_k, sh.s_k));
     CU(ctx, cudaStreamWaitEvent(sh.s_out, st.ev_k, 0));

@@ -22,8 +22,9 @@ DELTA_DTYPE = np.dtype([("off", "<u4"), ("len", "<u4")])
 
 F_OPEN = 0x04000000
 F_EXTRACT = 0x08000000
+F_RUN = 0x10000000
 LEN_MASK = 0x00FFFFFF
-ST_OK, ST_BAD_MAC, ST_TOO_SHORT, ST_EXTRACT_THROW, ST_EXTRACT_UNSUPPORTED = 0, 1, 2, 3, 4
+ST_OK, ST_BAD_MAC, ST_TOO_SHORT, ST_EXTRACT_THROW, ST_EXTRACT_UNSUPPORTED, ST_RETRY = 0, 1, 2, 3, 4, 5
 EAGAIN = -11
 PROVIDER_DEFAULT, PROVIDER_OLLAMA, PROVIDER_LLAMACPP = 0, 1, 2
 STATEBYTES, HEADERBYTES, KEYBYTES, WIRE_OVERHEAD = 52, 24, 32, 20
@@ -216,6 +217,12 @@ class SymRelay:
         a, m = C.c_double(0), C.c_double(0)
         self._check(self.lib.symrelay_probe_int_peak(self.ctx, gpu_index, C.byref(a), C.byref(m)))
         return a.value, m.value
+
+    def batch_device_runs(self, d_desc: int, n: int, d_tiles: int, n_tiles: int, n_bulk: int, d_in: int, d_out: int,
+                          d_status: int, d_scratch: int, scratch_bytes: int, stream: int = 0, gpu_index: int = 0):
+        """batch_device for batches with F_RUN frames; d_scratch: 16 bytes per descriptor of device scratch."""
+        self._check(self.lib.symrelay_batch_device_runs(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk, d_in,
+                                                        d_out, d_status, d_scratch, scratch_bytes, stream))
 
     def alloc_pinned(self, nbytes: int) -> np.ndarray:
         """Pinned host arena as a uint8 numpy view (freed with the context)."""

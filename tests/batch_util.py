@@ -8,6 +8,7 @@ import numpy as np
 
 F_OPEN = 0x04000000
 F_EXTRACT = 0x08000000
+F_RUN = 0x10000000
 
 DESC_DTYPE = np.dtype([("slot", "<u4"), ("in_off", "<u4"), ("out_off", "<u4"), ("len_flags", "<u4")])
 TILE_DTYPE = np.dtype([("first", "<u4"), ("n_kind", "<u4")])
@@ -42,7 +43,7 @@ def wire_layout(lens):
     return offs, cur
 
 
-def make_descs(slots, lens, in_offs, out_offs, *, open_=False, tags=None, extract=False) -> np.ndarray:
+def make_descs(slots, lens, in_offs, out_offs, *, open_=False, tags=None, extract=False, run=False) -> np.ndarray:
     d = np.zeros(len(lens), dtype=DESC_DTYPE)
     d["slot"] = slots
     d["in_off"] = in_offs
@@ -54,6 +55,8 @@ def make_descs(slots, lens, in_offs, out_offs, *, open_=False, tags=None, extrac
         lf |= F_OPEN
     if extract:
         lf |= F_EXTRACT
+    if run:
+        lf |= F_RUN
     d["len_flags"] = lf
     return d
 

@@ -8,6 +8,9 @@
 #include "../../symmetry_b200/csrc/plan.h"
 #include "../../symmetry_b200/csrc/ss_core.cuh"
 #include "../../symmetry_b200/csrc/ss_extract.cuh"
+#include "../../symmetry_b200/csrc/ss_runs.cuh"
+
+#include <vector>
 
 thread_local uint32_t emu_lane_id;
 thread_local EmuWarp *emu_warp;
@@ -35,13 +38,22 @@ extern "C" int64_t emu_plan(const symrelay_desc *desc, uint32_t n, symrelay_tile
 
 extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *tiles, uint32_t n_tiles, uint32_t n_bulk,
                              const uint8_t *in, uint8_t *out, void *states, uint32_t *status) {
+    // runs: nonce pre-pass (thread-local code, run serially here), tiles, then the commit pass
+    uint32_t n_desc = 0;
+    for (uint32_t t = 0; t < n_tiles; t++) {
+        const uint32_t end = tiles[t].first + (tiles[t].n_kind & 0xffffu);
+        if (end > n_desc) n_desc = end;
+    }
+    std::vector<uint4> run_nonce(n_desc ? n_desc : 1);
+    for (uint32_t i = 0; i < n_desc; i++)
+        ss_run_nonce((const SsDesc *)desc, n_desc, in, (const uint4 *)states, run_nonce.data(), i);
     EmuWarp warp;
     pthread_barrier_init(&warp.bar, nullptr, 32);
     Job jobs[32];
     pthread_t th[32];
     for (uint32_t l = 0; l < 32; l++) {
         jobs[l].warp = &warp;
-        jobs[l].args = SsArgs{(const SsDesc *)desc, (const SsTile *)tiles, n_tiles, in, out, (uint4 *)states, status, 0u};
+        jobs[l].args = SsArgs{(const SsDesc *)desc, (const SsTile *)tiles, n_tiles, in, out, (uint4 *)states, status, 0u, run_nonce.data()};
         jobs[l].n_packed = n_tiles - n_bulk;
         jobs[l].n_bulk = n_bulk;
         jobs[l].lane = l;
@@ -49,6 +61,7 @@ extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *til
     }
     for (uint32_t l = 0; l < 32; l++) pthread_join(th[l], nullptr);
     pthread_barrier_destroy(&warp.bar);
+    for (uint32_t i = 0; i < n_desc; i++) ss_run_commit((const SsDesc *)desc, n_desc, in, (uint4 *)states, status, i);
     return 0;
 }
 

@@ -116,3 +116,81 @@ def golden_chains(be, ss_vectors, max_frames=10**9):
             assert be.export(slot)[1].hex() == fr["state_after"]
             n += 1
     return n
+
+
+def run_open_scenario(be, seed=0, n_streams=24):
+    """Runs: several frames queued on one stream are opened in ONE batch (SYMRELAY_F_RUN).  Expected
+    behaviour = that many sequential libsodium pulls: a forged frame kills the stream there (frames
+    behind it: RETRY, state advanced only over the verified prefix), a REKEY tag or counter wrap is
+    honoured (frames behind it: RETRY, and they open fine when resubmitted)."""
+    rng = random.Random(seed)
+    keys = [rng.randbytes(32) for _ in range(n_streams)]
+    hdrs = [rng.randbytes(24) for _ in range(n_streams)]
+    senders = [ls.State(k, h) for k, h in zip(keys, hdrs)]      # the remote peers
+    mirrors = [ls.State(k, h) for k, h in zip(keys, hdrs)]      # what sequential pulls would do
+    slots = be.open_streams([s.raw for s in senders], [s.raw for s in mirrors])
+    plan = []   # (stream, [(msg, tag, forged)])
+    for i in range(n_streams):
+        k = rng.choice([1, 2, 3, 5, 9, 20])
+        frames = []
+        for j in range(k):
+            L = rng.choice([0, 1, 17, 64, 200, 1000, 1920, 1921, 5000])
+            frames.append([rng.randbytes(L), 0, False])
+        if i % 6 == 1 and k > 2:
+            frames[k // 2][2] = True            # forged in the middle
+        if i % 6 == 2 and k > 2:
+            frames[k // 2][1] = 2               # REKEY tag in the middle
+        if i % 6 == 3:
+            frames[0][1] = 3                    # FINAL (rekeys too: tag & 2)
+        plan.append((i, frames))
+    # wire bytes
+    wires, lens, owner = [], [], []
+    for i, frames in plan:
+        for m, tag, forged in frames:
+            w = bytearray(senders[i].seal_frame(m, tag))
+            if forged:
+                w[3 + rng.randrange(len(m) + 1)] ^= 0x40     # tag byte or ciphertext: the MAC bytes stay genuine
+            wires.append(bytes(w)); lens.append(len(m)); owner.append(i)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    p_offs, p_bytes = bu.plain_layout(lens)
+    arena = bu.aligned_zeros(w_bytes)
+    for w, o in zip(wires, w_offs):
+        arena[o : o + len(w)] = np.frombuffer(w, dtype=np.uint8)
+    out = bu.aligned_zeros(p_bytes)
+    d = bu.make_descs([slots[i] for i in owner], lens, w_offs, p_offs, open_=True, run=True)
+    status = be.run(d, arena, out)
+    idx = 0
+    retry = []
+    for i, frames in plan:
+        alive = True
+        for m, tag, forged in frames:
+            code = int(status[idx]) & 0xFF
+            if not alive:
+                assert code == 5, (i, idx, code)            # RETRY
+                retry.append(idx)
+            elif forged:
+                assert code == 1, (i, idx, code)            # BAD_MAC, as pull would report
+                alive = False
+            else:
+                assert int(status[idx]) == (tag << 8), (i, idx, status[idx])
+                assert bytes(out[p_offs[idx] : p_offs[idx] + len(m)]) == m
+                assert mirrors[i].open_frame(wires[idx]) == (m, tag)
+                if tag & 2:
+                    alive = False                           # speculation ends at a rekey
+            idx += 1
+        assert be.export(slots[i])[1] == mirrors[i].raw, f"rx state of stream {i}"
+    # resubmit what was held back behind a REKEY: it must now open (streams with a forged frame stay dead)
+    dead = {i for i, frames in plan if any(f[2] for f in frames)}
+    again = [j for j in retry if owner[j] not in dead]
+    if again:
+        d2 = bu.make_descs([slots[owner[j]] for j in again], [lens[j] for j in again], [w_offs[j] for j in again],
+                           [p_offs[j] for j in again], open_=True, run=True)
+        st2 = be.run(d2, arena, out)
+        for k, j in enumerate(again):
+            i = owner[j]
+            got = mirrors[i].open_frame(wires[j])
+            assert got is not None and int(st2[k]) == (got[1] << 8)
+            assert bytes(out[p_offs[j] : p_offs[j] + lens[j]]) == got[0]
+        for i in {owner[j] for j in again}:
+            assert be.export(slots[i])[1] == mirrors[i].raw
+    return len(wires), len(retry)

@@ -117,3 +117,8 @@ def test_mixed_ragged_with_forgeries(be):
 
 def test_golden_chains_through_emulated_kernel(be, ss_vectors):
     assert pc.golden_chains(be, ss_vectors[:3], max_frames=40) >= 80
+
+
+def test_runs_of_queued_frames(be):
+    n, n_retry = pc.run_open_scenario(be, seed=3)
+    assert n > 60 and n_retry > 0

@@ -55,9 +55,15 @@ class GpuDeviceBackend(GpuBackend):
         t_in = torch.from_numpy(np.ascontiguousarray(arena_in)).to(dev)
         t_out = torch.from_numpy(np.ascontiguousarray(arena_out)).to(dev)
         t_status = torch.full((len(descs),), 0xFF, dtype=torch.int32, device=dev)
-        self.relay.batch_device(t_desc.data_ptr(), len(descs), t_tiles.data_ptr(), len(tiles), n_bulk,
-                                t_in.data_ptr(), t_out.data_ptr(), t_status.data_ptr(),
-                                stream=torch.cuda.current_stream().cuda_stream)
+        if (descs["len_flags"] & bu.F_RUN).any():
+            scratch = torch.empty(16 * len(descs), dtype=torch.uint8, device=dev)   # caller-provided scratch
+            self.relay.batch_device_runs(t_desc.data_ptr(), len(descs), t_tiles.data_ptr(), len(tiles), n_bulk,
+                                         t_in.data_ptr(), t_out.data_ptr(), t_status.data_ptr(), scratch.data_ptr(),
+                                         scratch.numel(), stream=torch.cuda.current_stream().cuda_stream)
+        else:
+            self.relay.batch_device(t_desc.data_ptr(), len(descs), t_tiles.data_ptr(), len(tiles), n_bulk,
+                                    t_in.data_ptr(), t_out.data_ptr(), t_status.data_ptr(),
+                                    stream=torch.cuda.current_stream().cuda_stream)
         torch.cuda.synchronize()
         arena_out[:] = t_out.cpu().numpy()
         return t_status.cpu().numpy().astype(np.uint32)
@@ -103,6 +109,17 @@ def dbe(relay):
 def test_device_path_touches_only_its_frames(dbe):
     lens = list(range(0, 200)) + [1919, 1920, 1921, 2048, 4097, 65537]
     pc.seal_open_roundtrip(dbe, lens, [i % 4 for i in range(len(lens))], seed=12, chain=2, corrupt=(3, 64, 200, 205))
+
+
+def test_runs_of_queued_frames_host_path(be):
+    for seed in (3, 4):
+        n, n_retry = pc.run_open_scenario(be, seed=seed, n_streams=60)
+        assert n > 100 and n_retry > 0
+
+
+def test_runs_of_queued_frames_device_path(dbe):
+    n, n_retry = pc.run_open_scenario(dbe, seed=5, n_streams=60)
+    assert n > 100 and n_retry > 0
 
 
 def test_golden_chains(be, ss_vectors):
