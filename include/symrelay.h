@@ -211,6 +211,26 @@ SYMRELAY_API int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, co
                                             const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, void *d_scratch,
                                             uint64_t scratch_bytes, void *cuda_stream);
 
+/* Same work as symrelay_batch_device_runs, for callers that must not allocate.  No counterpart in
+ * the reference (it has no GPU and no scratch).  A provider normally shares its GPU with the model
+ * server it relays for, which owns almost all of HBM by the time bulk segments arrive, so scratch
+ * requested then may not exist; and the caller is an event-loop thread that cannot afford the
+ * device-wide synchronisation of cudaMalloc/cudaFree.  Here the nonce scratch is a fixed array inside
+ * the library: 1 MiB of HBM on every GPU that loads it, kept until the process exits, at most
+ * SYMRELAY_STATIC_RUN_MAX (65,536) descriptors per call -- larger batches are refused with
+ * SYMRELAY_EINVAL and a message naming the limit.  The call itself performs no cudaMalloc, cudaFree
+ * or other allocating call; all inputs and outputs are still the caller's device buffers.
+ * The first call on each GPU looks up the array's device address (one-time set-up): make that first
+ * call before starting any stream capture.  All calls on a GPU share the one array and it keeps the
+ * previous call's contents: nothing in it needs clearing (each call's pre-pass rewrites every entry
+ * its kernels read), but two calls whose kernels overlap on the GPU (different streams) race on it --
+ * issue them on one stream or otherwise order them. */
+#define SYMRELAY_STATIC_RUN_MAX 65536u
+SYMRELAY_API int symrelay_batch_device_runs_static(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc,
+                                                   uint32_t n, const symrelay_tile *d_tiles, uint32_t n_tiles,
+                                                   uint32_t n_bulk_tiles, const uint8_t *d_in, uint8_t *d_out,
+                                                   uint32_t *d_status, void *cuda_stream);
+
 /* HOST buffers (pinned from symrelay_alloc_pinned for full speed, pageable
  * accepted): plans, copies in, launches, copies out, waits.  Batches of up to
  * 1 MiB (in + out) whose arenas came from symrelay_alloc_pinned skip the copies:

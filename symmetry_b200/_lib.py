@@ -20,7 +20,7 @@ EXPORTS = (
     "symrelay_batch_host", "symrelay_batch_submit", "symrelay_batch_wait", "symrelay_alloc_pinned",
     "symrelay_free_pinned", "symrelay_probe_int_peak", "symrelay_submit_seal", "symrelay_submit_open",
     "symrelay_flush", "symrelay_poll", "symrelay_poll_wait", "symrelay_release", "symrelay_sched_stats",
-    "symrelay_sched_reset_stats", "symrelay_batch_device_runs",
+    "symrelay_sched_reset_stats", "symrelay_batch_device_runs", "symrelay_batch_device_runs_static",
 )
 
 
@@ -95,6 +95,8 @@ def load() -> C.CDLL:
     L.symrelay_probe_int_peak.argtypes = [vp, ci, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.symrelay_batch_device_runs.restype = ci
     L.symrelay_batch_device_runs.argtypes = [vp, ci, vp, u32, vp, u32, u32, vp, vp, vp, vp, u64, vp]
+    L.symrelay_batch_device_runs_static.restype = ci
+    L.symrelay_batch_device_runs_static.argtypes = [vp, ci, vp, u32, vp, u32, u32, vp, vp, vp, vp]
     L.symrelay_submit_seal.restype = i64
     L.symrelay_submit_seal.argtypes = [vp, u32, vp, u32, u32]
     L.symrelay_submit_open.restype = i64

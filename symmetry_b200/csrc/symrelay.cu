@@ -616,6 +616,59 @@ int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, const symrelay_
                         nullptr, (cudaStream_t)cuda_stream, 0u, reinterpret_cast<uint4 *>(d_scratch));
 }
 
+// ---- run batches without any allocation -------------------------------------------------------
+// Who needs this: a provider usually shares its GPU with the model server it relays for (Ollama,
+// llama.cpp ...), which has claimed nearly all of HBM before the relay receives its first bulk
+// segment; an allocation for run scratch made at that moment can simply fail.  And the caller is
+// Node's event-loop thread: cudaMalloc/cudaFree synchronise the whole device, which would stall
+// every connection's batch in flight.  For those callers the nonce scratch of a run batch lives in
+// this fixed array instead of caller- or library-allocated memory.  Cost: 1 MiB of HBM on every
+// GPU that loads the library, held until the process exits, and a hard cap on the batch size.
+#define SYMRELAY_STATIC_RUN_FRAMES 65536u
+static __device__ __align__(256) uint4 g_run_nonce_static[SYMRELAY_STATIC_RUN_FRAMES];
+
+// In host code `g_run_nonce_static` is only a handle for the runtime, not an address a kernel can
+// use, so the device address is looked up once per device (with that device current) and cached.
+static uint4 *g_run_nonce_static_ptr[64];
+static std::mutex g_run_nonce_static_mu;
+
+static int static_run_scratch(symrelay_ctx *ctx, int dev, uint4 **out) {
+    if (dev < 0 || dev >= 64) return fail(ctx, SYMRELAY_EINVAL, "device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_run_nonce_static_mu);
+    if (!g_run_nonce_static_ptr[dev]) {
+        uint4 *ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_run_nonce_static);
+        if (e != cudaSuccess || !ptr)
+            return fail(ctx, SYMRELAY_ECUDA, "cudaGetSymbolAddress(run scratch) failed on device %d: %s", dev,
+                        cudaGetErrorString(e));
+        g_run_nonce_static_ptr[dev] = ptr;
+    }
+    *out = g_run_nonce_static_ptr[dev];
+    return 0;
+}
+
+int symrelay_batch_device_runs_static(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
+                                      const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
+                                      const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, void *cuda_stream) {
+    if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
+    if (n == 0 || n_tiles == 0) return 0;
+    if (n > SYMRELAY_STATIC_RUN_FRAMES)
+        return fail(ctx, SYMRELAY_EINVAL,
+                    "symrelay_batch_device_runs_static: %u descriptors exceed the built-in scratch of %u; split the "
+                    "batch or use symrelay_batch_device_runs with your own scratch", n, SYMRELAY_STATIC_RUN_FRAMES);
+    if (!d_desc || !d_tiles || !d_in || !d_out || !d_status || n_bulk_tiles > n_tiles)
+        return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_device_runs_static: null pointer or bad tile counts");
+    Shard &sh = ctx->shard[gpu_index];
+    CU(ctx, set_device(sh.dev));
+    uint4 *scratch = nullptr;
+    const int rc = static_run_scratch(ctx, sh.dev, &scratch);
+    if (rc) return rc;
+    // Nothing in the array has to start at zero: the nonce pre-pass of this call writes every entry that
+    // this call's tile kernels read (entries of non-run descriptors keep stale values and are never read).
+    return launch_tiles(ctx, d_desc, n, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status, nullptr,
+                        nullptr, (cudaStream_t)cuda_stream, 0u, scratch);
+}
+
 static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st) {
     if (!st.busy) return 0;
     CU(ctx, set_device(sh.dev));

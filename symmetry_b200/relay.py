@@ -224,6 +224,16 @@ class SymRelay:
         self._check(self.lib.symrelay_batch_device_runs(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk, d_in,
                                                         d_out, d_status, d_scratch, scratch_bytes, stream))
 
+    def batch_device_runs_static(self, d_desc: int, n: int, d_tiles: int, n_tiles: int, n_bulk: int, d_in: int,
+                                 d_out: int, d_status: int, stream: int = 0, gpu_index: int = 0):
+        """batch_device_runs for callers that cannot allocate (the GPU is full of model weights, or the
+        caller is an event-loop thread that must not trigger cudaMalloc's device-wide sync): the nonce
+        scratch is a fixed 1 MiB array inside the library, so n is capped at 65,536 descriptors.  The
+        first call on a GPU does a one-time address look-up (do it before any stream capture); calls
+        share the array, so keep them ordered on one stream."""
+        self._check(self.lib.symrelay_batch_device_runs_static(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk,
+                                                               d_in, d_out, d_status, stream))
+
     def alloc_pinned(self, nbytes: int) -> np.ndarray:
         """Pinned host arena as a uint8 numpy view (freed with the context)."""
         p = self.lib.symrelay_alloc_pinned(self.ctx, nbytes)

@@ -1,0 +1,108 @@
+"""symrelay_batch_device_runs_static: the run-opening entry point for callers that cannot allocate.
+
+A provider's relay often shares its GPU with the model server, which has taken nearly all of HBM
+before the first bulk segment arrives, and its caller is an event-loop thread that must not pay
+cudaMalloc's device-wide synchronisation.  That entry point therefore keeps its scratch in a fixed
+array inside the library.  Here it is driven through the C ABI on two consecutive batches of the
+same streams and must give byte-for-byte the results of the existing entry point
+(symrelay_batch_device_runs with caller-provided scratch): plaintext, status words and the exported
+stream states.  Collected last on purpose, and self-contained so it also passes in a fresh process."""
+import random
+
+import numpy as np
+import pytest
+
+import batch_util as bu
+from oracle import libsodium as ls
+
+pytestmark = pytest.mark.gpu
+
+
+def _scenario(rng, n_streams, senders):
+    """One batch of queued frames per stream (runs of 1..12 frames, mixed sizes, one REKEY mid-run)."""
+    owner, wires, lens = [], [], []
+    for i in range(n_streams):
+        k = rng.choice([1, 2, 4, 7, 12])
+        for j in range(k):
+            m = rng.randbytes(rng.choice([0, 1, 64, 200, 1920, 1921, 4097]))
+            tag = 2 if (i % 9 == 4 and j == k // 2) else 0
+            wires.append(senders[i].seal_frame(m, tag))
+            lens.append(len(m))
+            owner.append(i)
+    return owner, wires, lens
+
+
+def _run_batch(relay, call, slots, owner, wires, lens):
+    import torch
+
+    dev = torch.device("cuda:0")
+    w_offs, w_bytes = bu.wire_layout(lens)
+    p_offs, p_bytes = bu.plain_layout(lens)
+    arena = np.zeros(w_bytes, dtype=np.uint8)
+    for w, o in zip(wires, w_offs):
+        arena[o : o + len(w)] = np.frombuffer(w, dtype=np.uint8)
+    descs = bu.make_descs([slots[i] for i in owner], lens, w_offs, p_offs, open_=True, run=True)
+    tiles, n_bulk = relay.plan(descs)
+    t_desc = torch.from_numpy(descs.view(np.uint8).copy()).to(dev)
+    t_tiles = torch.from_numpy(tiles.view(np.uint8).copy()).to(dev)
+    t_in = torch.from_numpy(arena).to(dev)
+    t_out = torch.zeros(p_bytes, dtype=torch.uint8, device=dev)
+    t_status = torch.full((len(descs),), 0xFF, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    if call == "static":
+        relay.batch_device_runs_static(t_desc.data_ptr(), len(descs), t_tiles.data_ptr(), len(tiles), n_bulk,
+                                       t_in.data_ptr(), t_out.data_ptr(), t_status.data_ptr(), stream=stream)
+    else:
+        scratch = torch.empty(16 * len(descs), dtype=torch.uint8, device=dev)
+        relay.batch_device_runs(t_desc.data_ptr(), len(descs), t_tiles.data_ptr(), len(tiles), n_bulk, t_in.data_ptr(),
+                                t_out.data_ptr(), t_status.data_ptr(), scratch.data_ptr(), scratch.numel(), stream=stream)
+    torch.cuda.synchronize()
+    return t_out.cpu().numpy(), t_status.cpu().numpy().astype(np.uint32), p_offs
+
+
+def test_static_scratch_entry_point_matches_the_existing_one_twice_in_a_row():
+    import symmetry_b200 as sb
+
+    rng = random.Random(1234)
+    n_streams = 96
+    keys = [rng.randbytes(32) for _ in range(n_streams)]
+    hdrs = [rng.randbytes(24) for _ in range(n_streams)]
+    senders = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+    mirrors = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+    karr = np.frombuffer(b"".join(keys), dtype=np.uint8).reshape(n_streams, 32)
+    harr = np.frombuffer(b"".join(hdrs), dtype=np.uint8).reshape(n_streams, 24)
+    with sb.SymRelay(gpu_ids=(0,), max_streams=1024) as relay:
+        slots_a = [int(s) for s in relay.open_streams(None, None, karr, harr)]   # driven by the existing entry point
+        slots_b = [int(s) for s in relay.open_streams(None, None, karr, harr)]   # driven by the new one
+        for call_no in range(2):                                                 # two calls in a row, chain continues
+            owner, wires, lens = _scenario(rng, n_streams, senders)
+            out_a, st_a, p_offs = _run_batch(relay, "existing", slots_a, owner, wires, lens)
+            out_b, st_b, _ = _run_batch(relay, "static", slots_b, owner, wires, lens)
+            assert (st_a == st_b).all(), f"status words differ on call {call_no}"
+            assert (out_a == out_b).all(), f"plaintext differs on call {call_no}"
+            # and both are what sequential libsodium pulls give; frames held back behind a REKEY are
+            # resubmitted through the same entry points so the next call starts from the full chain
+            retry = [j for j in range(len(owner)) if (int(st_b[j]) & 0xFF) == sb.relay.ST_RETRY]
+            for j in range(len(owner)):
+                if j in retry:
+                    continue
+                m, tag = mirrors[owner[j]].open_frame(wires[j])
+                assert int(st_b[j]) == (tag << 8) and bytes(out_b[p_offs[j] : p_offs[j] + lens[j]]) == m
+            if retry:
+                sub = ([owner[j] for j in retry], [wires[j] for j in retry], [lens[j] for j in retry])
+                out_a2, st_a2, po2 = _run_batch(relay, "existing", slots_a, *sub)
+                out_b2, st_b2, _ = _run_batch(relay, "static", slots_b, *sub)
+                assert (st_a2 == st_b2).all() and (out_a2 == out_b2).all()
+                for k, j in enumerate(retry):
+                    m, tag = mirrors[owner[j]].open_frame(wires[j])
+                    assert int(st_b2[k]) == (tag << 8) and bytes(out_b2[po2[k] : po2[k] + lens[j]]) == m
+            for i in range(0, n_streams, 7):
+                assert relay.export(slots_a[i])[1] == relay.export(slots_b[i])[1] == mirrors[i].raw
+
+
+def test_static_scratch_entry_point_refuses_oversized_batches():
+    import symmetry_b200 as sb
+
+    with sb.SymRelay(gpu_ids=(0,), max_streams=64) as relay:
+        with pytest.raises(sb.RelayError, match="65536"):
+            relay.batch_device_runs_static(16, 65537, 16, 1, 0, 16, 16, 16)   # rejected before any pointer is used
