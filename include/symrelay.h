@@ -263,6 +263,16 @@ SYMRELAY_API int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket);
 SYMRELAY_API int64_t symrelay_submit_seal(symrelay_ctx *ctx, uint32_t slot, const uint8_t *plain, uint32_t len,
                                           uint32_t flags);
 SYMRELAY_API int64_t symrelay_submit_open(symrelay_ctx *ctx, uint32_t slot, const uint8_t *wire, uint32_t wire_len);
+/* symrelay_rx_feed  <-  secret-stream `_onrawdata` (the state typed at src/types.ts:156-159: _state, _len,
+ *     _tmp, _message): feed raw transport bytes of one connection in arrival order, cut anywhere (inside
+ *     the 3-byte length too).  Every frame completed by this segment is submitted as an open frame;
+ *     several frames of one segment join one batch as a run (SYMRELAY_F_RUN) and are opened in parallel.
+ *     Returns the number of frames submitted (their tickets in tickets[0..)), *consumed = bytes of `seg`
+ *     taken; when the ring is full it returns what it could (or SYMRELAY_EAGAIN if nothing) and the caller
+ *     feeds the rest of the segment after draining completions.  A completion with SYMRELAY_ST_RETRY (only
+ *     behind a REKEY-tagged frame) must be resubmitted with symrelay_submit_open. */
+SYMRELAY_API int symrelay_rx_feed(symrelay_ctx *ctx, uint32_t slot, const uint8_t *seg, uint32_t n, uint32_t *consumed,
+                                  int64_t *tickets, int max_tickets);
 SYMRELAY_API int symrelay_flush(symrelay_ctx *ctx);
 SYMRELAY_API int symrelay_poll(symrelay_ctx *ctx, symrelay_completion *out, int max);
 SYMRELAY_API int symrelay_poll_wait(symrelay_ctx *ctx, symrelay_completion *out, int max);

@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>

@@ -185,6 +185,16 @@ class SymRelay:
         """One whole inbound wire frame (uint24-LE prefix included)."""
         return self._check(self.lib.symrelay_submit_open(self.ctx, int(slot), bytes(wire), len(wire)))
 
+    def rx_feed(self, slot: int, segment: bytes):
+        """secret-stream `_onrawdata`: raw transport bytes of one connection, cut anywhere.  Returns
+        (tickets of the frames this segment completed, bytes consumed)."""
+        tick = (C.c_int64 * 256)()
+        used = C.c_uint32(0)
+        n = self.lib.symrelay_rx_feed(self.ctx, int(slot), bytes(segment), len(segment), C.byref(used), tick, 256)
+        if n < 0 and n != EAGAIN:
+            self._check(n)
+        return [tick[i] for i in range(max(n, 0))], used.value
+
     def flush(self) -> None:
         self._check(self.lib.symrelay_flush(self.ctx))
 

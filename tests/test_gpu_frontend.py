@@ -198,3 +198,60 @@ def test_deadline_flush_and_latency_stats():
         assert got == 1000
         st = r.sched_stats()
         assert st["frames"] == 1000 and 0 < st["p50_us"] < 50000 and st["p99_us"] >= st["p50_us"]
+
+
+def test_receive_side_reassembly_and_runs(relay):
+    """secret-stream `_onrawdata` semantics: frames arrive as a byte stream cut at arbitrary points
+    (inside the uint24 length too); all frames completed by a segment are opened in one batch as a run."""
+    rng = random.Random(4)
+    n = 40
+    keys = [rng.randbytes(32) for _ in range(n)]
+    hdrs = [rng.randbytes(24) for _ in range(n)]
+    slots = [relay.open_stream(None, None, k, h) for k, h in zip(keys, hdrs)]
+    senders = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+    expect = {i: [] for i in range(n)}
+    streams = []
+    for i in range(n):
+        blob = b""
+        for _ in range(rng.randrange(1, 30)):
+            m = rng.randbytes(rng.choice([0, 0, 1, 40, 64, 200, 200, 1500, 4000]))   # 0 = keep-alive frame
+            expect[i].append(m)
+            blob += senders[i].seal_frame(m)
+        streams.append(blob)
+    # cut every connection's byte stream into random segments and feed them round-robin
+    cursors = [0] * n
+    tickets = {i: [] for i in range(n)}
+    got = {}
+    while any(c < len(s) for c, s in zip(cursors, streams)):
+        for i in rng.sample(range(n), n):
+            if cursors[i] >= len(streams[i]):
+                continue
+            seg = streams[i][cursors[i] : cursors[i] + rng.choice([1, 2, 3, 5, 19, 100, 700, 5000])]
+            tk, used = relay.rx_feed(slots[i], seg)
+            tickets[i] += tk
+            cursors[i] += used
+            if used < len(seg):                      # ring full: drain, the rest is fed again next round
+                for c in relay.poll(wait=True):
+                    got[c["ticket"]] = c
+        relay.flush()
+        for c in relay.poll():
+            got[c["ticket"]] = c
+    relay.flush()
+    want_total = sum(len(v) for v in expect.values())
+    while len(got) < want_total:
+        for c in relay.poll(wait=True):
+            got[c["ticket"]] = c
+        relay.flush()
+    for i in range(n):
+        assert len(tickets[i]) == len(expect[i])
+        for t, m in zip(tickets[i], expect[i]):
+            assert got[t]["status"] == 0 and got[t]["open"] and got[t]["data"] == m
+        ref = ls.State(keys[i], hdrs[i])
+        off = 0
+        blob = streams[i]
+        while off < len(blob):
+            ln = blob[off] | (blob[off + 1] << 8) | (blob[off + 2] << 16)
+            assert ref.open_frame(blob[off : off + 3 + ln]) is not None
+            off += 3 + ln
+        assert relay.export(slots[i])[1] == ref.raw
+    assert relay.sched_stats()["frames"] >= want_total
