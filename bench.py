@@ -46,6 +46,8 @@ def workload(name: str, n_gpus: int):
     elif name == "c3":
         total = 65536
         lens = synth.power_law_lens(total)[: total // n_gpus]
+        if os.environ.get("BENCH_C3_SORTED"):
+            lens = np.sort(lens)
         desc = "configs[2]: 65,536 streams, power-law frames 32 B-16 KiB (alpha 1.2), sharded by slot"
         scaling = "strong"
     elif name == "c4":

@@ -23,16 +23,42 @@ static inline int symrelay_desc_check_inline(const symrelay_desc *d) {
     return 0;
 }
 
-// Two passes over the descriptors: packed tiles first, bulk tiles after them.
+#ifndef SYMRELAY_THREAD_TILE_MIN_FRAMES
+#define SYMRELAY_THREAD_TILE_MIN_FRAMES 8192u /* batches smaller than this are latency-bound: packed tiles only */
+#endif
+#define SYMRELAY_THREAD_TILE_MAX_BLOCKS 6u   /* frames of up to 4 payload blocks (256 B) */
+
+// Two passes over the descriptors: small tiles first (packed, or thread-per-frame tiles: bit 17 of
+// n_kind, 32 consecutive frames with the same block count, one per lane), bulk tiles after them.
 static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles,
                                            uint32_t max_tiles, uint32_t *n_bulk_out) {
     uint64_t n_tiles = 0;
     uint32_t n_bulk = 0;
     uint32_t run_first = 0, run_n = 0, run_blocks = 0;
+    const bool thread_tiles = n >= SYMRELAY_THREAD_TILE_MIN_FRAMES;
     for (uint32_t i = 0; i < n; i++) {
         if (symrelay_desc_check_inline(&desc[i])) return SYMRELAY_EINVAL;
         const uint32_t nc = symrelay_nblocks(desc[i].len_flags & SYMRELAY_LEN_MASK);
         const bool bulk = nc > 32u;
+        if (thread_tiles && nc <= SYMRELAY_THREAD_TILE_MAX_BLOCKS && i + 32u <= n) {
+            // 32 consecutive frames with one block count -> one lane each, no lane idles
+            uint32_t j = 1;
+            for (; j < 32u; j++) {
+                if (symrelay_desc_check_inline(&desc[i + j])) return SYMRELAY_EINVAL;
+                if (symrelay_nblocks(desc[i + j].len_flags & SYMRELAY_LEN_MASK) != nc) break;
+            }
+            if (j == 32u) {
+                if (run_n) {   // close the packed tile in progress first
+                    if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = run_first; tiles[n_tiles].n_kind = run_n; }
+                    n_tiles++;
+                    run_n = 0; run_blocks = 0;
+                }
+                if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = 32u | (1u << 17); }
+                n_tiles++;
+                i += 31u;
+                continue;
+            }
+        }
         if (bulk || run_blocks + nc > 32u || run_n == 16u) {
             if (run_n) {
                 if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = run_first; tiles[n_tiles].n_kind = run_n; }

@@ -409,7 +409,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
     for (uint32_t it = 0; it < niter; ++it) {
         const uint32_t b = (lane - st) + 32u * it;
         const bool has_block = valid && b < nc;
-        const bool need_ks = has_block && (!(BULK && is_open) || b < 2u);
+        const bool need_ks = has_block;
         // (Bulk tiles load after the rounds: they have enough warps in flight, and holding the
         // payload registers across ChaCha20 cost them occupancy -- 65.8 % -> 62.9 % of the ALU peak.)
         const bool has_payload = has_block && b >= 2u;
@@ -473,6 +473,14 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
                     if (!BULK) {
 #pragma unroll
                         for (int i = 0; i < 16; i++) keep[i] = x[i] ^ m[i];
+                    } else {
+                        // Bulk frames cannot hold their plaintext in registers until the verdict, and a second
+                        // pass re-read the whole ciphertext from HBM (ncu: 3.28 GB read for 2.15 GB of input).
+                        // So decrypt now, in the same pass as the MAC, and wipe the output if the tag turns out
+                        // wrong: no unauthenticated byte is ever visible to the caller.
+#pragma unroll
+                        for (int i = 0; i < 16; i++) x[i] ^= m[i];
+                        ss_store64(dst + 64u * (size_t)j, cbytes, x);
                     }
 #pragma unroll
                     for (int i = 0; i < 16; i++) x[i] = m[i];      // MAC is over the ciphertext
@@ -578,20 +586,17 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
         }
     }
     if (BULK) {
-        // verified: second pass decrypts (lanes keep striding by 32 blocks); warp-uniform branch
-        if (is_open && ok) {
+        if (is_open && !ok) {   // forged bulk frame: wipe what was decrypted speculatively (warp-uniform branch)
+            uint32_t z[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) z[i] = 0;
 #pragma unroll 1
             for (uint32_t it = 0; it < niter; ++it) {
                 const uint32_t b = lane + 32u * it;
                 if (b >= 2u && b < nc) {
                     const uint32_t j = b - 2u;
                     const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
-                    uint32_t x[16], m[16];
-                    ss_chacha_block(k, b, nn[0], nn[1], nn[2], x);
-                    ss_load64(src + 64u * (size_t)j, cbytes, m);
-#pragma unroll
-                    for (int i = 0; i < 16; i++) x[i] ^= m[i];
-                    ss_store64(dst + 64u * (size_t)j, cbytes, x);
+                    ss_store64(dst + 64u * (size_t)j, cbytes, z);
                 }
             }
         }
@@ -621,4 +626,132 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
             a.status[frame_idx] = SS_ST_BAD_MAC;
         }
     }
+}
+
+
+// ------------------------------------------------------ thread-per-frame tile --
+// For large batches of SMALL frames (<= 4 payload blocks) the packed mapping leaves throughput on
+// the table: its lane-parallel Poly1305 (window fix-ups, r^E alignment, shuffle tree) and per-warp
+// bookkeeping cost about as many instructions as ChaCha20 itself, and the block counts rarely fill
+// all 32 lanes.  Here one LANE owns one whole frame: its ChaCha20 blocks run back to back and
+// Poly1305 is plain Horner with r -- no collectives at all, every lane busy when the frames of a
+// warp have the same block count (the planner only forms these tiles from such frames).  Latency per
+// frame is higher (blocks are serial), so the planner uses it only when a batch is big enough to be
+// throughput-bound; small batches (BASELINE config 2) stay on packed tiles.
+SS_DEV void ss_thread_window(uint32_t acc[5], uint32_t w[16], uint32_t q, uint32_t T, uint32_t V, const uint32_t r[5]) {
+    const int so = (int)(64u * q);
+    int nbytes = (int)T - so;
+    nbytes = nbytes < 0 ? 0 : (nbytes > 64 ? 64 : nbytes);
+    if (nbytes <= 0) return;
+    const int vo = (int)T - 8 - so;
+    if (vo < 64 && vo > -4) ss_insert(w, vo, V);
+    if ((T & 15u) && (int)T - so < 64) ss_insert(w, (int)T - so, 1u);
+    ss_phorner(acc, w, (uint32_t)nbytes, r);
+}
+
+SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx) {
+    const uint32_t lane = ss_lane();
+    ss_pdl_launch_dependents();
+    if (!(a.flags & SS_ARG_INPUT_INDEPENDENT)) ss_pdl_wait();
+    const SsTile tile = a.tiles[tile_idx];
+    const uint32_t nfr = tile.n_kind & 0xffffu;
+    bool valid = lane < nfr;
+    SsDesc d;
+    d.slot = d.in_off = d.out_off = d.len_flags = 0;
+    if (valid) d = a.desc[tile.first + lane];
+    ss_pdl_wait();
+    const uint32_t lf = d.len_flags;
+    if (valid && (lf & SS_F_EXTRACT) && !(lf & SS_F_OPEN) && a.status[tile.first + lane] != SS_ST_OK) valid = false;
+    if (!valid) return;
+    const uint32_t mlen = lf & 0xffffffu;
+    const bool is_open = (lf & SS_F_OPEN) != 0;
+    const uint32_t npay = (mlen + 63u) >> 6;
+    const uint32_t nc = 2u + npay;
+    const uint32_t T = 80u + mlen + (mlen & 15u);
+    const uint32_t V = 64u + mlen;
+    const uint8_t *src = a.in + d.in_off + (is_open ? 4u : 0u);
+    uint8_t *dst = a.out + d.out_off + (is_open ? 0u : 4u);
+    uint4 *sp = a.states + ((size_t)d.slot * 2u + (is_open ? 1u : 0u)) * 3u;
+    const uint4 s0 = sp[0], s1 = sp[1], s2 = sp[2];
+    uint32_t k[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    uint32_t nn[3] = {s2.x, s2.y, s2.z};
+    const bool in_run = (lf & SS_F_RUN) != 0 && is_open;
+    if (in_run) {
+        const uint4 o = a.run_nonce[tile.first + lane];
+        nn[0] = o.x; nn[1] = o.y; nn[2] = o.z;
+    }
+    uint32_t x[16], r[5], sw[4], acc[5] = {0, 0, 0, 0, 0};
+    ss_chacha_block(k, 0, nn[0], nn[1], nn[2], x);            // Poly1305 key block
+    ss_r_limbs(x[0], x[1], x[2], x[3], r);
+    sw[0] = x[4]; sw[1] = x[5]; sw[2] = x[6]; sw[3] = x[7];
+    ss_chacha_block(k, 1, nn[0], nn[1], nn[2], x);            // tag block
+    uint32_t tag;
+    if (!is_open) {
+        tag = (lf >> 24) & 3u;
+        x[0] ^= tag;
+        *reinterpret_cast<uint32_t *>(a.out + d.out_off) = (mlen + 17u) | ((x[0] & 0xffu) << 24);
+    } else {
+        const uint32_t c0 = *reinterpret_cast<const uint32_t *>(a.in + d.in_off) >> 24;
+        tag = (x[0] ^ c0) & 0xffu;
+        x[0] = (x[0] & 0xffffff00u) | c0;
+    }
+    ss_thread_window(acc, x, 0, T, V, r);
+    // payload windows: seal encrypts and MACs in one pass; open MACs the ciphertext first
+#pragma unroll 1
+    for (uint32_t j = 0; j < npay; j++) {
+        const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
+        uint32_t m[16];
+        ss_load64(src + 64u * (size_t)j, cbytes, m);
+        if (!is_open) {
+            ss_chacha_block(k, 2u + j, nn[0], nn[1], nn[2], x);
+#pragma unroll
+            for (int i = 0; i < 16; i++) m[i] ^= x[i];
+            ss_store64(dst + 64u * (size_t)j, cbytes, m);
+        }
+        if (cbytes < 64) ss_keep_bytes(m, cbytes);
+        ss_thread_window(acc, m, 1u + j, T, V, r);
+    }
+    if (64u * (nc - 1u) < T) {                                 // overflow window: the tail of the length block
+#pragma unroll
+        for (int i = 0; i < 16; i++) x[i] = 0;
+        ss_thread_window(acc, x, nc - 1u, T, V, r);
+    }
+    uint32_t mac[4];
+    ss_pfinal(acc, sw, mac);
+    bool ok = true;
+    if (!is_open) ss_store_mac(dst + mlen, mac);
+    else {
+        uint32_t wmac[4];
+        ss_load_mac(src + mlen, wmac);
+        ok = ((wmac[0] ^ mac[0]) | (wmac[1] ^ mac[1]) | (wmac[2] ^ mac[2]) | (wmac[3] ^ mac[3])) == 0;
+        if (ok) {
+#pragma unroll 1
+            for (uint32_t j = 0; j < npay; j++) {              // verified: decrypt (ciphertext is still in L1/L2)
+                const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
+                uint32_t m[16];
+                ss_load64(src + 64u * (size_t)j, cbytes, m);
+                ss_chacha_block(k, 2u + j, nn[0], nn[1], nn[2], x);
+#pragma unroll
+                for (int i = 0; i < 16; i++) m[i] ^= x[i];
+                ss_store64(dst + 64u * (size_t)j, cbytes, m);
+            }
+        }
+    }
+    const uint32_t frame_idx = tile.first + lane;
+    if (!ok) { a.status[frame_idx] = SS_ST_BAD_MAC; return; }
+    if (in_run) { a.status[frame_idx] = SS_ST_OK | (tag << 8); return; }
+    nn[1] ^= mac[0];
+    nn[2] ^= mac[1];
+    nn[0] += 1u;
+    if ((tag & 2u) || nn[0] == 0u) {
+        ss_rekey(k, nn);
+        uint4 t0, t1;
+        t0.x = k[0]; t0.y = k[1]; t0.z = k[2]; t0.w = k[3];
+        t1.x = k[4]; t1.y = k[5]; t1.z = k[6]; t1.w = k[7];
+        sp[0] = t0; sp[1] = t1;
+    }
+    uint4 t2;
+    t2.x = nn[0]; t2.y = nn[1]; t2.z = nn[2]; t2.w = s2.w;
+    sp[2] = t2;
+    a.status[frame_idx] = SS_ST_OK | (tag << 8);
 }

@@ -35,7 +35,8 @@ static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) =
 __global__ void __launch_bounds__(128) ss_packed_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
-    ss_process_tile<false>(a, warp);
+    if (a.tiles[warp].n_kind & (1u << 17)) ss_process_thread_tile(a, warp);   // warp-uniform: whole tile is one kind
+    else ss_process_tile<false>(a, warp);
 }
 
 // Bulk tiles: one frame per warp, lanes stride over its 64-byte blocks.

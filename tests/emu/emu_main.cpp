@@ -26,7 +26,10 @@ static void *lane_main(void *p) {
     Job *j = (Job *)p;
     emu_lane_id = j->lane;
     emu_warp = j->warp;
-    for (uint32_t t = 0; t < j->n_packed; t++) ss_process_tile<false>(j->args, t);
+    for (uint32_t t = 0; t < j->n_packed; t++) {
+        if (j->args.tiles[t].n_kind & (1u << 17)) ss_process_thread_tile(j->args, t);
+        else ss_process_tile<false>(j->args, t);
+    }
     for (uint32_t t = 0; t < j->n_bulk; t++) ss_process_tile<true>(j->args, j->n_packed + t);
     return nullptr;
 }

@@ -122,3 +122,21 @@ def test_golden_chains_through_emulated_kernel(be, ss_vectors):
 def test_runs_of_queued_frames(be):
     n, n_retry = pc.run_open_scenario(be, seed=3)
     assert n > 60 and n_retry > 0
+
+
+def test_thread_per_frame_tiles(be):
+    """The emulator library is built with the thread-tile threshold lowered to 64 frames so this path
+    (one lane = one whole frame, serial blocks, plain Horner) is covered on CPU."""
+    lens = [64] * 70 + [0] * 40 + [200] * 33 + [256] * 32 + [1] * 32 + [17, 300, 64, 64]
+    p, _ = bu.plain_layout(lens)
+    w, _ = bu.wire_layout(lens)
+    tiles, n_bulk = be.plan(bu.make_descs(np.arange(len(lens)), lens, p, w))
+    kinds = [int(t["n_kind"]) >> 16 for t in tiles]
+    assert kinds.count(2) >= 5 and kinds.count(0) >= 2 and n_bulk == 0   # both small-tile kinds in one batch
+    tags = [(i % 4) if i % 7 == 0 else 0 for i in range(len(lens))]
+    pc.seal_open_roundtrip(be, lens, tags, seed=8, chain=3, corrupt=(0, 5, 71, 111, 150, 180))
+
+
+def test_thread_tiles_in_runs(be):
+    n, n_retry = pc.run_open_scenario(be, seed=9, n_streams=40)
+    assert n > 64

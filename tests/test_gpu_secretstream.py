@@ -152,6 +152,16 @@ def test_config2_1024_streams_x64B_chain(be):
     pc.seal_open_roundtrip(be, [64] * 1024, [0] * 1024, seed=6, chain=8)
 
 
+def test_thread_per_frame_tiles_on_a_large_uniform_batch(be):
+    """>= 8,192 frames with runs of equal block counts: the planner switches those to thread-per-frame
+    tiles (one lane = one frame).  Same bit-exact bar, incl. tags, rekey and forged frames."""
+    lens = [64] * 6000 + [200] * 5000 + [0] * 640 + [256] * 320 + [1500, 5000, 30]
+    tiles, _ = be.relay.plan(bu.make_descs(np.arange(len(lens)), lens, bu.plain_layout(lens)[0], bu.wire_layout(lens)[0]))
+    assert sum(1 for t in tiles if int(t["n_kind"]) >> 17) == 6000 // 32 + 5000 // 32 + 640 // 32 + 320 // 32
+    tags = [(i % 4) if i % 11 == 0 else 0 for i in range(len(lens))]
+    pc.seal_open_roundtrip(be, lens, tags, seed=31, chain=2, corrupt=(0, 31, 32, 6001, 11000, 11700, 11960))
+
+
 def test_counter_wrap_rekeys(be):
     key, hdr = bytes(range(32)), bytes(24)
     raw = bytearray(ls.State(key, hdr).raw)
