@@ -20,7 +20,7 @@ HEADERS = ["ss_core.cuh", "plan.h", os.path.join("..", "..", "include", "symrela
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC,-O2,-fvisibility=hidden",
+    "-Xcompiler", "-fPIC,-O3,-fvisibility=hidden",
     "-shared", "-cudart", "static", "-Xlinker", "--exclude-libs,ALL",
     "-Xptxas", "-v",
 ]

@@ -28,25 +28,36 @@ static inline int symrelay_desc_check_inline(const symrelay_desc *d) {
 #endif
 #define SYMRELAY_THREAD_TILE_MAX_BLOCKS 6u   /* frames of up to 4 payload blocks (256 B) */
 
-// Two passes over the descriptors: small tiles first (packed, or thread-per-frame tiles: bit 17 of
-// n_kind, 32 consecutive frames with the same block count, one per lane), bulk tiles after them.
+// Small tiles first (packed, or thread-per-frame tiles: bit 17 of n_kind, 32 consecutive frames with
+// the same block count, one per lane), bulk tiles after them.  Runs on the host's per-batch critical
+// path, so pass 1 (validation + block counts) is a branch-free loop the compiler vectorises and the
+// tile cutting only walks the block-count array.
+#include <vector>
+
 static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles,
                                            uint32_t max_tiles, uint32_t *n_bulk_out) {
+    static thread_local std::vector<uint32_t> ncv;
+    if (ncv.size() < n) ncv.resize(n);
+    uint32_t *nc = ncv.data();
+    uint32_t bad = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t lf = desc[i].len_flags;
+        const uint32_t mlen = lf & SYMRELAY_LEN_MASK;
+        const uint32_t op = (lf >> 26) & 1u;   // SYMRELAY_F_OPEN
+        bad |= (uint32_t)(mlen > SYMRELAY_MAX_FRAME) | (uint32_t)((desc[i].in_off & 15u) != 12u * op) |
+               (uint32_t)((desc[i].out_off & 15u) != 12u * (1u - op));
+        nc[i] = 2u + ((mlen + 63u) >> 6);
+    }
+    if (bad) return SYMRELAY_EINVAL;
     uint64_t n_tiles = 0;
     uint32_t n_bulk = 0;
     uint32_t run_first = 0, run_n = 0, run_blocks = 0;
     const bool thread_tiles = n >= SYMRELAY_THREAD_TILE_MIN_FRAMES;
     for (uint32_t i = 0; i < n; i++) {
-        if (symrelay_desc_check_inline(&desc[i])) return SYMRELAY_EINVAL;
-        const uint32_t nc = symrelay_nblocks(desc[i].len_flags & SYMRELAY_LEN_MASK);
-        const bool bulk = nc > 32u;
-        if (thread_tiles && nc <= SYMRELAY_THREAD_TILE_MAX_BLOCKS && i + 32u <= n) {
-            // 32 consecutive frames with one block count -> one lane each, no lane idles
-            uint32_t j = 1;
-            for (; j < 32u; j++) {
-                if (symrelay_desc_check_inline(&desc[i + j])) return SYMRELAY_EINVAL;
-                if (symrelay_nblocks(desc[i + j].len_flags & SYMRELAY_LEN_MASK) != nc) break;
-            }
+        const uint32_t c = nc[i];
+        if (thread_tiles && c <= SYMRELAY_THREAD_TILE_MAX_BLOCKS && i + 32u <= n) {
+            uint32_t j = 1;   // 32 consecutive frames with one block count -> one lane each, no lane idles
+            while (j < 32u && nc[i + j] == c) j++;
             if (j == 32u) {
                 if (run_n) {   // close the packed tile in progress first
                     if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = run_first; tiles[n_tiles].n_kind = run_n; }
@@ -59,7 +70,8 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
                 continue;
             }
         }
-        if (bulk || run_blocks + nc > 32u || run_n == 16u) {
+        const bool bulk = c > 32u;
+        if (bulk || run_blocks + c > 32u || run_n == 16u) {
             if (run_n) {
                 if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = run_first; tiles[n_tiles].n_kind = run_n; }
                 n_tiles++;
@@ -68,7 +80,7 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
         }
         if (bulk) { n_bulk++; continue; }
         if (run_n == 0) run_first = i;
-        run_n++; run_blocks += nc;
+        run_n++; run_blocks += c;
     }
     if (run_n) {
         if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = run_first; tiles[n_tiles].n_kind = run_n; }
@@ -76,8 +88,7 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
     }
     if (n_bulk) {
         for (uint32_t i = 0; i < n; i++) {
-            const uint32_t nc = symrelay_nblocks(desc[i].len_flags & SYMRELAY_LEN_MASK);
-            if (nc > 32u) {
+            if (nc[i] > 32u) {
                 if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = 1u | (1u << 16); }
                 n_tiles++;
             }

@@ -20,6 +20,8 @@
 #pragma once
 #include <stdint.h>
 
+#include <initializer_list>
+
 #ifndef SS_DEV
 #define SS_DEV static inline
 #endif
@@ -37,12 +39,6 @@ namespace sx {
 enum : uint32_t { V_ABSENT = 0, V_UNDEF, V_NULL, V_FALSE, V_TRUE, V_NUMBER, V_STRING, V_OBJECT, V_ARRAY };
 enum : uint32_t { NF_FRAC = 1, NF_EXP = 2, NF_NONZERO = 4, AF_EMPTY = 8 };
 enum : uint32_t { KEY_NONE = 0, KEY_CHOICES, KEY_CONTENT, KEY_DELTA, KEY_ZERO };
-enum : uint32_t {
-    S_VALUE = 0, S_AFTER, S_OBJ_FIRST, S_OBJ_KEY, S_COLON, S_ARR_FIRST,
-    S_STR, S_ESC, S_U1, S_U2, S_U3, S_U4,
-    S_NMINUS, S_NZERO, S_NINT, S_NDOT, S_NFRAC, S_NE, S_NESIGN, S_NEXP,
-    S_LIT, S_ERR
-};
 enum : uint32_t { T_ROOT = 0, T_CHOICES, T_ELEM0, T_DELTA, T_CONTENT, T_RCONTENT, T_NONE };
 
 struct Val {
@@ -180,15 +176,163 @@ SS_DEV bool emit_number(const uint8_t *t, const Val &v, Out &o) {
     return true;
 }
 
+// ---- the automaton ----------------------------------------------------------------------------
+// One table look-up per input byte: T[state][byte] -> next state (bits 0..5) | action (bits 6..10).
+// Actions fire only at structural characters and at the first/last character of a value, so the
+// inner loop is the same handful of instructions for every lane whatever its chunk contains (the
+// first version was a switch over ~20 states: the lanes of a warp, each in its own JSON position,
+// serialised the switch arms and the kernel took 72 us for 16,384 chunks).
+enum : uint32_t {
+    S_VALUE = 0, S_ARR_FIRST, S_AFTER, S_OBJ_FIRST, S_OBJ_KEY, S_COLON,
+    S_STR, S_ESC, S_U1, S_U2, S_U3, S_U4,
+    S_KSTR, S_KESC, S_KU1, S_KU2, S_KU3, S_KU4,
+    S_NMINUS, S_NZERO, S_NINT, S_NDOT, S_NFRAC, S_NE, S_NESIGN, S_NEXP,
+    S_T1, S_T2, S_T3, S_F1, S_F2, S_F3, S_F4, S_N1, S_N2, S_N3,
+    S_ERR, S_COUNT
+};
+enum : uint32_t {
+    A_NONE = 0, A_OPEN_OBJ, A_OPEN_ARR, A_STR_START, A_NUM_START, A_LIT_T, A_LIT_F, A_LIT_N,
+    A_KEY_START, A_KEY_ESC, A_KEY_END, A_STR_END, A_CLOSE_OBJ, A_CLOSE_ARR, A_CLOSE_ARR_EMPTY, A_COMMA,
+    A_NUM_END, A_NUM_END_COMMA, A_NUM_END_CLOSE_OBJ, A_NUM_END_CLOSE_ARR
+};
+#define SX_TABLE_ENTRIES (sx::S_COUNT * 256u)
+
+// Fills T (SX_TABLE_ENTRIES uint16) with the ECMA-404 grammar.  Host code: the CUDA library builds it
+// once per device and the kernel stages it in shared memory.
+static inline void build_table(uint16_t *T) {
+    auto set = [&](uint32_t st, uint32_t c, uint32_t next, uint32_t act) { T[st * 256u + c] = (uint16_t)(next | (act << 6)); };
+    auto is_hex = [](uint32_t c) { return (c >= '0' && c <= '9') || ((c | 0x20u) >= 'a' && (c | 0x20u) <= 'f'); };
+    for (uint32_t st = 0; st < S_COUNT; st++)
+        for (uint32_t c = 0; c < 256; c++) set(st, c, S_ERR, A_NONE);
+    const uint8_t ws[4] = {0x20, 0x09, 0x0a, 0x0d};
+    for (uint32_t st : {(uint32_t)S_VALUE, (uint32_t)S_ARR_FIRST}) {
+        for (uint8_t w : ws) set(st, w, st, A_NONE);
+        set(st, '{', S_OBJ_FIRST, A_OPEN_OBJ);
+        set(st, '[', S_ARR_FIRST, A_OPEN_ARR);
+        set(st, '"', S_STR, A_STR_START);
+        set(st, '-', S_NMINUS, A_NUM_START);
+        set(st, '0', S_NZERO, A_NUM_START);
+        for (uint32_t c = '1'; c <= '9'; c++) set(st, c, S_NINT, A_NUM_START);
+        set(st, 't', S_T1, A_LIT_T);
+        set(st, 'f', S_F1, A_LIT_F);
+        set(st, 'n', S_N1, A_LIT_N);
+    }
+    set(S_ARR_FIRST, ']', S_AFTER, A_CLOSE_ARR_EMPTY);
+    for (uint8_t w : ws) set(S_AFTER, w, S_AFTER, A_NONE);
+    set(S_AFTER, ',', S_VALUE, A_COMMA);
+    set(S_AFTER, '}', S_AFTER, A_CLOSE_OBJ);
+    set(S_AFTER, ']', S_AFTER, A_CLOSE_ARR);
+    for (uint32_t st : {(uint32_t)S_OBJ_FIRST, (uint32_t)S_OBJ_KEY}) {
+        for (uint8_t w : ws) set(st, w, st, A_NONE);
+        set(st, '"', S_KSTR, A_KEY_START);
+    }
+    set(S_OBJ_FIRST, '}', S_AFTER, A_CLOSE_OBJ);
+    for (uint8_t w : ws) set(S_COLON, w, S_COLON, A_NONE);
+    set(S_COLON, ':', S_VALUE, A_NONE);
+    // strings (value strings and key strings have the same grammar; keys report their end differently)
+    for (int k = 0; k < 2; k++) {
+        const uint32_t str = k ? S_KSTR : S_STR, esc = k ? S_KESC : S_ESC, u1 = k ? S_KU1 : S_U1;
+        for (uint32_t c = 0x20; c < 256; c++) set(str, c, str, A_NONE);
+        set(str, '"', k ? S_COLON : S_AFTER, k ? A_KEY_END : A_STR_END);
+        set(str, 0x5c, esc, k ? A_KEY_ESC : A_NONE);
+        for (char c : {'"', '\\', '/', 'b', 'f', 'n', 'r', 't'}) set(esc, (uint8_t)c, str, A_NONE);
+        set(esc, 'u', u1, A_NONE);
+        for (uint32_t j = 0; j < 4; j++)
+            for (uint32_t c = 0; c < 256; c++)
+                if (is_hex(c)) set(u1 + j, c, j == 3 ? str : u1 + j + 1, A_NONE);
+    }
+    // numbers
+    set(S_NMINUS, '0', S_NZERO, A_NONE);
+    for (uint32_t c = '1'; c <= '9'; c++) set(S_NMINUS, c, S_NINT, A_NONE);
+    for (uint32_t c = '0'; c <= '9'; c++) {
+        set(S_NINT, c, S_NINT, A_NONE);
+        set(S_NDOT, c, S_NFRAC, A_NONE);
+        set(S_NFRAC, c, S_NFRAC, A_NONE);
+        set(S_NE, c, S_NEXP, A_NONE);
+        set(S_NESIGN, c, S_NEXP, A_NONE);
+        set(S_NEXP, c, S_NEXP, A_NONE);
+    }
+    set(S_NZERO, '.', S_NDOT, A_NONE);
+    set(S_NINT, '.', S_NDOT, A_NONE);
+    for (uint32_t st : {(uint32_t)S_NZERO, (uint32_t)S_NINT, (uint32_t)S_NFRAC}) { set(st, 'e', S_NE, A_NONE); set(st, 'E', S_NE, A_NONE); }
+    set(S_NE, '+', S_NESIGN, A_NONE);
+    set(S_NE, '-', S_NESIGN, A_NONE);
+    for (uint32_t st : {(uint32_t)S_NZERO, (uint32_t)S_NINT, (uint32_t)S_NFRAC, (uint32_t)S_NEXP}) {   // a number ends at a delimiter
+        for (uint8_t w : ws) set(st, w, S_AFTER, A_NUM_END);
+        set(st, ',', S_VALUE, A_NUM_END_COMMA);
+        set(st, '}', S_AFTER, A_NUM_END_CLOSE_OBJ);
+        set(st, ']', S_AFTER, A_NUM_END_CLOSE_ARR);
+    }
+    // literals
+    set(S_T1, 'r', S_T2, A_NONE); set(S_T2, 'u', S_T3, A_NONE); set(S_T3, 'e', S_AFTER, A_NONE);
+    set(S_F1, 'a', S_F2, A_NONE); set(S_F2, 'l', S_F3, A_NONE); set(S_F3, 's', S_F4, A_NONE); set(S_F4, 'e', S_AFTER, A_NONE);
+    set(S_N1, 'u', S_N2, A_NONE); set(S_N2, 'l', S_N3, A_NONE); set(S_N3, 'l', S_AFTER, A_NONE);
+}
+
+// Which of the four names the path reads does the key text[s,e) spell?  Escapes are legal in keys
+// ("choices"), so a key that contains a backslash is decoded character by character.
+SS_DEV uint32_t match_key(const uint8_t *t, uint32_t s, uint32_t e, bool has_esc) {
+    if (!has_esc) {
+        const uint32_t len = e - s;
+        if (len != 1u && len != 5u && len != 7u) return KEY_NONE;
+        uint32_t cand = len == 7u ? ((1u << KEY_CHOICES) | (1u << KEY_CONTENT)) : len == 5u ? (1u << KEY_DELTA) : (1u << KEY_ZERO);
+        for (uint32_t i = 0; i < len; i++) {
+            const uint32_t c = t[s + i];
+#pragma unroll
+            for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
+                if (name_char(k, i) != c) cand &= ~(1u << k);
+        }
+#pragma unroll
+        for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
+            if ((cand >> k) & 1u) return k;
+        return KEY_NONE;
+    }
+    uint32_t cand = 0x1e, kpos = 0, i = s;
+    while (i < e) {
+        uint32_t c = t[i++];
+        if (c == 0x5c) {
+            const uint32_t x = t[i++];
+            if (x == 'u') {
+                c = ((uint32_t)hexval(t[i]) << 12) | ((uint32_t)hexval(t[i + 1]) << 8) | ((uint32_t)hexval(t[i + 2]) << 4) |
+                    (uint32_t)hexval(t[i + 3]);
+                i += 4;
+                if (c == 0) c = 0xffffu;   // never equal to the zero padding of a name
+            } else {
+                c = x == 'b' ? 8u : x == 'f' ? 12u : x == 'n' ? 10u : x == 'r' ? 13u : x == 't' ? 9u : x;
+            }
+        }
+#pragma unroll
+        for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
+            if (name_char(k, kpos) != c) cand &= ~(1u << k);
+        kpos++;
+    }
+#pragma unroll
+    for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
+        if (((cand >> k) & 1u) && kpos == name_len(k)) return k;
+    return KEY_NONE;
+}
+
+SS_DEV uint32_t number_flags(const uint8_t *t, uint32_t s, uint32_t e) {
+    uint32_t f = 0;
+    bool mant = true;
+    for (uint32_t i = s; i < e; i++) {
+        const uint32_t c = t[i];
+        if (c == '.') f |= NF_FRAC;
+        else if (c == 'e' || c == 'E') { f |= NF_EXP; mant = false; }
+        else if (mant && c >= '1' && c <= '9') f |= NF_NONZERO;
+    }
+    return f;
+}
+
 struct Result {
     uint32_t status, len;
 };
 
-// text = chunk bytes, n = length, kind = SX_KIND_*, out = at least `cap` writable bytes
-SS_DEV Result extract_chunk(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap) {
+// text = chunk bytes, n = length, kind = SX_KIND_*, out = at least `cap` writable bytes, T = build_table()
+SS_DEV Result extract_chunk(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap, const uint16_t *T) {
     // ---- utils.ts:16-27: prefix test and split('data:')[1] ------------------
     uint32_t pos = 0, end = n;
-    bool prefixed = n >= 5 && text[0] == 'd' && text[1] == 'a' && text[2] == 't' && text[3] == 'a' && text[4] == ':';
+    const bool prefixed = n >= 5 && text[0] == 'd' && text[1] == 'a' && text[2] == 't' && text[3] == 'a' && text[4] == ':';
     if (prefixed) pos = 5;
 
     Val tv[6];
@@ -198,233 +342,93 @@ SS_DEV Result extract_chunk(const uint8_t *text, uint32_t n, uint32_t kind, uint
     uint64_t stack = 0;                  // bit d-1: container at depth d is an object
     uint32_t lastkey = KEY_NONE;
     bool act2 = false, act3 = false, act4 = false, first2 = false;
-    bool str_is_key = false;
-    uint32_t cand = 0, kpos = 0, ucode = 0;   // key matching
-    uint32_t cur = T_NONE;               // tracked slot of the value being scanned (string/number/literal)
+    bool key_esc = false;
+    uint32_t cur = T_NONE;               // tracked slot of the string/number being scanned
     uint32_t last_started = T_NONE;      // tracked slot of the most recently started value (array emptiness)
-    uint32_t lit_word = 0, lit_pos = 0;  // literal matching: 0 true, 1 false, 2 null
-    uint32_t nflags = 0, vstart = 0;
+    uint32_t vstart = 0;
     bool too_deep = false;
 
-    // which tracked slot does a value that starts now belong to?
-#define SX_SLOT_OF_NEW_VALUE()                                                                         \
-    (depth == 0 ? T_ROOT                                                                               \
-     : depth == 1 && ((stack >> 0) & 1) && lastkey == KEY_CHOICES ? T_CHOICES                          \
-     : depth == 1 && ((stack >> 0) & 1) && lastkey == KEY_CONTENT ? T_RCONTENT                         \
-     : depth == 2 && act2 && (((stack >> 1) & 1) ? lastkey == KEY_ZERO : first2) ? T_ELEM0             \
-     : depth == 3 && act3 && lastkey == KEY_DELTA ? T_DELTA                                            \
-     : depth == 4 && act4 && lastkey == KEY_CONTENT ? T_CONTENT                                        \
-     : T_NONE)
-    // a tracked value is (re)assigned: it and everything below it start over (duplicate keys: last wins)
-#define SX_BEGIN_TRACKED(slot, k)                                                                       \
-    do {                                                                                               \
-        if ((slot) != T_NONE) {                                                                        \
-            tv[slot].kind = (k); tv[slot].s = pos; tv[slot].e = pos; tv[slot].flags = 0;               \
-            if ((slot) == T_CHOICES) { tv[T_ELEM0].kind = tv[T_DELTA].kind = tv[T_CONTENT].kind = V_ABSENT; act2 = act3 = act4 = false; } \
-            if ((slot) == T_ELEM0) { tv[T_DELTA].kind = tv[T_CONTENT].kind = V_ABSENT; act3 = act4 = false; } \
-            if ((slot) == T_DELTA) { tv[T_CONTENT].kind = V_ABSENT; act4 = false; }                    \
-        }                                                                                              \
-        if (depth == 2 && act2 && !((stack >> 1) & 1)) first2 = false;                                 \
-        last_started = (slot);                                                                         \
-    } while (0)
-
-    for (;; pos++) {
-        uint32_t c;
-        bool at_end = pos >= end;
-        if (!at_end && prefixed && pos + 5 <= n && text[pos] == 'd' && text[pos + 1] == 'a' && text[pos + 2] == 't' &&
-            text[pos + 3] == 'a' && text[pos + 4] == ':') {
-            at_end = true;               // the second 'data:' ends split()[1], wherever it falls
-            end = pos;
+    for (; pos < end; pos++) {
+        const uint32_t c = text[pos];
+        if (c == 'd' && prefixed && pos + 5 <= n && text[pos + 1] == 'a' && text[pos + 2] == 't' && text[pos + 3] == 'a' &&
+            text[pos + 4] == ':') {
+            end = pos;                   // the second 'data:' ends split()[1], wherever it falls
+            break;
         }
-        c = at_end ? 0x100u : text[pos];
-
-        // a number ends at the first character that cannot continue it
-        if (state == S_NZERO || state == S_NINT || state == S_NFRAC || state == S_NEXP) {
-            bool cont = false;
-            if (!at_end) {
-                if (state == S_NINT && is_digit(c)) cont = true;
-                else if ((state == S_NZERO || state == S_NINT) && c == '.') cont = true;
-                else if ((state == S_NZERO || state == S_NINT || state == S_NFRAC) && (c == 'e' || c == 'E')) cont = true;
-                else if ((state == S_NFRAC || state == S_NEXP) && is_digit(c)) cont = true;
+        const uint32_t ent = T[state * 256u + c];
+        uint32_t next = ent & 63u;
+        uint32_t act = ent >> 6;
+        if (act != A_NONE) {
+            // a number that ends here first closes itself, then the delimiter acts as it would after any value
+            if (act >= A_NUM_END) {
+                if (cur != T_NONE) { tv[cur].e = pos; tv[cur].flags = number_flags(text, tv[cur].s, pos); }
+                act = act == A_NUM_END ? A_NONE : act == A_NUM_END_COMMA ? A_COMMA : act == A_NUM_END_CLOSE_OBJ ? A_CLOSE_OBJ : A_CLOSE_ARR;
             }
-            if (!cont) {
-                if (cur != T_NONE) { tv[cur].e = pos; tv[cur].flags = nflags; }
-                state = S_AFTER;
-            }
-        }
-        if (at_end) break;
-
-        switch (state) {
-            case S_VALUE:
-            case S_ARR_FIRST: {
-                if (is_ws(c)) break;
-                if (state == S_ARR_FIRST && c == ']') {
-                    if (last_started != T_NONE && tv[last_started].kind == V_ARRAY) tv[last_started].flags |= AF_EMPTY;
-                    depth--;
-                    if (depth < 2) act2 = false;
-                    if (depth < 3) act3 = false;
-                    if (depth < 4) act4 = false;
-                    state = S_AFTER;
-                    break;
+            if (act >= A_OPEN_OBJ && act <= A_LIT_N) {
+                // ---- a value starts: is it one of the values the provider branches read? ----
+                const uint32_t slot =
+                    depth == 0 ? T_ROOT
+                    : depth == 1 && ((stack >> 0) & 1) && lastkey == KEY_CHOICES ? T_CHOICES
+                    : depth == 1 && ((stack >> 0) & 1) && lastkey == KEY_CONTENT ? T_RCONTENT
+                    : depth == 2 && act2 && (((stack >> 1) & 1) ? lastkey == KEY_ZERO : first2) ? T_ELEM0
+                    : depth == 3 && act3 && lastkey == KEY_DELTA ? T_DELTA
+                    : depth == 4 && act4 && lastkey == KEY_CONTENT ? T_CONTENT
+                    : T_NONE;
+                const uint32_t vk = act == A_OPEN_OBJ ? V_OBJECT : act == A_OPEN_ARR ? V_ARRAY : act == A_STR_START ? V_STRING
+                                  : act == A_NUM_START ? V_NUMBER : act == A_LIT_T ? V_TRUE : act == A_LIT_F ? V_FALSE : V_NULL;
+                if (slot != T_NONE) {      // (re)assigned: it and everything below start over (duplicate keys: last wins)
+                    tv[slot].kind = vk; tv[slot].s = pos; tv[slot].e = pos; tv[slot].flags = 0;
+                    if (slot == T_CHOICES) { tv[T_ELEM0].kind = tv[T_DELTA].kind = tv[T_CONTENT].kind = V_ABSENT; act2 = act3 = act4 = false; }
+                    if (slot == T_ELEM0) { tv[T_DELTA].kind = tv[T_CONTENT].kind = V_ABSENT; act3 = act4 = false; }
+                    if (slot == T_DELTA) { tv[T_CONTENT].kind = V_ABSENT; act4 = false; }
                 }
-                const uint32_t slot = SX_SLOT_OF_NEW_VALUE();
-                if (c == '{' || c == '[') {
-                    const bool obj = c == '{';
-                    SX_BEGIN_TRACKED(slot, obj ? V_OBJECT : V_ARRAY);
+                if (depth == 2 && act2 && !((stack >> 1) & 1)) first2 = false;
+                last_started = slot;
+                cur = slot;
+                if (act == A_OPEN_OBJ || act == A_OPEN_ARR) {
+                    const bool obj = act == A_OPEN_OBJ;
                     if (depth >= 64) { too_deep = true; state = S_ERR; break; }
                     stack = (stack & ~(1ull << depth)) | ((uint64_t)(obj ? 1 : 0) << depth);
                     depth++;
                     if (slot == T_CHOICES) { act2 = true; first2 = !obj; }
                     if (slot == T_ELEM0) act3 = obj;
                     if (slot == T_DELTA) act4 = obj;
-                    state = obj ? S_OBJ_FIRST : S_ARR_FIRST;
-                } else if (c == '"') {
-                    SX_BEGIN_TRACKED(slot, V_STRING);
-                    cur = slot; str_is_key = false; vstart = pos + 1;
-                    state = S_STR;
-                } else if (c == '-' || is_digit(c)) {
-                    SX_BEGIN_TRACKED(slot, V_NUMBER);
-                    cur = slot; nflags = (c >= '1' && c <= '9') ? NF_NONZERO : 0;
-                    state = c == '-' ? S_NMINUS : c == '0' ? S_NZERO : S_NINT;
-                } else if (c == 't' || c == 'f' || c == 'n') {
-                    lit_word = c == 't' ? 0 : c == 'f' ? 1 : 2;
-                    SX_BEGIN_TRACKED(slot, lit_word == 0 ? V_TRUE : lit_word == 1 ? V_FALSE : V_NULL);
-                    cur = slot; lit_pos = 1;
-                    state = S_LIT;
-                } else {
-                    state = S_ERR;
+                } else if (act == A_STR_START) {
+                    vstart = pos + 1;
                 }
-                break;
-            }
-            case S_LIT: {
-                const char *w = lit_word == 0 ? "true" : lit_word == 1 ? "false" : "null";
-                const uint32_t wl = lit_word == 1 ? 5u : 4u;
-                if (c != (uint32_t)(uint8_t)w[lit_pos]) { state = S_ERR; break; }
-                lit_pos++;
-                if (lit_pos == wl) state = S_AFTER;
-                break;
-            }
-            case S_AFTER: {
-                if (is_ws(c)) break;
-                if (depth == 0) { state = S_ERR; break; }
-                const bool in_obj = (stack >> (depth - 1)) & 1;
-                if (c == ',') state = in_obj ? S_OBJ_KEY : S_VALUE;
-                else if ((c == '}' && in_obj) || (c == ']' && !in_obj)) {
+            } else if (act == A_KEY_START) {
+                vstart = pos + 1; key_esc = false;
+            } else if (act == A_KEY_ESC) {
+                key_esc = true;
+            } else if (act == A_KEY_END) {
+                lastkey = match_key(text, vstart, pos, key_esc);
+            } else if (act == A_STR_END) {
+                if (cur != T_NONE) { tv[cur].s = vstart; tv[cur].e = pos; }
+            } else if (act == A_COMMA) {
+                if (depth == 0) next = S_ERR;
+                else next = ((stack >> (depth - 1)) & 1) ? S_OBJ_KEY : S_VALUE;
+            } else if (act == A_CLOSE_OBJ || act == A_CLOSE_ARR || act == A_CLOSE_ARR_EMPTY) {
+                const bool want_obj = act == A_CLOSE_OBJ;
+                if (depth == 0 || (((stack >> (depth - 1)) & 1) != 0) != want_obj) next = S_ERR;
+                else {
+                    if (act == A_CLOSE_ARR_EMPTY && last_started != T_NONE && tv[last_started].kind == V_ARRAY)
+                        tv[last_started].flags |= AF_EMPTY;
                     depth--;
                     if (depth < 2) act2 = false;
                     if (depth < 3) act3 = false;
                     if (depth < 4) act4 = false;
-                } else state = S_ERR;
-                break;
-            }
-            case S_OBJ_FIRST:
-            case S_OBJ_KEY: {
-                if (is_ws(c)) break;
-                if (c == '"') { str_is_key = true; cand = 0x1e; kpos = 0; state = S_STR; }
-                else if (c == '}' && state == S_OBJ_FIRST) {
-                    depth--;
-                    if (depth < 2) act2 = false;
-                    if (depth < 3) act3 = false;
-                    if (depth < 4) act4 = false;
-                    state = S_AFTER;
-                } else state = S_ERR;
-                break;
-            }
-            case S_COLON: {
-                if (is_ws(c)) break;
-                state = c == ':' ? S_VALUE : S_ERR;
-                break;
-            }
-            case S_STR: {
-                if (c == '"') {
-                    if (str_is_key) {
-                        lastkey = KEY_NONE;
-#pragma unroll
-                        for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
-                            if (((cand >> k) & 1) && kpos == name_len(k)) lastkey = k;
-                        state = S_COLON;
-                    } else {
-                        if (cur != T_NONE) { tv[cur].s = vstart; tv[cur].e = pos; }
-                        state = S_AFTER;
-                    }
-                } else if (c == 0x5c) state = S_ESC;
-                else if (c < 0x20) state = S_ERR;
-                else if (str_is_key) {
-#pragma unroll
-                    for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
-                        if (name_char(k, kpos) != c) cand &= ~(1u << k);
-                    kpos++;
+                    next = S_AFTER;
                 }
-                break;
             }
-            case S_ESC: {
-                uint32_t dc = 0xffffffffu;
-                if (c == '"' || c == 0x5c || c == '/') dc = c;
-                else if (c == 'b') dc = 8; else if (c == 'f') dc = 12; else if (c == 'n') dc = 10;
-                else if (c == 'r') dc = 13; else if (c == 't') dc = 9;
-                else if (c == 'u') { ucode = 0; state = S_U1; break; }
-                if (dc == 0xffffffffu) { state = S_ERR; break; }
-                if (str_is_key) {
-#pragma unroll
-                    for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
-                        if (name_char(k, kpos) != dc) cand &= ~(1u << k);
-                    kpos++;
-                }
-                state = S_STR;
-                break;
-            }
-            case S_U1: case S_U2: case S_U3: case S_U4: {
-                const int h = hexval(c);
-                if (h < 0) { state = S_ERR; break; }
-                ucode = (ucode << 4) | (uint32_t)h;
-                if (state == S_U4) {
-                    if (str_is_key) {
-#pragma unroll
-                        for (uint32_t k = KEY_CHOICES; k <= KEY_ZERO; k++)
-                            if (name_char(k, kpos) != ucode || ucode == 0) cand &= ~(1u << k);
-                        kpos++;
-                    }
-                    state = S_STR;
-                } else state = state + 1;
-                break;
-            }
-            case S_NMINUS:
-                if (c == '0') state = S_NZERO;
-                else if (c >= '1' && c <= '9') { nflags |= NF_NONZERO; state = S_NINT; }
-                else state = S_ERR;
-                break;
-            case S_NZERO:   // continuation characters only ('.', e/E) reach here
-            case S_NINT:
-                if (is_digit(c)) { /* S_NINT digit */ }
-                else if (c == '.') { nflags |= NF_FRAC; state = S_NDOT; }
-                else { nflags |= NF_EXP; state = S_NE; }
-                break;
-            case S_NDOT:
-                if (is_digit(c)) { if (c != '0') nflags |= NF_NONZERO; state = S_NFRAC; }
-                else state = S_ERR;
-                break;
-            case S_NFRAC:
-                if (is_digit(c)) { if (c != '0') nflags |= NF_NONZERO; }
-                else { nflags |= NF_EXP; state = S_NE; }
-                break;
-            case S_NE:
-                if (c == '+' || c == '-') state = S_NESIGN;
-                else if (is_digit(c)) state = S_NEXP;
-                else state = S_ERR;
-                break;
-            case S_NESIGN:
-                state = is_digit(c) ? S_NEXP : S_ERR;
-                break;
-            case S_NEXP:
-                break;  // digits only reach here
-            default:
-                state = S_ERR;
-                break;
         }
+        state = next;
         if (state == S_ERR) break;
     }
-#undef SX_SLOT_OF_NEW_VALUE
-#undef SX_BEGIN_TRACKED
+    // a number may also end with the input
+    if (state == S_NZERO || state == S_NINT || state == S_NFRAC || state == S_NEXP) {
+        if (cur != T_NONE) { tv[cur].e = end; tv[cur].flags = number_flags(text, tv[cur].s, end); }
+        state = S_AFTER;
+    }
 
     Result res;
     res.status = SX_OK;

@@ -67,8 +67,11 @@ __global__ void __launch_bounds__(128) ss_run_commit_kernel(const SsDesc *desc, 
 // OK) and the delta bytes at delta_arena + in_off (the plaintext layout, so no
 // allocation or scratch is needed: every frame slot holds >= max(16, mlen) bytes).
 #define SS_EXTRACT_THREADS 64
-#define SS_EXTRACT_STAGE 512u                      // chunks up to this size are staged in shared memory
-#define SS_EXTRACT_STRIDE (SS_EXTRACT_STAGE + 4u)  // 129 words: lanes hit distinct banks
+#define SS_EXTRACT_STAGE 384u                      // chunks up to this size are staged in shared memory
+#define SS_EXTRACT_STRIDE (SS_EXTRACT_STAGE + 4u)  // 97 words: lanes hit distinct banks
+#define SS_EXTRACT_SMEM (SX_TABLE_ENTRIES * 2u + SS_EXTRACT_THREADS * SS_EXTRACT_STRIDE)
+// The automaton's transition table (sx::build_table), uploaded once per device by symrelay_create.
+static __device__ __align__(16) uint16_t g_sx_table[SX_TABLE_ENTRIES];
 __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const SsDesc *desc, uint32_t n, const uint8_t *in,
                                                                        const uint4 *states, uint32_t *status,
                                                                        symrelay_delta *delta, uint8_t *delta_arena) {
@@ -76,7 +79,15 @@ __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const Ss
     // global memory that is ~600 cycles per byte (measured: 72 us for 16,384 chunks of ~216 B).  So each
     // thread first pulls its chunk into a private slice of shared memory with 16-byte loads that are all
     // in flight together, and the byte loop then runs against shared memory.
-    extern __shared__ __align__(16) uint8_t sx_stage[];
+    extern __shared__ __align__(16) uint8_t sx_smem[];
+    uint16_t *table = reinterpret_cast<uint16_t *>(sx_smem);
+    uint8_t *sx_stage = sx_smem + SX_TABLE_ENTRIES * 2u;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(g_sx_table);
+        uint4 *dst = reinterpret_cast<uint4 *>(table);
+        for (uint32_t j = threadIdx.x; j < SX_TABLE_ENTRIES * 2u / 16u; j += blockDim.x) dst[j] = src[j];
+    }
+    __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const SsDesc d = desc[i];
@@ -97,7 +108,7 @@ __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const Ss
         }
         text = mine;
     }
-    const sx::Result r = sx::extract_chunk(text, mlen, kind, delta_arena + d.in_off, cap);
+    const sx::Result r = sx::extract_chunk(text, mlen, kind, delta_arena + d.in_off, cap, table);
     status[i] = r.status;
     delta[i].off = d.in_off;
     delta[i].len = r.len;
@@ -323,7 +334,7 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     }
     if (d_delta && d_delta_arena) {
         ss_extract_kernel<<<(n + SS_EXTRACT_THREADS - 1) / SS_EXTRACT_THREADS, SS_EXTRACT_THREADS,
-                            SS_EXTRACT_THREADS * SS_EXTRACT_STRIDE, stream>>>(
+                            SS_EXTRACT_SMEM, stream>>>(
             reinterpret_cast<const SsDesc *>(d_desc), n, d_in, d_states, d_status, d_delta, d_delta_arena);
         ctx->launches++;
     }
@@ -392,6 +403,11 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_in, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_k, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_out, cudaStreamNonBlocking));
+    {
+        std::vector<uint16_t> table(SX_TABLE_ENTRIES);
+        sx::build_table(table.data());
+        CU(ctx, cudaMemcpyToSymbol(g_sx_table, table.data(), SX_TABLE_ENTRIES * sizeof(uint16_t)));
+    }
     sh.init_cap = 4096;
     CU(ctx, cudaHostAlloc(&sh.h_init, sizeof(SsInitRec) * sh.init_cap, cudaHostAllocDefault));
     CU(ctx, cudaMalloc(&sh.d_init, sizeof(SsInitRec) * sh.init_cap));
@@ -724,22 +740,35 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     uint32_t n_bulk = 0;
     const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk);
     if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
-    bool extract = false, runs = false;
+    // bounds / ownership checks: one branch-free pass (this loop is on the per-batch critical path of the
+    // host; the per-descriptor early returns and the modulo it used to have cost ~3 us per 2,048 frames)
+    uint32_t bad = 0, any_flags = 0;
+    const uint32_t max_streams = ctx->opts.max_streams;
+    const uint32_t ng = (uint32_t)ctx->n_gpus;
     for (uint32_t i = 0; i < n; i++) {
-        const uint32_t mlen = desc[i].len_flags & SYMRELAY_LEN_MASK;
-        const bool op = desc[i].len_flags & SYMRELAY_F_OPEN;
-        if (op && (desc[i].len_flags & SYMRELAY_F_RUN)) runs = true;
-        if ((desc[i].len_flags & SYMRELAY_F_EXTRACT) && !op) {
-            extract = true;
-            const uint64_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
-            if ((uint64_t)desc[i].in_off + cap > delta_arena_bytes || (uint64_t)desc[i].in_off + cap > in_bytes)
-                return fail(ctx, SYMRELAY_EINVAL, "descriptor %u: delta slot (in_off + max(16, align16(len))) outside the arenas", i);
+        const symrelay_desc d = desc[i];
+        const uint32_t mlen = d.len_flags & SYMRELAY_LEN_MASK;
+        const uint32_t op = (d.len_flags >> 26) & 1u;   // SYMRELAY_F_OPEN
+        const uint64_t in_end = (uint64_t)d.in_off + mlen + 20u * op;
+        const uint64_t out_end = (uint64_t)d.out_off + mlen + 20u * (1u - op);
+        bad |= (uint32_t)(in_end > in_bytes) | (uint32_t)(out_end > out_bytes) | (uint32_t)(d.slot >= max_streams);
+        any_flags |= d.len_flags;
+    }
+    if (ng > 1)
+        for (uint32_t i = 0; i < n; i++) bad |= (uint32_t)((int)(desc[i].slot % ng) != gpu_index);
+    if (bad) return fail(ctx, SYMRELAY_EINVAL, "a descriptor points outside its arena, names a slot beyond max_streams, or a slot that is not on gpu %d", gpu_index);
+    bool extract = false;
+    const bool runs = (any_flags & SYMRELAY_F_RUN) != 0;
+    if (any_flags & SYMRELAY_F_EXTRACT) {
+        for (uint32_t i = 0; i < n; i++) {
+            const uint32_t mlen = desc[i].len_flags & SYMRELAY_LEN_MASK;
+            if ((desc[i].len_flags & SYMRELAY_F_EXTRACT) && !(desc[i].len_flags & SYMRELAY_F_OPEN)) {
+                extract = true;
+                const uint64_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
+                if ((uint64_t)desc[i].in_off + cap > delta_arena_bytes || (uint64_t)desc[i].in_off + cap > in_bytes)
+                    return fail(ctx, SYMRELAY_EINVAL, "descriptor %u: delta slot (in_off + max(16, align16(len))) outside the arenas", i);
+            }
         }
-        const uint64_t in_end = (uint64_t)desc[i].in_off + mlen + (op ? 20u : 0u);
-        const uint64_t out_end = (uint64_t)desc[i].out_off + mlen + (op ? 0u : 20u);
-        if (in_end > in_bytes || out_end > out_bytes || desc[i].slot >= ctx->opts.max_streams ||
-            (int)(desc[i].slot % (uint32_t)ctx->n_gpus) != gpu_index)
-            return fail(ctx, SYMRELAY_EINVAL, "descriptor %u: frame outside its arena or slot not on gpu %d", i, gpu_index);
     }
     if (extract && (!delta || !delta_arena))
         return fail(ctx, SYMRELAY_EINVAL, "SYMRELAY_F_EXTRACT needs delta and delta_arena");

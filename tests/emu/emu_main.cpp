@@ -71,7 +71,10 @@ extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *til
 // The extractor is thread-local code (no warp collectives): call it directly.
 extern "C" uint32_t emu_extract(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap,
                                 uint32_t *len_out) {
-    const sx::Result r = sx::extract_chunk(text, n, kind, out, cap);
+    static uint16_t table[SX_TABLE_ENTRIES];
+    static bool built = false;
+    if (!built) { sx::build_table(table); built = true; }
+    const sx::Result r = sx::extract_chunk(text, n, kind, out, cap, table);
     *len_out = r.len;
     return r.status;
 }
