@@ -53,7 +53,7 @@ extern "C" {
 /* per-frame status word written by the kernels: bits 0..7 code, bits 8..15 opened tag */
 #define SYMRELAY_ST_OK 0u
 #define SYMRELAY_ST_BAD_MAC 1u            /* pull returned -1: that slot's state is untouched; no plaintext is released
-                                             (frames up to 1,920 B leave `out` untouched, larger ones leave zeros) */
+                                             (the frame's output bytes are left untouched or zeroed) */
 #define SYMRELAY_ST_TOO_SHORT 2u          /* wire frame shorter than 17 bytes after the prefix */
 #define SYMRELAY_ST_EXTRACT_THROW 3u      /* the reference would throw a TypeError here (utils.ts:38-50) */
 #define SYMRELAY_ST_EXTRACT_UNSUPPORTED 4u /* value shape outside the GPU extractor's domain: use the JS helper */

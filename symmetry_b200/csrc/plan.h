@@ -34,23 +34,78 @@ static inline int symrelay_desc_check_inline(const symrelay_desc *d) {
 // tile cutting only walks the block-count array.
 #include <vector>
 
+// Optional bounds checks folded into the planner's first pass (the host batch entry points use them so
+// that the descriptors are walked once, not three times).
+struct symrelay_plan_check {
+    uint64_t in_bytes, out_bytes;
+    uint32_t max_streams;
+    // results
+    uint32_t out_of_bounds;   // some frame leaves its arena or names a slot >= max_streams
+    uint32_t any_flags;       // OR of all len_flags
+    uint32_t out_overlap;     // output rows (16 B) not strictly increasing in descriptor order
+};
+
 static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles,
-                                           uint32_t max_tiles, uint32_t *n_bulk_out) {
+                                           uint32_t max_tiles, uint32_t *n_bulk_out,
+                                           symrelay_plan_check *chk = nullptr) {
     static thread_local std::vector<uint32_t> ncv;
-    if (ncv.size() < n) ncv.resize(n);
+    if (ncv.size() < 3u * (size_t)n) ncv.resize(3u * (size_t)n);
     uint32_t *nc = ncv.data();
-    uint32_t bad = 0;
+    uint32_t *row_lo = nc + n, *row_hi = nc + 2u * (size_t)n;   // output rows in 16-byte units
+    // pass 1: no loop-carried dependency, so the compiler vectorises it
+    // (all 32-bit: offsets are uint32 and arenas are capped just below 4 GiB, so `off > size - need` cannot wrap)
+    uint32_t bad = 0, oob = 0, any_flags = 0, nc_min = 0xffffffffu, nc_max = 0;
+    const uint64_t cap = 0xffffffffull;
+    const uint32_t in_bytes = (uint32_t)(chk && chk->in_bytes < cap ? chk->in_bytes : cap);
+    const uint32_t out_bytes = (uint32_t)(chk && chk->out_bytes < cap ? chk->out_bytes : cap);
+    const uint32_t max_streams = chk ? chk->max_streams : 0xffffffffu;
     for (uint32_t i = 0; i < n; i++) {
-        const uint32_t lf = desc[i].len_flags;
+        const uint32_t lf = desc[i].len_flags, in_off = desc[i].in_off, out_off = desc[i].out_off;
         const uint32_t mlen = lf & SYMRELAY_LEN_MASK;
         const uint32_t op = (lf >> 26) & 1u;   // SYMRELAY_F_OPEN
-        bad |= (uint32_t)(mlen > SYMRELAY_MAX_FRAME) | (uint32_t)((desc[i].in_off & 15u) != 12u * op) |
-               (uint32_t)((desc[i].out_off & 15u) != 12u * (1u - op));
-        nc[i] = 2u + ((mlen + 63u) >> 6);
+        const uint32_t c = 2u + ((mlen + 63u) >> 6);
+        const uint32_t need_in = mlen + 20u * op, need_out = mlen + 20u - 20u * op;
+        bad |= (uint32_t)(mlen > SYMRELAY_MAX_FRAME) | (uint32_t)((in_off & 15u) != 12u * op) |
+               (uint32_t)((out_off & 15u) != 12u - 12u * op);
+        oob |= (uint32_t)(need_in > in_bytes) | (uint32_t)(in_off > in_bytes - need_in) |
+               (uint32_t)(need_out > out_bytes) | (uint32_t)(out_off > out_bytes - need_out) |
+               (uint32_t)(desc[i].slot >= max_streams);
+        any_flags |= lf;
+        nc[i] = c;
+        nc_min = c < nc_min ? c : nc_min;
+        nc_max = c > nc_max ? c : nc_max;
+        row_lo[i] = out_off >> 4;
+        row_hi[i] = (out_off >> 4) + (((out_off & 15u) + need_out + 15u) >> 4);
+    }
+    if (chk) {
+        // output rows strictly increasing in descriptor order?  (plain arrays: vectorises without gathers)
+        uint32_t overlap = 0;
+        for (uint32_t i = 1; i < n; i++) overlap |= (uint32_t)(row_lo[i] < row_hi[i - 1]);
+        chk->out_of_bounds = oob; chk->any_flags = any_flags; chk->out_overlap = overlap;
     }
     if (bad) return SYMRELAY_EINVAL;
     uint64_t n_tiles = 0;
     uint32_t n_bulk = 0;
+    if (n && nc_min == nc_max && nc_max <= 32u) {
+        // every frame has the same block count (token streaming, BASELINE config 2): the tiles follow in
+        // closed form -- no per-descriptor walk
+        const bool thread_ok = n >= SYMRELAY_THREAD_TILE_MIN_FRAMES && nc_max <= SYMRELAY_THREAD_TILE_MAX_BLOCKS;
+        uint32_t per = 32u / nc_max;
+        if (per > 16u) per = 16u;
+        uint32_t i = 0;
+        if (thread_ok)
+            for (; i + 32u <= n; i += 32u) {
+                if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = 32u | (1u << 17); }
+                n_tiles++;
+            }
+        for (; i < n; i += per) {
+            const uint32_t k = n - i < per ? n - i : per;
+            if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = k; }
+            n_tiles++;
+        }
+        if (n_bulk_out) *n_bulk_out = 0;
+        return (int64_t)n_tiles;
+    }
     uint32_t run_first = 0, run_n = 0, run_blocks = 0;
     const bool thread_tiles = n >= SYMRELAY_THREAD_TILE_MIN_FRAMES;
     for (uint32_t i = 0; i < n; i++) {

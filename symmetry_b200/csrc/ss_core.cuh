@@ -36,6 +36,14 @@ SS_DEV uint32_t ss_shfl_up(uint32_t v, uint32_t d) { return __shfl_up_sync(0xfff
 SS_DEV uint32_t ss_shfl_down(uint32_t v, uint32_t d) { return __shfl_down_sync(0xffffffffu, v, d); }
 SS_DEV uint32_t ss_reduce_or(uint32_t v) { return __reduce_or_sync(0xffffffffu, v); }
 SS_DEV uint32_t ss_reduce_max(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
+SS_DEV uint32_t ss_reduce_min(uint32_t v) { return __reduce_min_sync(0xffffffffu, v); }
+SS_DEV void ss_syncwarp() { __syncwarp(); }
+#define SS_STAGE_BYTES 2048u
+// per-warp staging window in shared memory (packed tiles, see ss_process_tile)
+SS_DEV uint4 *ss_stage_buffer() {
+    __shared__ __align__(16) uint4 stage[4][SS_STAGE_BYTES / 16u];
+    return stage[(threadIdx.x >> 5) & 3u];
+}
 SS_DEV uint32_t ss_popc(uint32_t v) { return (uint32_t)__popc(v); }
 SS_DEV uint32_t ss_clz(uint32_t v) { return (uint32_t)__clz((int)v); }
 SS_DEV uint32_t ss_rotl16(uint32_t x) { return __byte_perm(x, 0, 0x1032); }
@@ -58,6 +66,8 @@ SS_DEV void ss_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #endif
 
 #define SS_ARG_INPUT_INDEPENDENT 1u  // SsArgs.flags: desc/tiles/in were not written by the preceding kernel
+#define SS_ARG_STAGE_INPUT 2u        // SsArgs.flags: pull each packed tile's input through shared memory
+#define SS_ARG_STAGE_OUTPUT 4u       // SsArgs.flags: assemble each packed tile's output in shared memory, store whole lines
 
 #define SS_F_OPEN 0x04000000u
 #define SS_F_EXTRACT 0x08000000u
@@ -318,7 +328,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
         d_slot = d.slot; d_in = d.in_off; d_out = d.out_off; d_lf = d.len_flags;
         my_nc = 2u + (((d_lf & 0xffffffu) + 63u) >> 6);
     }
-    uint32_t f = 0, st = 0;
+    uint32_t f = 0, st = 0, my_start = 0;
     bool valid = true;
     if (!BULK) {
         uint32_t incl = my_nc;
@@ -327,6 +337,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
             const uint32_t t = ss_shfl_up(incl, o);
             if (lane >= o) incl += t;
         }
+        my_start = incl - my_nc;   // first lane of frame #lane (meaningful for lane < nfr)
         const uint32_t startmask = ss_reduce_or(lane < nfr ? (1u << (incl - my_nc)) : 0u);
         const uint32_t total = ss_shfl(incl, 31);
         const uint32_t below = startmask & (0xffffffffu >> (31u - lane));
@@ -345,7 +356,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
     const uint32_t T = 80u + mlen + (mlen & 15u);          // MAC input bytes (libsodium pad quirk)
     const uint32_t NB = (T + 15u) >> 4;                    // Poly1305 blocks
     const uint32_t V = 64u + mlen;                         // LE64(64+mlen) sits at stream offset T-8
-    const uint8_t *src = a.in + in_off + (is_open ? 4u : 0u);   // payload in  (16-aligned)
+    const uint8_t *src = a.in + in_off + (is_open ? 4u : 0u);   // payload in  (16-aligned)  [may be re-pointed at the staged copy]
     uint8_t *dst = a.out + out_off + (is_open ? 0u : 4u);       // payload out (16-aligned)
     uint4 *sp = a.states + ((size_t)slot * 2u + (is_open ? 1u : 0u)) * 3u;
 
@@ -359,9 +370,33 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
     const bool pre_payload = !BULK && valid && b_first >= 2u && b_first < nc;
     const int pre_cbytes = pre_payload ? ((int)(mlen - 64u * (b_first - 2u)) < 64 ? (int)(mlen - 64u * (b_first - 2u)) : 64) : 0;
     const bool early = !BULK && (a.flags & SS_ARG_INPUT_INDEPENDENT);
+    // Zero-copy batches read the arena over PCIe, where the 16-byte-per-lane pattern below turns into
+    // 32-byte requests and the link, not the SMs, sets the pace.  When all frames of the tile sit in one
+    // window of <= 2 KiB (they do when the scheduler wrote them back to back) the warp fetches that window
+    // with fully coalesced 512-byte loads into shared memory and every later read comes from there.
+    const uint8_t *in_base = a.in;
+    if (!BULK && (a.flags & SS_ARG_STAGE_INPUT)) {
+        const uint32_t f_lo = (is_open ? in_off - 12u : in_off) & ~15u;
+        const uint32_t f_hi = in_off + mlen + (is_open ? 20u : 0u);
+        const uint32_t w_lo = ss_reduce_min(valid ? f_lo : 0xffffffffu);
+        const uint32_t w_hi = ss_reduce_max(valid ? f_hi : 0u);
+        if (w_hi > w_lo && w_hi - w_lo <= SS_STAGE_BYTES) {   // warp-uniform
+            uint4 *stage = ss_stage_buffer();
+            const uint4 *g = reinterpret_cast<const uint4 *>(a.in + w_lo);
+            const uint32_t pieces = (w_hi - w_lo + 15u) >> 4;
+#pragma unroll
+            for (uint32_t i = 0; i < SS_STAGE_BYTES / 512u; i++) {
+                const uint32_t p = lane + 32u * i;
+                if (p < pieces) stage[p] = g[p];
+            }
+            ss_syncwarp();
+            in_base = reinterpret_cast<const uint8_t *>(stage) - w_lo;
+            src = in_base + in_off + (is_open ? 4u : 0u);
+        }
+    }
     if (early) {
         ss_load64(src + 64u * (size_t)(pre_payload ? b_first - 2u : 0u), pre_cbytes, m);
-        if (valid && is_open && b_first == 1u) hw = *reinterpret_cast<const uint32_t *>(a.in + in_off);
+        if (valid && is_open && b_first == 1u) hw = *reinterpret_cast<const uint32_t *>(in_base + in_off);
         if (valid && is_open && b_first == 0u) ss_load_mac(src + mlen, wmac);
     }
     ss_pdl_wait();   // from here on we touch what the previous kernel may have written
@@ -391,9 +426,40 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
     if (!early) {
         if (!BULK) {
             ss_load64(src + 64u * (size_t)(pre_payload ? b_first - 2u : 0u), pre_cbytes, m);
-            if (valid && is_open && b_first == 1u) hw = *reinterpret_cast<const uint32_t *>(a.in + in_off);
+            if (valid && is_open && b_first == 1u) hw = *reinterpret_cast<const uint32_t *>(in_base + in_off);
         }
         if (!BULK && valid && is_open && lane == st) ss_load_mac(src + mlen, wmac);   // the wire tag, long before it is compared
+    }
+
+    // Output side of the same idea: over PCIe, 16-byte stores at a 64-byte stride (plus 4-byte headers,
+    // tags and status words) leave as tiny write transactions.  When the tile's outputs share one
+    // <= 2 KiB window the lanes assemble them in shared memory (the input copy is no longer needed: every
+    // lane holds its input in registers by now) and the warp stores the window in whole 512-byte rows.
+    // Bytes between the frames of that window are written as zeros, which the host-arena entry points
+    // allow (they never promised to preserve gaps).
+    uint8_t *out_base = a.out;
+    bool out_staged = false;
+    uint32_t ow_lo = 0, ow_pieces = 0;
+    if (!BULK && (a.flags & SS_ARG_STAGE_OUTPUT)) {
+        const uint32_t o_lo = (is_open ? out_off : out_off - 12u) & ~15u;
+        const uint32_t o_hi = out_off + mlen + (is_open ? 0u : 20u);
+        const uint32_t w_lo = ss_reduce_min(valid ? o_lo : 0xffffffffu);
+        const uint32_t w_hi = ss_reduce_max(valid ? o_hi : 0u);
+        if (w_hi > w_lo && w_hi - w_lo <= SS_STAGE_BYTES) {   // warp-uniform
+            uint4 *stage = ss_stage_buffer();
+            ow_lo = w_lo;
+            ow_pieces = (w_hi - w_lo + 15u) >> 4;
+            ss_syncwarp();   // all reads of the staged input are done
+            uint4 zero;
+            zero.x = zero.y = zero.z = zero.w = 0;
+#pragma unroll
+            for (uint32_t i = 0; i < SS_STAGE_BYTES / 512u; i++)
+                if (lane + 32u * i < ow_pieces) stage[lane + 32u * i] = zero;
+            ss_syncwarp();
+            out_base = reinterpret_cast<uint8_t *>(stage) - w_lo;
+            dst = out_base + out_off + (is_open ? 0u : 4u);
+            out_staged = true;
+        }
     }
 
     uint32_t A[5] = {0, 0, 0, 0, 0};   // lane partial, to be scaled by r^E
@@ -456,7 +522,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
                 if (!is_open) {
                     x[0] ^= (lf >> 24) & 3u;                        // (tag ‖ 0^63) ^ keystream
                     tagval = x[0] & 0xffu;
-                    *reinterpret_cast<uint32_t *>(a.out + out_off) = (mlen + 17u) | (tagval << 24);
+                    *reinterpret_cast<uint32_t *>(out_base + out_off) = (mlen + 17u) | (tagval << 24);
                 } else {
                     const uint32_t c0 = hw >> 24;
                     tagval = (x[0] ^ c0) & 0xffu;                  // decrypted tag
@@ -602,10 +668,10 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
         }
     }
 
+    uint32_t stword = SS_ST_BAD_MAC;
     if (leader) {
-        const uint32_t frame_idx = tile.first + f;
         if (ok && in_run) {
-            a.status[frame_idx] = SS_ST_OK | (tag_b1 << 8);   // state untouched: ss_run_commit_kernel owns it
+            stword = SS_ST_OK | (tag_b1 << 8);   // state untouched: ss_run_commit_kernel owns it
         } else if (ok) {
             const uint32_t tag = is_open ? tag_b1 : ((lf >> 24) & 3u);
             nn[1] ^= mac[0];
@@ -621,13 +687,24 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
             uint4 s2;
             s2.x = nn[0]; s2.y = nn[1]; s2.z = nn[2]; s2.w = meta;
             sp[2] = s2;
-            a.status[frame_idx] = SS_ST_OK | (tag << 8);
-        } else {
-            a.status[frame_idx] = SS_ST_BAD_MAC;
+            stword = SS_ST_OK | (tag << 8);
+        }
+        if (BULK) a.status[tile.first + f] = stword;
+    }
+    if (!BULK) {
+        // lane i collects the status of frame i from that frame's leader: one coalesced store per tile
+        const uint32_t v = ss_shfl(stword, lane < nfr ? my_start : 0u);
+        if (lane < nfr && !d_skip) a.status[tile.first + lane] = v;
+        if (out_staged) {
+            ss_syncwarp();   // every lane's pieces are in shared memory
+            const uint4 *stage = ss_stage_buffer();
+            uint4 *g = reinterpret_cast<uint4 *>(a.out + ow_lo);
+#pragma unroll
+            for (uint32_t i = 0; i < SS_STAGE_BYTES / 512u; i++)
+                if (lane + 32u * i < ow_pieces) g[lane + 32u * i] = stage[lane + 32u * i];
         }
     }
 }
-
 
 // ------------------------------------------------------ thread-per-frame tile --
 // For large batches of SMALL frames (<= 4 payload blocks) the packed mapping leaves throughput on

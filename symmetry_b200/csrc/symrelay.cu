@@ -262,6 +262,8 @@ struct symrelay_ctx {
     uint64_t zero_copy_max = 1ull << 20;                   // in+out bytes up to which a batch runs zero-copy
     uint64_t zero_copy_batches = 0, staged_batches = 0;
     bool pdl = true;   // SYMRELAY_PDL=0 turns programmatic dependent launch off
+    bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
+    uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
     int zc_mode = 1;   // experiment knob SYMRELAY_ZC_MODE: 1 all zero-copy, 2 copy ctrl+in / write out zero-copy, 3 copy ctrl only
 };
 
@@ -471,6 +473,8 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (ctx->opts.flags & SYMRELAY_OPT_NO_ZERO_COPY) ctx->zero_copy_max = 0;
     if (const char *m = getenv("SYMRELAY_ZC_MODE")) ctx->zc_mode = atoi(m);
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
+    if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
+    if (const char *m = getenv("SYMRELAY_STAGE_DEV")) ctx->device_arg_flags = atoi(m) ? (SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT) : 0u;
     ctx->n_gpus = n_gpus;
     for (int g = 0; g < n_gpus; g++) {
         if (gpu_ids[g] < 0 || gpu_ids[g] >= count) {
@@ -637,7 +641,7 @@ int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const symrelay_desc 
     Shard &sh = ctx->shard[gpu_index];
     CU(ctx, set_device(sh.dev));
     return launch_tiles(ctx, d_desc, n, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status, d_delta,
-                        d_delta_arena, (cudaStream_t)cuda_stream);
+                        d_delta_arena, (cudaStream_t)cuda_stream, ctx->device_arg_flags);
 }
 
 int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
@@ -738,22 +742,14 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     // control block: tiles ‖ descs, planned straight into pinned memory
     symrelay_tile *h_tiles = reinterpret_cast<symrelay_tile *>(st.h_ctrl);
     uint32_t n_bulk = 0;
-    const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk);
+    symrelay_plan_check chk;
+    chk.in_bytes = in_bytes; chk.out_bytes = out_bytes; chk.max_streams = ctx->opts.max_streams;
+    const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk, &chk);
     if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
-    // bounds / ownership checks: one branch-free pass (this loop is on the per-batch critical path of the
-    // host; the per-descriptor early returns and the modulo it used to have cost ~3 us per 2,048 frames)
-    uint32_t bad = 0, any_flags = 0;
-    const uint32_t max_streams = ctx->opts.max_streams;
+    // bounds / ownership checks (computed by the planner's first pass over the descriptors)
+    uint32_t bad = chk.out_of_bounds;
+    const uint32_t any_flags = chk.any_flags, out_overlap = chk.out_overlap;
     const uint32_t ng = (uint32_t)ctx->n_gpus;
-    for (uint32_t i = 0; i < n; i++) {
-        const symrelay_desc d = desc[i];
-        const uint32_t mlen = d.len_flags & SYMRELAY_LEN_MASK;
-        const uint32_t op = (d.len_flags >> 26) & 1u;   // SYMRELAY_F_OPEN
-        const uint64_t in_end = (uint64_t)d.in_off + mlen + 20u * op;
-        const uint64_t out_end = (uint64_t)d.out_off + mlen + 20u * (1u - op);
-        bad |= (uint32_t)(in_end > in_bytes) | (uint32_t)(out_end > out_bytes) | (uint32_t)(d.slot >= max_streams);
-        any_flags |= d.len_flags;
-    }
     if (ng > 1)
         for (uint32_t i = 0; i < n; i++) bad |= (uint32_t)((int)(desc[i].slot % ng) != gpu_index);
     if (bad) return fail(ctx, SYMRELAY_EINVAL, "a descriptor points outside its arena, names a slot beyond max_streams, or a slot that is not on gpu %d", gpu_index);
@@ -799,7 +795,8 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(k_ctrl + tiles_bytes), n,
                           reinterpret_cast<const symrelay_tile *>(k_ctrl), (uint32_t)n_tiles, n_bulk, k_in, out,
                           sh.d_states, st.h_status, extract ? st.h_delta : nullptr, extract ? delta_arena : nullptr,
-                          sh.s_k, (ctx->zc_mode == 1 && !extract) ? SS_ARG_INPUT_INDEPENDENT : 0u,
+                          sh.s_k, ((ctx->zc_mode == 1 && !extract) ? SS_ARG_INPUT_INDEPENDENT : 0u) |
+                                      (ctx->stage_input ? (SS_ARG_STAGE_INPUT | (out_overlap ? 0u : SS_ARG_STAGE_OUTPUT)) : 0u),
                           runs ? st.d_run_nonce : nullptr);
         if (rc) return rc;
         CU(ctx, cudaEventRecord(st.ev_out, sh.s_k));

@@ -12,6 +12,8 @@
 
 #include <vector>
 
+static uint32_t emu_arg_flags = 0;   // SsArgs.flags for the next batches (tests flip SS_ARG_STAGE_INPUT)
+extern "C" void emu_set_arg_flags(uint32_t f) { emu_arg_flags = f; }
 thread_local uint32_t emu_lane_id;
 thread_local EmuWarp *emu_warp;
 
@@ -56,7 +58,7 @@ extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *til
     pthread_t th[32];
     for (uint32_t l = 0; l < 32; l++) {
         jobs[l].warp = &warp;
-        jobs[l].args = SsArgs{(const SsDesc *)desc, (const SsTile *)tiles, n_tiles, in, out, (uint4 *)states, status, 0u, run_nonce.data()};
+        jobs[l].args = SsArgs{(const SsDesc *)desc, (const SsTile *)tiles, n_tiles, in, out, (uint4 *)states, status, emu_arg_flags, run_nonce.data()};
         jobs[l].n_packed = n_tiles - n_bulk;
         jobs[l].n_bulk = n_bulk;
         jobs[l].lane = l;

@@ -66,9 +66,15 @@ def emu_lib():
     return L
 
 
-@pytest.fixture()
-def be(emu_lib):
-    return EmuBackend(emu_lib)
+@pytest.fixture(params=[0, 2, 6], ids=["direct", "staged_input", "staged_input_output"])
+def be(emu_lib, request):
+    """Every scenario runs twice: plain per-lane loads, and with each packed tile's input window pulled
+    through shared memory first (SS_ARG_STAGE_INPUT, what zero-copy host batches use)."""
+    emu_lib.emu_set_arg_flags(request.param)
+    b = EmuBackend(emu_lib)
+    b.preserves_gaps = not (request.param & 4)   # staged output rewrites whole 16-byte rows of its window
+    yield b
+    emu_lib.emu_set_arg_flags(0)
 
 
 def test_planner_packs_and_splits(be):
