@@ -433,7 +433,7 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
 
 static void shard_free(Shard &sh) {
     if (sh.dev < 0) return;
-    cudaSetDevice(sh.dev);
+    set_device(sh.dev);
     if (sh.s_k) cudaStreamSynchronize(sh.s_k);
     if (sh.s_out) cudaStreamSynchronize(sh.s_out);
     for (Stage &st : sh.stages) {
@@ -910,7 +910,7 @@ int symrelay_probe_int_peak(symrelay_ctx *ctx, int gpu_index, double *arx_tops, 
 void *symrelay_alloc_pinned(symrelay_ctx *ctx, uint64_t bytes) {
     void *p = nullptr;
     if (!ctx || bytes == 0) return nullptr;
-    cudaSetDevice(ctx->shard[0].dev);
+    set_device(ctx->shard[0].dev);
     if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) {
         fail(ctx, SYMRELAY_ENOMEM, "cudaHostAlloc(%llu) failed", (unsigned long long)bytes);
         return nullptr;

@@ -255,3 +255,44 @@ def test_receive_side_reassembly_and_runs(relay):
             off += 3 + ln
         assert relay.export(slots[i])[1] == ref.raw
     assert relay.sched_stats()["frames"] >= want_total
+
+
+def test_two_gpus_in_one_context_shard_by_slot():
+    """A Node provider is ONE process: slots are sharded slot % n_gpus inside one context, each GPU
+    keeps its own state table and pipeline, and no state ever crosses GPUs."""
+    import torch
+
+    import symmetry_b200 as sb
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    rng = random.Random(6)
+    n = 400
+    keys = [rng.randbytes(32) for _ in range(n)]
+    hdrs = [rng.randbytes(24) for _ in range(n)]
+    with sb.SymRelay(gpu_ids=(0, 1), max_streams=4096) as r:
+        karr = np.frombuffer(b"".join(keys), dtype=np.uint8).reshape(n, 32)
+        harr = np.frombuffer(b"".join(hdrs), dtype=np.uint8).reshape(n, 24)
+        slots = [int(s) for s in r.open_streams(karr, harr, karr, harr)]
+        assert {s % 2 for s in slots} == {0, 1}
+        refs = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+        want = {}
+        for rnd in range(3):
+            for i in range(n):
+                m = rng.randbytes(rng.choice([0, 64, 200, 3000]))
+                want[r.submit_seal(slots[i], m)] = (i, m)
+            r.flush()
+            assert len(want) == n, "tickets must be unique across the context's GPUs"
+            got = {}
+            for _ in range(10000):
+                for c in r.poll(wait=True):
+                    got[c["ticket"]] = c
+                if len(got) >= n:
+                    break
+            assert len(got) == n
+            for t, (i, m) in want.items():
+                assert got[t]["status"] == 0 and got[t]["data"] == refs[i].seal_frame(m)
+                # and the peer's frames come back through the same slot's rx state on the same GPU
+            want = {}
+        for i in (0, 1, n - 2, n - 1):
+            assert r.export(slots[i])[0] == refs[i].raw
