@@ -237,6 +237,8 @@ struct Shard {
     int dev = -1;
     uint4 *d_states = nullptr;
     cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;
+    cudaStream_t s_aux = nullptr;                  // bulk tiles run here, next to the packed tiles of the same batch
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::vector<Stage> stages;
     SsInitRec *h_init = nullptr, *d_init = nullptr;  // staging for stream_open
     uint32_t init_cap = 0;
@@ -326,7 +328,7 @@ static cudaError_t launch_pdl(K kernel, uint32_t grid, uint32_t threads, cudaStr
 static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t n, const symrelay_tile *d_tiles,
                         uint32_t n_tiles, uint32_t n_bulk, const uint8_t *d_in, uint8_t *d_out, uint4 *d_states,
                         uint32_t *d_status, symrelay_delta *d_delta, uint8_t *d_delta_arena, cudaStream_t stream,
-                        uint32_t arg_flags = 0, uint4 *d_run_nonce = nullptr) {
+                        uint32_t arg_flags = 0, uint4 *d_run_nonce = nullptr, Shard *fork = nullptr) {
     const uint32_t n_packed = n_tiles - n_bulk;
     if (d_run_nonce) {
         ss_run_nonce_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
@@ -351,22 +353,35 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     // PDL only where it was measured to help: the host zero-copy path (16.2 -> 10.9 us per C2 batch).
     // Device-resident launches replayed from a CUDA graph got slower with it (6.3 -> 10.3 us).
     const bool pdl = ctx->pdl && (arg_flags & SS_ARG_INPUT_INDEPENDENT);
+    // Small and bulk tiles of one batch touch disjoint frames: when both exist the bulk kernel runs on a
+    // side stream next to the packed kernel (fork/join with events; measured on BASELINE config 3 they
+    // took 57 us + 35 us back to back).
+    const bool side = fork && n_packed && n_bulk;
+    cudaStream_t bulk_stream = stream;
+    if (side) {
+        CU(ctx, cudaEventRecord(fork->ev_fork, stream));
+        CU(ctx, cudaStreamWaitEvent(fork->s_aux, fork->ev_fork, 0));
+        bulk_stream = fork->s_aux;
+    }
+    if (n_bulk) {
+        SsArgs b = a;
+        b.tiles = reinterpret_cast<const SsTile *>(d_tiles) + n_packed;
+        b.n_tiles = n_bulk;
+        const uint32_t threads = n_bulk <= 148u * 8u ? 32u : 128u;
+        const uint32_t wpb = threads / 32u;
+        CU(ctx, launch_pdl(ss_bulk_kernel, (n_bulk + wpb - 1) / wpb, threads, bulk_stream, pdl && !side, b));
+        ctx->launches++;
+        if (side) CU(ctx, cudaEventRecord(fork->ev_join, bulk_stream));
+    }
     if (n_packed) {
         a.tiles = reinterpret_cast<const SsTile *>(d_tiles);
         a.n_tiles = n_packed;
         const uint32_t threads = n_packed <= 148u * 8u ? 32u : 128u;  // few tiles: one warp per SM sub-partition
         const uint32_t wpb = threads / 32u;
-        CU(ctx, launch_pdl(ss_packed_kernel, (n_packed + wpb - 1) / wpb, threads, stream, pdl, a));
+        CU(ctx, launch_pdl(ss_packed_kernel, (n_packed + wpb - 1) / wpb, threads, stream, pdl && !side, a));
         ctx->launches++;
     }
-    if (n_bulk) {
-        a.tiles = reinterpret_cast<const SsTile *>(d_tiles) + n_packed;
-        a.n_tiles = n_bulk;
-        const uint32_t threads = n_bulk <= 148u * 8u ? 32u : 128u;
-        const uint32_t wpb = threads / 32u;
-        CU(ctx, launch_pdl(ss_bulk_kernel, (n_bulk + wpb - 1) / wpb, threads, stream, pdl, a));
-        ctx->launches++;
-    }
+    if (side) CU(ctx, cudaStreamWaitEvent(stream, fork->ev_join, 0));
     if (d_run_nonce) {
         ss_run_commit_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
                                                                   d_states, d_status);
@@ -405,6 +420,9 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_in, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_k, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_out, cudaStreamNonBlocking));
+    CU(ctx, cudaStreamCreateWithFlags(&sh.s_aux, cudaStreamNonBlocking));
+    CU(ctx, cudaEventCreateWithFlags(&sh.ev_fork, cudaEventDisableTiming));
+    CU(ctx, cudaEventCreateWithFlags(&sh.ev_join, cudaEventDisableTiming));
     {
         std::vector<uint16_t> table(SX_TABLE_ENTRIES);
         sx::build_table(table.data());
@@ -448,6 +466,9 @@ static void shard_free(Shard &sh) {
     if (sh.s_in) cudaStreamDestroy(sh.s_in);
     if (sh.s_k) cudaStreamDestroy(sh.s_k);
     if (sh.s_out) cudaStreamDestroy(sh.s_out);
+    if (sh.s_aux) cudaStreamDestroy(sh.s_aux);
+    if (sh.ev_fork) cudaEventDestroy(sh.ev_fork);
+    if (sh.ev_join) cudaEventDestroy(sh.ev_join);
 }
 
 symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opts *opts) {
@@ -641,7 +662,7 @@ int symrelay_batch_device(symrelay_ctx *ctx, int gpu_index, const symrelay_desc 
     Shard &sh = ctx->shard[gpu_index];
     CU(ctx, set_device(sh.dev));
     return launch_tiles(ctx, d_desc, n, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status, d_delta,
-                        d_delta_arena, (cudaStream_t)cuda_stream, ctx->device_arg_flags);
+                        d_delta_arena, (cudaStream_t)cuda_stream, ctx->device_arg_flags, nullptr, &sh);
 }
 
 int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
@@ -797,7 +818,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
                           sh.d_states, st.h_status, extract ? st.h_delta : nullptr, extract ? delta_arena : nullptr,
                           sh.s_k, ((ctx->zc_mode == 1 && !extract) ? SS_ARG_INPUT_INDEPENDENT : 0u) |
                                       (ctx->stage_input ? (SS_ARG_STAGE_INPUT | (out_overlap ? 0u : SS_ARG_STAGE_OUTPUT)) : 0u),
-                          runs ? st.d_run_nonce : nullptr);
+                          runs ? st.d_run_nonce : nullptr, &sh);
         if (rc) return rc;
         CU(ctx, cudaEventRecord(st.ev_out, sh.s_k));
         ctx->zero_copy_batches++;
@@ -816,7 +837,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(st.d_ctrl + tiles_bytes), n,
                       reinterpret_cast<const symrelay_tile *>(st.d_ctrl), (uint32_t)n_tiles, n_bulk, st.d_in, st.d_out,
                       sh.d_states, st.d_status, extract ? st.d_delta : nullptr, extract ? st.d_delta_arena : nullptr,
-                      sh.s_k, 0u, runs ? st.d_run_nonce : nullptr);
+                      sh.s_k, 0u, runs ? st.d_run_nonce : nullptr, &sh);
     if (rc) return rc;
     CU(ctx, cudaEventRecord(st.ev_k, sh.s_k));
     CU(ctx, cudaStreamWaitEvent(sh.s_out, st.ev_k, 0));
