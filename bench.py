@@ -217,6 +217,8 @@ def run_reference(args):
     if rank != 0:
         return
     lens, desc, scaling = workload(args.workload, 1)
+    if scaling == "weak" and args.gpus > 1:
+        lens = np.tile(lens, args.gpus)      # same whole-job batch as our arm at N GPUs (per-GPU work is fixed)
     threads = host_threads()
     # bound the run: a step is the same batch, but never let warmup+steps exceed ~2 minutes
     probe, kind = cpu_run(lens, 1, 0, threads)
