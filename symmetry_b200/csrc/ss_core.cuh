@@ -38,6 +38,11 @@ SS_DEV uint32_t ss_reduce_or(uint32_t v) { return __reduce_or_sync(0xffffffffu, 
 SS_DEV uint32_t ss_reduce_max(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
 SS_DEV uint32_t ss_reduce_min(uint32_t v) { return __reduce_min_sync(0xffffffffu, v); }
 SS_DEV void ss_syncwarp() { __syncwarp(); }
+// bulk tiles: r, r^2, r^3, r^4, r^128 of the warp's frame, each as 5 limbs followed by 4 limbs-times-5 (45 words)
+SS_DEV uint32_t *ss_powers_buffer() {
+    __shared__ uint32_t pw[4][48];
+    return pw[(threadIdx.x >> 5) & 3u];
+}
 #define SS_STAGE_BYTES 2048u
 // per-warp staging window in shared memory (packed tiles, see ss_process_tile)
 SS_DEV uint4 *ss_stage_buffer() {
@@ -150,6 +155,28 @@ SS_DEV void ss_pmul(uint32_t h[5], const uint32_t a[5], const uint32_t b[5]) {
     c = (uint32_t)(d4 >> 26); h[4] = (uint32_t)d4 & 0x3ffffffu;
     h[0] += c * 5u;
     c = h[0] >> 26; h[0] &= 0x3ffffffu; h[1] += c;
+}
+
+// d += a * P where P is stored as {p0..p4, 5*p1..5*p4} (9 words, shared memory in the bulk kernel)
+SS_DEV void ss_pmac(uint64_t d[5], const uint32_t a[5], const uint32_t *P) {
+    const uint32_t b0 = P[0], b1 = P[1], b2 = P[2], b3 = P[3], b4 = P[4], s1 = P[5], s2 = P[6], s3 = P[7], s4 = P[8];
+    d[0] += (uint64_t)a[0] * b0 + (uint64_t)a[1] * s4 + (uint64_t)a[2] * s3 + (uint64_t)a[3] * s2 + (uint64_t)a[4] * s1;
+    d[1] += (uint64_t)a[0] * b1 + (uint64_t)a[1] * b0 + (uint64_t)a[2] * s4 + (uint64_t)a[3] * s3 + (uint64_t)a[4] * s2;
+    d[2] += (uint64_t)a[0] * b2 + (uint64_t)a[1] * b1 + (uint64_t)a[2] * b0 + (uint64_t)a[3] * s4 + (uint64_t)a[4] * s3;
+    d[3] += (uint64_t)a[0] * b3 + (uint64_t)a[1] * b2 + (uint64_t)a[2] * b1 + (uint64_t)a[3] * b0 + (uint64_t)a[4] * s4;
+    d[4] += (uint64_t)a[0] * b4 + (uint64_t)a[1] * b3 + (uint64_t)a[2] * b2 + (uint64_t)a[3] * b1 + (uint64_t)a[4] * b0;
+}
+SS_DEV void ss_store_power(uint32_t *P, const uint32_t v[5]) {
+    P[0] = v[0]; P[1] = v[1]; P[2] = v[2]; P[3] = v[3]; P[4] = v[4];
+    P[5] = v[1] * 5u; P[6] = v[2] * 5u; P[7] = v[3] * 5u; P[8] = v[4] * 5u;
+}
+// limbs of a full 16-byte block (2^128 bit set)
+SS_DEV void ss_block_limbs(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3, uint32_t l[5]) {
+    l[0] = t0 & 0x3ffffffu;
+    l[1] = ss_fsr(t0, t1, 26) & 0x3ffffffu;
+    l[2] = ss_fsr(t1, t2, 20) & 0x3ffffffu;
+    l[3] = ss_fsr(t2, t3, 14) & 0x3ffffffu;
+    l[4] = (t3 >> 8) | (1u << 24);
 }
 
 // acc <- (acc + block) * r for the 16-byte block (t0..t3) with the given 2^128 bit.
@@ -496,15 +523,23 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
             ss_r_limbs(t0, t1, t2, t3, r);
             sw[0] = x[4]; sw[1] = x[5]; sw[2] = x[6]; sw[3] = x[7];
             if (BULK) {
-                uint32_t t[5];
+                uint32_t t[5], t3[5];
+                uint32_t *pw = ss_powers_buffer();
                 ss_pmul(t, r, r);        // r^2
+                ss_pmul(t3, t, r);       // r^3
                 ss_pmul(r128, t, t);     // r^4
+                ss_syncwarp();           // (the previous tile of this warp is done with the buffer)
+                if (lane == 0) {         // every lane holds the same values: one writer is enough
+                    ss_store_power(pw, r); ss_store_power(pw + 9, t); ss_store_power(pw + 18, t3); ss_store_power(pw + 27, r128);
+                }
 #pragma unroll 1
                 for (int i = 0; i < 5; i++) {  // r^8 .. r^128
                     ss_pmul(t, r128, r128);
 #pragma unroll
                     for (int j = 0; j < 5; j++) r128[j] = t[j];
                 }
+                if (lane == 0) ss_store_power(pw + 36, r128);
+                ss_syncwarp();
             }
         }
 
@@ -565,9 +600,33 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
             const int vo = (int)T - 8 - so;
             if (vo < 64 && vo > -4) ss_insert(x, vo, V);
             if ((T & 15u) && (int)T - so < 64) ss_insert(x, (int)T - so, 1u);   // Poly1305 terminator of the partial last block
+            const bool final_win = (uint32_t)so + 64u >= T;
+            if (BULK && nbytes == 64 && !final_win) {
+                // Full window of a bulk frame: A <- A*r^128 + b0*r^4 + b1*r^3 + b2*r^2 + b3*r as FIVE products
+                // accumulated in 64-bit and ONE carry pass (instead of five multiply-reduce rounds); the
+                // powers come from shared memory so they cost no registers.
+                const uint32_t *pw = ss_powers_buffer();
+                uint64_t d[5] = {0, 0, 0, 0, 0};
+                uint32_t l[5];
+                if (have_A) ss_pmac(d, A, pw + 36);
+                ss_block_limbs(x[0], x[1], x[2], x[3], l);     ss_pmac(d, l, pw + 27);
+                ss_block_limbs(x[4], x[5], x[6], x[7], l);     ss_pmac(d, l, pw + 18);
+                ss_block_limbs(x[8], x[9], x[10], x[11], l);   ss_pmac(d, l, pw + 9);
+                ss_block_limbs(x[12], x[13], x[14], x[15], l); ss_pmac(d, l, pw);
+                uint32_t c;
+                c = (uint32_t)(d[0] >> 26); A[0] = (uint32_t)d[0] & 0x3ffffffu; d[1] += c;
+                c = (uint32_t)(d[1] >> 26); A[1] = (uint32_t)d[1] & 0x3ffffffu; d[2] += c;
+                c = (uint32_t)(d[2] >> 26); A[2] = (uint32_t)d[2] & 0x3ffffffu; d[3] += c;
+                c = (uint32_t)(d[3] >> 26); A[3] = (uint32_t)d[3] & 0x3ffffffu; d[4] += c;
+                const uint64_t c4 = d[4] >> 26; A[4] = (uint32_t)d[4] & 0x3ffffffu;
+                const uint64_t h0 = (uint64_t)A[0] + c4 * 5u;
+                A[0] = (uint32_t)h0 & 0x3ffffffu; A[1] += (uint32_t)(h0 >> 26);
+                have_A = true;
+                E = NB - 4u * q - 4u;
+                continue;
+            }
             uint32_t C[5] = {0, 0, 0, 0, 0};
             ss_phorner(C, x, (uint32_t)nbytes, r);
-            const bool final_win = (uint32_t)so + 64u >= T;
             if (BULK && final_win) {
 #pragma unroll
                 for (int i = 0; i < 5; i++) HX[i] = C[i];

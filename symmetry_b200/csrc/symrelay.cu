@@ -266,7 +266,6 @@ struct symrelay_ctx {
     bool pdl = true;   // SYMRELAY_PDL=0 turns programmatic dependent launch off
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
     uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
-    int zc_mode = 1;   // experiment knob SYMRELAY_ZC_MODE: 1 all zero-copy, 2 copy ctrl+in / write out zero-copy, 3 copy ctrl only
 };
 
 static bool is_library_pinned(const symrelay_ctx *ctx, const void *p, uint64_t bytes) {
@@ -492,7 +491,6 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (!ctx->opts.max_batch_frames) ctx->opts.max_batch_frames = 131072;
     ctx->opts.stage_bytes = align_up(ctx->opts.stage_bytes, 256);
     if (ctx->opts.flags & SYMRELAY_OPT_NO_ZERO_COPY) ctx->zero_copy_max = 0;
-    if (const char *m = getenv("SYMRELAY_ZC_MODE")) ctx->zc_mode = atoi(m);
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE_DEV")) ctx->device_arg_flags = atoi(m) ? (SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT) : 0u;
@@ -803,20 +801,14 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
                            is_library_pinned(ctx, out, out_bytes) &&
                            (!extract || is_library_pinned(ctx, delta_arena, in_bytes < delta_arena_bytes ? in_bytes : delta_arena_bytes));
     if (zero_copy) {
+        // (Copying the control block or the input with cudaMemcpyAsync on the kernel's stream instead was
+        // measured and is much worse: 26-36 us per batch against 16 us, small DMA copies have a high fixed cost.)
         const uint8_t *k_ctrl = st.h_ctrl;
         const uint8_t *k_in = in;
-        if (ctx->zc_mode >= 2) {
-            CU(ctx, cudaMemcpyAsync(st.d_ctrl, st.h_ctrl, ctrl_bytes, cudaMemcpyHostToDevice, sh.s_k));
-            k_ctrl = st.d_ctrl;
-        }
-        if (ctx->zc_mode == 2) {
-            CU(ctx, cudaMemcpyAsync(st.d_in, in, in_bytes, cudaMemcpyHostToDevice, sh.s_k));
-            k_in = st.d_in;
-        }
         rc = launch_tiles(ctx, reinterpret_cast<const symrelay_desc *>(k_ctrl + tiles_bytes), n,
                           reinterpret_cast<const symrelay_tile *>(k_ctrl), (uint32_t)n_tiles, n_bulk, k_in, out,
                           sh.d_states, st.h_status, extract ? st.h_delta : nullptr, extract ? delta_arena : nullptr,
-                          sh.s_k, ((ctx->zc_mode == 1 && !extract) ? SS_ARG_INPUT_INDEPENDENT : 0u) |
+                          sh.s_k, (!extract ? SS_ARG_INPUT_INDEPENDENT : 0u) |
                                       (ctx->stage_input ? (SS_ARG_STAGE_INPUT | (out_overlap ? 0u : SS_ARG_STAGE_OUTPUT)) : 0u),
                           runs ? st.d_run_nonce : nullptr, &sh);
         if (rc) return rc;
