@@ -111,3 +111,29 @@ def _drain(relay, by_ticket, wait, host_extract=None):
             raise RuntimeError(f"frame failed with status {c['status']}")
         if p.next >= len(p.frames):
             p.done = True
+
+
+# ---- transcript output: provider.ts:264-269, 277-297 -------------------------
+def _json_stringify(value) -> str:
+    """JSON.stringify for the shapes saveCompletion writes (arrays of {role, content} objects):
+    compact separators, non-ASCII left as is, lone surrogates escaped as \\udxxx (ES2019)."""
+    s = json.dumps(value, separators=(",", ":"), ensure_ascii=False)
+    if any(0xD800 <= ord(c) <= 0xDFFF for c in s):
+        s = "".join(f"\\u{ord(c):04x}" if 0xD800 <= ord(c) <= 0xDFFF else c for c in s)
+    return s
+
+
+def saveCompletion(completion: bytes, peer_public_key: bytes, conversation_index: int, messages, path: str) -> str:
+    """Writes `<path>/<peerPubKeyHex>-<conversationIndex>.json` = JSON.stringify([...messages,
+    {role:'assistant', content: completion}]) exactly as provider.ts:282-293 does, fed from the
+    extractor's accumulated delta bytes (WTF-8) instead of a JS string.  Returns the file name."""
+    import os
+
+    text = completion.decode("utf-8", "surrogatepass")
+    # halves of a surrogate pair that arrived in different chunks join up in the JS string
+    text = text.encode("utf-16", "surrogatepass").decode("utf-16", "surrogatepass")
+    body = _json_stringify(list(messages) + [{"role": "assistant", "content": text}])
+    name = os.path.join(path, f"{peer_public_key.hex()}-{conversation_index}.json")
+    with open(name, "w", encoding="utf-8") as f:
+        f.write(body)
+    return name
