@@ -206,13 +206,14 @@ SS_DEV void ss_phorner(uint32_t acc[5], const uint32_t w[16], uint32_t nbytes, c
 // OR the 4-byte little-endian value `val` into the window at byte offset `o`
 // (any alignment, may hang over either edge).
 SS_DEV void ss_insert(uint32_t w[16], int o, uint32_t val) {
+    // branch-free: the value lands in word o>>2 (low part) and the next one (spill-over); selects, no
+    // divergent branches -- this routine was the top stall site of the packed kernel in ncu's source view
+    const int wi = o >> 2;
+    const uint32_t sh = (uint32_t)(o & 3) * 8u;
+    const uint32_t lo = val << sh;
+    const uint32_t hi = sh ? (val >> (32u - sh)) : 0u;
 #pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const int d = o - 4 * i;
-        if (d == 0) w[i] |= val;
-        else if (d > 0 && d < 4) w[i] |= val << (8 * d);
-        else if (d < 0 && d > -4) w[i] |= val >> (8 * -d);
-    }
+    for (int i = 0; i < 16; i++) w[i] |= (i == wi ? lo : 0u) | (i == wi + 1 ? hi : 0u);
 }
 
 // Zero the bytes of the window at offsets >= n (n may be <= 0 or >= 64).
