@@ -193,7 +193,16 @@ SS_DEV void ss_pblock(uint32_t acc[5], uint32_t t0, uint32_t t1, uint32_t t2, ui
 
 // Horner over the first `nbytes` (0..64) bytes of a 64-byte window.  Bytes past
 // nbytes must already be zero except for the 0x01 terminator of a partial block.
+// FULL_FAST: take a test-free path for full windows.  Only for bulk tiles, where all lanes of the warp
+// have full windows together; in packed tiles the lanes differ and a second path would just be executed
+// in addition to the first (measured: C2 5.1 -> 5.8 us per step).
+template <bool FULL_FAST = false>
 SS_DEV void ss_phorner(uint32_t acc[5], const uint32_t w[16], uint32_t nbytes, const uint32_t r[5]) {
+    if (FULL_FAST && nbytes == 64u) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) ss_pblock(acc, w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3], 1u << 24, r);
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         if ((uint32_t)(16 * i) < nbytes) {
@@ -285,8 +294,17 @@ void ss_rekey(uint32_t k[8], uint32_t nn[3]) {
 
 // ------------------------------------------------------- payload load/store --
 // Loads up to 64 bytes (16-byte pieces that start below nbytes) from a 16-aligned address.
+template <bool FULL_FAST = false>
 SS_DEV void ss_load64(const uint8_t *p, int nbytes, uint32_t m[16]) {
     const uint4 *q = reinterpret_cast<const uint4 *>(p);
+    if (FULL_FAST && nbytes == 64) {    // full block: four unconditional vector loads
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint4 v = q[i];
+            m[4 * i] = v.x; m[4 * i + 1] = v.y; m[4 * i + 2] = v.z; m[4 * i + 3] = v.w;
+        }
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         uint4 v;
@@ -299,8 +317,18 @@ SS_DEV void ss_load64(const uint8_t *p, int nbytes, uint32_t m[16]) {
 // Stores exactly nbytes (1..64) bytes to a 16-aligned address: whole 16-byte
 // pieces as one vector store, the ragged tail byte by byte (the MAC or the next
 // frame's bytes may follow immediately).
+template <bool FULL_FAST = false>
 SS_DEV void ss_store64(uint8_t *p, int nbytes, const uint32_t m[16]) {
     uint4 *q = reinterpret_cast<uint4 *>(p);
+    if (FULL_FAST && nbytes == 64) {    // full block: four vector stores, none of the ragged-tail tests
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            uint4 v;
+            v.x = m[4 * i]; v.y = m[4 * i + 1]; v.z = m[4 * i + 2]; v.w = m[4 * i + 3];
+            q[i] = v;
+        }
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         if (16 * i + 16 <= nbytes) {
@@ -513,7 +541,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
         for (int i = 0; i < 16; i++) x[i] = 0;
         if (need_ks) ss_chacha_block(k, b, nn[0], nn[1], nn[2], x);
         if (BULK) {
-            ss_load64(src + 64u * (size_t)(has_payload ? b - 2u : 0u), cbytes, m);
+            ss_load64<true>(src + 64u * (size_t)(has_payload ? b - 2u : 0u), cbytes, m);
             if (valid && b == 1u && is_open) hw = *reinterpret_cast<const uint32_t *>(a.in + in_off);
         }
 
@@ -570,7 +598,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
                 if (!is_open) {
 #pragma unroll
                     for (int i = 0; i < 16; i++) x[i] ^= m[i];     // ciphertext
-                    ss_store64(dst + 64u * (size_t)j, cbytes, x);
+                    ss_store64<BULK>(dst + 64u * (size_t)j, cbytes, x);
                 } else {
                     if (!BULK) {
 #pragma unroll
@@ -582,7 +610,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
                         // wrong: no unauthenticated byte is ever visible to the caller.
 #pragma unroll
                         for (int i = 0; i < 16; i++) x[i] ^= m[i];
-                        ss_store64(dst + 64u * (size_t)j, cbytes, x);
+                        ss_store64<true>(dst + 64u * (size_t)j, cbytes, x);
                     }
 #pragma unroll
                     for (int i = 0; i < 16; i++) x[i] = m[i];      // MAC is over the ciphertext
@@ -627,7 +655,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
                 continue;
             }
             uint32_t C[5] = {0, 0, 0, 0, 0};
-            ss_phorner(C, x, (uint32_t)nbytes, r);
+            ss_phorner<BULK>(C, x, (uint32_t)nbytes, r);
             if (BULK && final_win) {
 #pragma unroll
                 for (int i = 0; i < 5; i++) HX[i] = C[i];
