@@ -37,6 +37,7 @@ SS_DEV uint32_t ss_shfl_down(uint32_t v, uint32_t d) { return __shfl_down_sync(0
 SS_DEV uint32_t ss_reduce_or(uint32_t v) { return __reduce_or_sync(0xffffffffu, v); }
 SS_DEV uint32_t ss_reduce_max(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
 SS_DEV uint32_t ss_reduce_min(uint32_t v) { return __reduce_min_sync(0xffffffffu, v); }
+SS_DEV bool ss_any(bool p) { return __any_sync(0xffffffffu, p) != 0; }
 SS_DEV void ss_syncwarp() { __syncwarp(); }
 // bulk tiles: r, r^2, r^3, r^4, r^128 of the warp's frame, each as 5 limbs followed by 4 limbs-times-5 (45 words)
 SS_DEV uint32_t *ss_powers_buffer() {
@@ -684,11 +685,12 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
         for (int i = 0; i < 5; i++) base[i] = r[i];
 #pragma unroll 1
         for (uint32_t bit = 0; bit < bits; ++bit) {
-            if ((E >> bit) & 1u) {
+            const bool mine = (E >> bit) & 1u;
+            if (ss_any(mine)) {   // warp-uniform branch, lanes select: no divergent region to reconverge from
                 uint32_t t[5];
                 ss_pmul(t, A, base);
 #pragma unroll
-                for (int i = 0; i < 5; i++) A[i] = t[i];
+                for (int i = 0; i < 5; i++) A[i] = mine ? t[i] : A[i];
             }
             if (bit + 1u < bits) {
                 uint32_t t[5];

@@ -67,6 +67,7 @@ static inline uint32_t ss_reduce_min(uint32_t v) {
     emu_sync();
     return r;
 }
+static inline bool ss_any(bool p) { return ss_reduce_or(p ? 1u : 0u) != 0; }
 static inline void ss_syncwarp() { emu_sync(); }
 #define SS_STAGE_BYTES 2048u
 static uint4 emu_stage[SS_STAGE_BYTES / 16u];   // one warp runs at a time
