@@ -228,11 +228,12 @@ SS_DEV void ss_insert(uint32_t w[16], int o, uint32_t val) {
 
 // Zero the bytes of the window at offsets >= n (n may be <= 0 or >= 64).
 SS_DEV void ss_keep_bytes(uint32_t w[16], int n) {
+    // branch-free: per word a mask of 0, a partial byte mask, or all ones (selects, no divergent branches)
 #pragma unroll
     for (int i = 0; i < 16; i++) {
         const int nb = n - 4 * i;
-        if (nb <= 0) w[i] = 0;
-        else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
+        const uint32_t part = (1u << (8 * (nb & 3))) - 1u;
+        w[i] &= nb <= 0 ? 0u : (nb >= 4 ? 0xffffffffu : part);
     }
 }
 
@@ -337,10 +338,17 @@ SS_DEV void ss_store64(uint8_t *p, int nbytes, const uint32_t m[16]) {
             v.x = m[4 * i]; v.y = m[4 * i + 1]; v.z = m[4 * i + 2]; v.w = m[4 * i + 3];
             q[i] = v;
         } else if (16 * i < nbytes) {
-            const int rem = nbytes - 16 * i;
-#pragma unroll
-            for (int j = 0; j < 15; j++)
-                if (j < rem) p[16 * i + j] = (uint8_t)(m[4 * i + (j >> 2)] >> (8 * (j & 3)));
+            // ragged tail of 1..15 bytes as at most one 8-, 4-, 2- and 1-byte store (naturally aligned because
+            // the piece is), instead of up to fifteen byte stores
+            const uint32_t rem = (uint32_t)(nbytes - 16 * i);
+            uint8_t *t = p + 16 * i;
+            const uint32_t p0 = m[4 * i], p1 = m[4 * i + 1], p2 = m[4 * i + 2], p3 = m[4 * i + 3];
+            uint32_t off = 0;
+            if (rem & 8u) { *reinterpret_cast<uint2 *>(t) = make_uint2(p0, p1); off = 8; }
+            if (rem & 4u) { *reinterpret_cast<uint32_t *>(t + off) = off ? p2 : p0; off += 4; }
+            const uint32_t wsel = off >= 12u ? p3 : (off >= 8u ? p2 : (off >= 4u ? p1 : p0));   // word that holds byte `off`
+            if (rem & 2u) { *reinterpret_cast<uint16_t *>(t + off) = (uint16_t)wsel; off += 2; }
+            if (rem & 1u) t[off] = (uint8_t)(wsel >> (8u * (off & 3u)));
         }
     }
 }

@@ -32,7 +32,10 @@ static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) =
 
 // ------------------------------------------------------------------ kernels --
 // One warp per tile.  Packed tiles: several small frames per warp.
-__global__ void __launch_bounds__(128) ss_packed_kernel(SsArgs a) {
+#ifndef SS_PACKED_MIN_BLOCKS
+#define SS_PACKED_MIN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
     if (a.tiles[warp].n_kind & (1u << 17)) ss_process_thread_tile(a, warp);   // warp-uniform: whole tile is one kind

@@ -12,6 +12,10 @@
 struct alignas(16) uint4 {
     uint32_t x, y, z, w;
 };
+struct alignas(8) uint2 {
+    uint32_t x, y;
+};
+static inline uint2 make_uint2(uint32_t x, uint32_t y) { uint2 v; v.x = x; v.y = y; return v; }
 
 struct EmuWarp {
     pthread_barrier_t bar;
