@@ -177,6 +177,9 @@ SYMRELAY_API int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, 
 SYMRELAY_API int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_keys, const uint8_t *tx_inits,
                                const uint8_t *rx_keys, const uint8_t *rx_inits, int init_len, int provider_kind,
                                uint32_t *slots_out);
+/* Wipes the slot's keys on the device and frees the slot.  Close only after every frame submitted for the
+ * slot has completed: a frame still in flight would be sealed with the wiped state.  Host batches that name a
+ * closed slot are refused (SYMRELAY_ENOENT). */
 SYMRELAY_API int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot);
 /* Copies the live libsodium-compatible 52-byte states back (either may be NULL). */
 SYMRELAY_API int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_t tx_state[SYMRELAY_STATEBYTES],

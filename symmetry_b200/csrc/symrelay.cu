@@ -775,6 +775,12 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (ng > 1)
         for (uint32_t i = 0; i < n; i++) bad |= (uint32_t)((int)(desc[i].slot % ng) != gpu_index);
     if (bad) return fail(ctx, SYMRELAY_EINVAL, "a descriptor points outside its arena, names a slot beyond max_streams, or a slot that is not on gpu %d", gpu_index);
+    {   // a closed slot holds an all-zero key: sealing with it must be impossible, not merely wrong
+        const uint8_t *open_slot = ctx->slot_state.data();
+        uint32_t closed = 0;
+        for (uint32_t i = 0; i < n; i++) closed |= (uint32_t)(open_slot[desc[i].slot] == 0);
+        if (closed) return fail(ctx, SYMRELAY_ENOENT, "a descriptor names a slot that is not open");
+    }
     bool extract = false;
     const bool runs = (any_flags & SYMRELAY_F_RUN) != 0;
     if (any_flags & SYMRELAY_F_EXTRACT) {

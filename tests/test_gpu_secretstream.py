@@ -344,3 +344,9 @@ def test_bad_arguments_are_rejected(relay):
         relay.batch_host(d, bu.aligned_zeros(128), bu.aligned_zeros(128))  # misaligned plaintext
     with pytest.raises(sb.RelayError):
         relay.export(99999)  # not open
+    k, h = bytes(32), bytes(24)
+    slot = relay.open_stream(k, h, k, h)
+    relay.close_stream(slot)
+    d = bu.make_descs([slot], [64], [0], [12])
+    with pytest.raises(sb.RelayError, match="not open"):
+        relay.batch_host(d, bu.aligned_zeros(128), bu.aligned_zeros(128))  # a closed slot has no key
