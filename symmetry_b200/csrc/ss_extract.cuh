@@ -328,6 +328,87 @@ struct Result {
     uint32_t status, len;
 };
 
+// What the scan leaves behind: the kinds of the five values on the path and, for the two values that can
+// reach `completion +=`, where their text sits.
+struct Tracked {
+    uint32_t root, choices, elem0, delta;
+    bool choices_nonempty;      // data.choices is a string with at least one character ("abc"[0])
+    Val content, rcontent;      // choices[0].delta.content and root.content
+};
+
+// ---- utils.ts:33-52: the provider switch, truthiness and ToString -------------------------------
+SS_DEV Result finish(const uint8_t *text, bool parsed, bool too_deep, const Tracked &tr, uint32_t kind, uint8_t *out,
+                     uint32_t cap) {
+    Result res;
+    res.status = SX_OK;
+    res.len = 0;
+    if (too_deep) { res.status = SX_UNSUPPORTED; return res; }
+
+    Out o;
+    o.p = out; o.n = 0; o.cap = cap; o.overflow = false;
+
+    Val v;          // the value handed to `completion +=`
+    v.kind = V_UNDEF; v.s = v.e = v.flags = 0;
+    bool coerce_all = false;   // llamacpp appends whatever it got; the others append '' unless truthy
+    const uint32_t root = parsed ? tr.root : V_UNDEF;   // JSON.parse threw -> data === undefined
+    if (kind == SX_KIND_LLAMACPP) {
+        coerce_all = true;
+        if (root == V_OBJECT && tr.rcontent.kind != V_ABSENT) v = tr.rcontent;          // data?.content
+    } else {
+        if (root == V_UNDEF || root == V_NULL) { res.len = 0; return res; }            // data?. short-circuits -> ''
+        // data.choices
+        uint32_t ck = root == V_OBJECT ? tr.choices : V_UNDEF;
+        if (ck == V_ABSENT) ck = V_UNDEF;
+        if (ck == V_UNDEF || ck == V_NULL) { res.status = SX_THROW; return res; }      // undefined[0]
+        // choices[0]
+        uint32_t ek;
+        if (ck == V_ARRAY || ck == V_OBJECT) ek = tr.elem0 == V_ABSENT ? V_UNDEF : tr.elem0;
+        else if (ck == V_STRING) ek = tr.choices_nonempty ? V_STRING : V_UNDEF;         // "abc"[0] === "a"
+        else ek = V_UNDEF;                                                              // number / boolean
+        if (ek == V_UNDEF || ek == V_NULL) { res.status = SX_THROW; return res; }      // undefined.delta
+        // .delta
+        uint32_t dk = (ek == V_OBJECT && ck != V_STRING) ? (tr.delta == V_ABSENT ? V_UNDEF : tr.delta) : V_UNDEF;
+        if (dk == V_UNDEF || dk == V_NULL) {
+            if (kind == SX_KIND_DEFAULT) { res.status = SX_THROW; return res; }        // delta.content (utils.ts:46)
+            res.len = 0; return res;                                                    // delta?.content -> ''
+        }
+        if (dk == V_OBJECT && tr.content.kind != V_ABSENT) v = tr.content;
+    }
+
+    // ---- truthiness and ToString ------------------------------------------------
+    bool truthy = false;
+    switch (v.kind) {
+        case V_TRUE: case V_OBJECT: case V_ARRAY: truthy = true; break;
+        case V_NUMBER: truthy = (v.flags & NF_NONZERO) != 0; break;
+        case V_STRING: truthy = v.e > v.s; break;
+        default: truthy = false; break;
+    }
+    if (!coerce_all && !truthy) { res.len = 0; return res; }
+    bool ok = true;
+    switch (v.kind) {
+        case V_UNDEF: case V_ABSENT: put_lit(o, "undefined"); break;
+        case V_NULL: put_lit(o, "null"); break;
+        case V_TRUE: put_lit(o, "true"); break;
+        case V_FALSE: put_lit(o, "false"); break;
+        case V_OBJECT: put_lit(o, "[object Object]"); break;
+        case V_ARRAY: ok = (v.flags & AF_EMPTY) != 0; break;        // [] -> ''; others: Array#join on the host
+        case V_NUMBER:
+            if ((v.flags & NF_NONZERO) && (v.flags & NF_EXP)) ok = false;   // may under/overflow: host decides
+            else ok = emit_number(text, v, o);
+            break;
+        case V_STRING: {
+            const bool is_undefined_word = decode_string(text, v.s, v.e, o);
+            if (kind == SX_KIND_DEFAULT && is_undefined_word) o.n = 0;      // utils.ts:46
+            break;
+        }
+        default: break;
+    }
+    if (!ok || o.overflow) { res.status = SX_UNSUPPORTED; res.len = 0; return res; }
+    res.len = o.n;
+    return res;
+}
+
+
 // text = chunk bytes, n = length, kind = SX_KIND_*, out = at least `cap` writable bytes, T = build_table()
 SS_DEV Result extract_chunk(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap, const uint16_t *T) {
     // ---- utils.ts:16-27: prefix test and split('data:')[1] ------------------
@@ -348,7 +429,22 @@ SS_DEV Result extract_chunk(const uint8_t *text, uint32_t n, uint32_t kind, uint
     uint32_t vstart = 0;
     bool too_deep = false;
 
+    const bool word_ok = (reinterpret_cast<uintptr_t>(text) & 3u) == 0;
     for (; pos < end; pos++) {
+        // Inside a string nothing happens until a quote, a backslash or a control character: skip four
+        // bytes at a time while a word holds none of them (and no 'd', which could start the second
+        // "data:" that ends split()[1]).  Most bytes of a chat-completion chunk sit inside strings.
+        if ((state == S_STR || state == S_KSTR) && word_ok) {
+            while ((pos & 3u) == 0 && pos + 4u <= end) {
+                const uint32_t w = *reinterpret_cast<const uint32_t *>(text + pos);
+                const uint32_t q = w ^ 0x22222222u, b = w ^ 0x5c5c5c5cu, d = w ^ 0x64646464u, ctl = w & 0xe0e0e0e0u;
+                const uint32_t hit = ((q - 0x01010101u) & ~q) | ((b - 0x01010101u) & ~b) | ((d - 0x01010101u) & ~d) |
+                                     ((ctl - 0x01010101u) & ~ctl);
+                if (hit & 0x80808080u) break;
+                pos += 4u;
+            }
+            if (pos >= end) break;
+        }
         const uint32_t c = text[pos];
         if (c == 'd' && prefixed && pos + 5 <= n && text[pos + 1] == 'a' && text[pos + 2] == 't' && text[pos + 3] == 'a' &&
             text[pos + 4] == ':') {
@@ -430,75 +526,379 @@ SS_DEV Result extract_chunk(const uint8_t *text, uint32_t n, uint32_t kind, uint
         state = S_AFTER;
     }
 
-    Result res;
-    res.status = SX_OK;
-    res.len = 0;
-    if (too_deep) { res.status = SX_UNSUPPORTED; return res; }
-    const bool parsed = state == S_AFTER && depth == 0;   // else JSON.parse threw -> data === undefined
+    Tracked tr;
+    tr.root = tv[T_ROOT].kind; tr.choices = tv[T_CHOICES].kind; tr.elem0 = tv[T_ELEM0].kind; tr.delta = tv[T_DELTA].kind;
+    tr.choices_nonempty = tv[T_CHOICES].e > tv[T_CHOICES].s;
+    tr.content = tv[T_CONTENT]; tr.rcontent = tv[T_RCONTENT];
+    return finish(text, state == S_AFTER && depth == 0, too_deep, tr, kind, out, cap);
+}
 
-    Out o;
-    o.p = out; o.n = 0; o.cap = cap; o.overflow = false;
 
-    // ---- utils.ts:33-52 ------------------------------------------------------
-    Val v;          // the value handed to `completion +=`
-    v.kind = V_UNDEF; v.s = v.e = v.flags = 0;
-    bool coerce_all = false;   // llamacpp appends whatever it got; the others append '' unless truthy
-    const uint32_t root = parsed ? tv[T_ROOT].kind : V_UNDEF;
-    if (kind == SX_KIND_LLAMACPP) {
-        coerce_all = true;
-        if (root == V_OBJECT && tv[T_RCONTENT].kind != V_ABSENT) v = tv[T_RCONTENT];   // data?.content
-    } else {
-        if (root == V_UNDEF || root == V_NULL) { res.len = 0; return res; }            // data?. short-circuits -> ''
-        // data.choices
-        uint32_t ck = root == V_OBJECT ? tv[T_CHOICES].kind : V_UNDEF;
-        if (ck == V_ABSENT) ck = V_UNDEF;
-        if (ck == V_UNDEF || ck == V_NULL) { res.status = SX_THROW; return res; }      // undefined[0]
-        // choices[0]
-        uint32_t ek;
-        if (ck == V_ARRAY || ck == V_OBJECT) ek = tv[T_ELEM0].kind == V_ABSENT ? V_UNDEF : tv[T_ELEM0].kind;
-        else if (ck == V_STRING) ek = tv[T_CHOICES].e > tv[T_CHOICES].s ? V_STRING : V_UNDEF;   // "abc"[0] === "a"
-        else ek = V_UNDEF;                                                              // number / boolean
-        if (ek == V_UNDEF || ek == V_NULL) { res.status = SX_THROW; return res; }      // undefined.delta
-        // .delta
-        uint32_t dk = (ek == V_OBJECT && ck != V_STRING) ? (tv[T_DELTA].kind == V_ABSENT ? V_UNDEF : tv[T_DELTA].kind) : V_UNDEF;
-        if (dk == V_UNDEF || dk == V_NULL) {
-            if (kind == SX_KIND_DEFAULT) { res.status = SX_THROW; return res; }        // delta.content (utils.ts:46)
-            res.len = 0; return res;                                                    // delta?.content -> ''
+// ---- the two-pass form the kernel runs on staged chunks ---------------------------------------------
+// The single pass above puts the bookkeeping (which value is this? which key was that?) inside the byte
+// loop.  One thread owns one chunk, so in every iteration some lane of the warp is at a structural
+// character and the whole warp walks the bookkeeping code: measured 60 us for 16,384 chunks of ~216 B,
+// about 550 cycles per byte.  Here the byte loop only runs the grammar: one class look-up and one table
+// look-up per byte, the same few instructions for every lane, and what the grammar meets on the way (a
+// key, a string, a number, a bracket) is appended to a per-thread event list.  The bookkeeping then runs
+// once per event (~30 per chunk) with the lanes in step.
+//
+//  - The container kind is not on a stack the byte loop has to consult: the states after a value are
+//    split by container (top level / object / array) and `ctx` holds, one per byte, the four states that
+//    depend on the container: after a value, after a comma, after '}' and after ']'.  A table entry
+//    either names its next state or picks one of those four, and a single byte-permute does the pick, so
+//    the loop-carried chain is: table load -> permute -> address -> table load.
+//  - Bytes are first mapped to classes (columns of the full table that are identical in every state);
+//    the class table is derived from the grammar, not written by hand.
+enum : uint32_t {
+    Q_ERR = 0,                   // zero: a permute digit that replicates a clear sign bit yields this state
+    Q_VALUE, Q_ARR_FIRST, Q_AFTER_T, Q_AFTER_A, Q_AFTER_O, Q_OBJ_FIRST, Q_OBJ_KEY, Q_COLON,
+    Q_STR, Q_ESC, Q_U1, Q_U2, Q_U3, Q_U4,
+    Q_KSTR, Q_KSTR2, Q_KESC, Q_KU1, Q_KU2, Q_KU3, Q_KU4,   // KSTR2: a key in which a backslash has been seen
+    Q_NMINUS, Q_NZERO, Q_NINT, Q_NDOT, Q_NFRAC, Q_NE, Q_NESIGN, Q_NEXP,
+    Q_T1, Q_T2, Q_T3, Q_F1, Q_F2, Q_F3, Q_F4, Q_N1, Q_N2, Q_N3,
+    // the second "data:" (src/utils.ts:22 keeps what lies between the first and the second):
+    Q_STR_D1, Q_STR_D2, Q_STR_D3, Q_STR_D4,         // a string body that ends in "d", "da", "dat", "data"
+    Q_KSTR_D1, Q_KSTR_D2, Q_KSTR_D3, Q_KSTR_D4,
+    Q_KSTR2_D1, Q_KSTR2_D2, Q_KSTR2_D3, Q_KSTR2_D4,
+    Q_U4_D, Q_KU4_D,                                // the third hex digit of a \u escape was 'd'
+    Q_X1, Q_X2, Q_X3, Q_X4, Q_DONE,                 // after a complete top-level value: "d", "da", "dat", "data", "data:"
+    Q_CUT,                                          // "data:" inside a string: the piece before it ends mid-string
+    Q_COUNT
+};
+enum : uint32_t {   // events, values first
+    E_NONE = 0, E_OPEN_OBJ, E_OPEN_ARR, E_STR, E_NUM, E_NUM_CLOSE, E_LIT_T, E_LIT_F, E_LIT_N,
+    E_KEY, E_KEY_ESC, E_CLOSE, E_CLOSE_EMPTY
+};
+// byte 3 of an entry's low word: event in bits 0..3, QF_START, QF_SPLIT (see build_fast_tables) and in the top two bits the change of
+// nesting depth as a signed number (01 = a container opens, 11 = one closes).  QF_OBJ only tells
+// fast_entry() which container opens and is not stored.
+enum : uint32_t { QF_START = 0x10, QF_SPLIT = 0x20, QF_PUSH = 0x40, QF_POP = 0xc0, QF_OBJ = 0x100 };
+enum : uint32_t { QSEL_AFTER = 0, QSEL_COMMA = 1, QSEL_CLOSE_OBJ = 2, QSEL_CLOSE_ARR = 3, QSEL_TABLE = 6 };
+#define SX_FAST_CLASSES 32u
+#define SX_FAST_ENTRIES (sx::Q_COUNT * SX_FAST_CLASSES)
+#define SX_FAST_MAX_LEN 4095u       /* positions are stored in 12 bits */
+#define SX_FAST_MAX_DEPTH 13u       /* deeper chunks are left to the single pass */
+#define SX_FAST_STACK_WORDS (SX_FAST_MAX_DEPTH + 3u)
+#define SX_FAST_SCRATCH_WORDS(ev_cap) (SX_FAST_STACK_WORDS + (ev_cap) + 1u)
+#define SX_CTX_TOP ((uint32_t)sx::Q_AFTER_T)                          /* comma, '}' and ']' are errors at top level */
+#define SX_CTX_OBJ ((uint32_t)sx::Q_AFTER_O | (sx::Q_OBJ_KEY << 8))   /* | state after this object's '}' << 16 */
+#define SX_CTX_ARR ((uint32_t)sx::Q_AFTER_A | (sx::Q_VALUE << 8))     /* | state after this array's ']' << 24 */
+
+// entry, low word: bits 0..15 the permute selector, 16..23 the next state, 24..31 event | QF_*.  The
+// selector's low digit picks a byte of `ctx` (0..3) or byte 2 of the entry itself (6); the other three
+// digits pick the sign of that byte, i.e. zero.
+// entry, high word: how this byte changes `ctx`, again as a permute of (ctx, word): the identity for
+// most bytes; an opening bracket builds the new container's four states from bytes 2 and 3 of the word
+// and moves the old "after a value" state into the slot of the matching closing bracket.
+static inline uint64_t fast_entry(uint32_t next, uint32_t sel, uint32_t flags) {
+    const uint32_t lo = (0xeee0u | sel) | (next << 16) | ((flags & 0xffu) << 24);
+    uint32_t hi = 0x3210u;
+    if ((flags & 0xc0u) == QF_PUSH) hi = (flags & QF_OBJ) ? (0xe076u | (SX_CTX_OBJ << 16)) : (0x0e76u | (SX_CTX_ARR << 16));
+    return lo | ((uint64_t)hi << 32);
+}
+
+// Fills F[SX_FAST_ENTRIES] and cls8[256] (class * 8: the byte offset of the class inside a table row).
+// Returns the number of byte classes (<= SX_FAST_CLASSES), or 0 if the grammar no longer fits.
+static inline uint32_t build_fast_tables(uint64_t *F, uint8_t *cls8) {
+    static uint64_t G[Q_COUNT][256];
+    auto set = [&](uint32_t st, uint32_t c, uint32_t next, uint32_t flags) { G[st][c] = fast_entry(next, QSEL_TABLE, flags); };
+    auto pick = [&](uint32_t st, uint32_t c, uint32_t sel, uint32_t flags) { G[st][c] = fast_entry(Q_ERR, sel, flags); };
+    auto is_hex = [](uint32_t c) { return (c >= '0' && c <= '9') || ((c | 0x20u) >= 'a' && (c | 0x20u) <= 'f'); };
+    for (uint32_t st = 0; st < Q_COUNT; st++)
+        for (uint32_t c = 0; c < 256; c++) set(st, c, Q_ERR, 0);
+    const uint8_t ws[4] = {0x20, 0x09, 0x0a, 0x0d};
+    for (uint32_t st : {(uint32_t)Q_VALUE, (uint32_t)Q_ARR_FIRST}) {
+        for (uint8_t w : ws) set(st, w, st, 0);
+        set(st, '{', Q_OBJ_FIRST, E_OPEN_OBJ | QF_PUSH | QF_OBJ);
+        set(st, '[', Q_ARR_FIRST, E_OPEN_ARR | QF_PUSH);
+        set(st, '"', Q_STR, QF_START);
+        set(st, '-', Q_NMINUS, QF_START);
+        set(st, '0', Q_NZERO, QF_START);
+        for (uint32_t c = '1'; c <= '9'; c++) set(st, c, Q_NINT, QF_START);
+        set(st, 't', Q_T1, E_LIT_T);
+        set(st, 'f', Q_F1, E_LIT_F);
+        set(st, 'n', Q_N1, E_LIT_N);
+    }
+    pick(Q_ARR_FIRST, ']', QSEL_CLOSE_ARR, E_CLOSE_EMPTY | QF_POP);
+    for (uint32_t st : {(uint32_t)Q_AFTER_T, (uint32_t)Q_AFTER_O, (uint32_t)Q_AFTER_A})
+        for (uint8_t w : ws) set(st, w, st, 0);
+    set(Q_AFTER_O, ',', Q_OBJ_KEY, 0);
+    pick(Q_AFTER_O, '}', QSEL_CLOSE_OBJ, E_CLOSE | QF_POP);
+    set(Q_AFTER_A, ',', Q_VALUE, 0);
+    pick(Q_AFTER_A, ']', QSEL_CLOSE_ARR, E_CLOSE | QF_POP);
+    for (uint32_t st : {(uint32_t)Q_OBJ_FIRST, (uint32_t)Q_OBJ_KEY}) {
+        for (uint8_t w : ws) set(st, w, st, 0);
+        set(st, '"', Q_KSTR, QF_START);
+    }
+    pick(Q_OBJ_FIRST, '}', QSEL_CLOSE_OBJ, E_CLOSE | QF_POP);
+    for (uint8_t w : ws) set(Q_COLON, w, Q_COLON, 0);
+    set(Q_COLON, ':', Q_VALUE, 0);
+    // value strings
+    for (uint32_t c = 0x20; c < 256; c++) set(Q_STR, c, Q_STR, 0);
+    pick(Q_STR, '"', QSEL_AFTER, E_STR);
+    set(Q_STR, 0x5c, Q_ESC, 0);
+    for (char c : {'"', '\\', '/', 'b', 'f', 'n', 'r', 't'}) set(Q_ESC, (uint8_t)c, Q_STR, 0);
+    set(Q_ESC, 'u', Q_U1, 0);
+    for (uint32_t j = 0; j < 4; j++)
+        for (uint32_t c = 0; c < 256; c++)
+            if (is_hex(c)) set(Q_U1 + j, c, j == 3 ? (uint32_t)Q_STR : Q_U1 + j + 1, 0);
+    // key strings: the same grammar; a key that held an escape ends in a different event
+    for (uint32_t st : {(uint32_t)Q_KSTR, (uint32_t)Q_KSTR2}) {
+        for (uint32_t c = 0x20; c < 256; c++) set(st, c, st, 0);
+        set(st, '"', Q_COLON, st == Q_KSTR ? E_KEY : E_KEY_ESC);
+        set(st, 0x5c, Q_KESC, 0);
+    }
+    for (char c : {'"', '\\', '/', 'b', 'f', 'n', 'r', 't'}) set(Q_KESC, (uint8_t)c, Q_KSTR2, 0);
+    set(Q_KESC, 'u', Q_KU1, 0);
+    for (uint32_t j = 0; j < 4; j++)
+        for (uint32_t c = 0; c < 256; c++)
+            if (is_hex(c)) set(Q_KU1 + j, c, j == 3 ? (uint32_t)Q_KSTR2 : Q_KU1 + j + 1, 0);
+    // numbers
+    set(Q_NMINUS, '0', Q_NZERO, 0);
+    for (uint32_t c = '1'; c <= '9'; c++) set(Q_NMINUS, c, Q_NINT, 0);
+    for (uint32_t c = '0'; c <= '9'; c++) {
+        set(Q_NINT, c, Q_NINT, 0);
+        set(Q_NDOT, c, Q_NFRAC, 0);
+        set(Q_NFRAC, c, Q_NFRAC, 0);
+        set(Q_NE, c, Q_NEXP, 0);
+        set(Q_NESIGN, c, Q_NEXP, 0);
+        set(Q_NEXP, c, Q_NEXP, 0);
+    }
+    set(Q_NZERO, '.', Q_NDOT, 0);
+    set(Q_NINT, '.', Q_NDOT, 0);
+    for (uint32_t st : {(uint32_t)Q_NZERO, (uint32_t)Q_NINT, (uint32_t)Q_NFRAC}) { set(st, 'e', Q_NE, 0); set(st, 'E', Q_NE, 0); }
+    set(Q_NE, '+', Q_NESIGN, 0);
+    set(Q_NE, '-', Q_NESIGN, 0);
+    for (uint32_t st : {(uint32_t)Q_NZERO, (uint32_t)Q_NINT, (uint32_t)Q_NFRAC, (uint32_t)Q_NEXP}) {   // a number ends at a delimiter
+        for (uint8_t w : ws) pick(st, w, QSEL_AFTER, E_NUM);
+        pick(st, ',', QSEL_COMMA, E_NUM);
+        pick(st, '}', QSEL_CLOSE_OBJ, E_NUM_CLOSE | QF_POP);
+        pick(st, ']', QSEL_CLOSE_ARR, E_NUM_CLOSE | QF_POP);
+    }
+    // literals
+    set(Q_T1, 'r', Q_T2, 0); set(Q_T2, 'u', Q_T3, 0); pick(Q_T3, 'e', QSEL_AFTER, 0);
+    set(Q_F1, 'a', Q_F2, 0); set(Q_F2, 'l', Q_F3, 0); set(Q_F3, 's', Q_F4, 0); pick(Q_F4, 'e', QSEL_AFTER, 0);
+    set(Q_N1, 'u', Q_N2, 0); set(Q_N2, 'l', Q_N3, 0); pick(Q_N3, 'l', QSEL_AFTER, 0);
+
+    // ---- the second "data:" ----
+    // For a chunk that starts with "data:" the reference parses only what lies before the next "data:".
+    // Where that next one follows a complete top-level value (two events in one chunk) the grammar ends
+    // there: Q_DONE swallows the rest.  Inside a string body the four states per string kind follow "d",
+    // "da", "dat", "data" and the ':' ends in Q_CUT: the piece before the split stops inside a string, so
+    // JSON.parse throws.  Anywhere else the table only notices that a split may be there (QF_SPLIT: the
+    // chunk is then left to the single pass).  In strings (a \\u escape can supply the 'd' or the "da"
+    // with its last hex digits; earlier in an escape, or right after the backslash, what follows "d" or
+    // "da" is an error with or without the split).  Outside strings the pattern would have to start at a
+    // 'd' met in a state that is not Q_ERR -- after Q_ERR the piece before the split holds the same error.
+    {
+        const uint32_t body[3] = {Q_STR, Q_KSTR, Q_KSTR2}, d1[3] = {Q_STR_D1, Q_KSTR_D1, Q_KSTR2_D1};
+        for (uint32_t st = Q_VALUE; st <= Q_N3; st++) {
+            const bool in_string = (st >= Q_STR && st <= Q_KU4);
+            if (!in_string) G[st]['d'] |= (uint64_t)QF_SPLIT << 24;
         }
-        if (dk == V_OBJECT && tv[T_CONTENT].kind != V_ABSENT) v = tv[T_CONTENT];
+        const uint32_t u3[2] = {Q_U3, Q_KU3}, u4[2] = {Q_U4, Q_KU4}, u4d[2] = {Q_U4_D, Q_KU4_D}, ud1[2] = {Q_STR_D1, Q_KSTR2_D1};
+        for (uint32_t k = 0; k < 2; k++) {
+            for (uint32_t c = 0; c < 256; c++) G[u4d[k]][c] = G[u4[k]][c];
+            set(u3[k], 'd', u4d[k], 0);
+            set(u4[k], 'd', ud1[k], 0);
+            set(u4d[k], 'd', ud1[k], 0);
+            set(u4d[k], 'a', ud1[k] + 1, 0);
+        }
+        for (uint32_t k = 0; k < 3; k++) {
+            for (uint32_t j = 0; j < 4; j++)
+                for (uint32_t c = 0; c < 256; c++) G[d1[k] + j][c] = G[body[k]][c];
+            for (uint32_t j = 0; j < 5; j++) set(j ? d1[k] + j - 1 : body[k], 'd', d1[k], 0);
+            set(d1[k], 'a', d1[k] + 1, 0);
+            set(d1[k] + 1, 't', d1[k] + 2, 0);
+            set(d1[k] + 2, 'a', d1[k] + 3, 0);
+            set(d1[k] + 3, ':', Q_CUT, 0);
+        }
+        set(Q_AFTER_T, 'd', Q_X1, 0);
+        set(Q_X1, 'a', Q_X2, 0); set(Q_X2, 't', Q_X3, 0); set(Q_X3, 'a', Q_X4, 0); set(Q_X4, ':', Q_DONE, 0);
+        for (uint32_t c = 0; c < 256; c++) { set(Q_DONE, c, Q_DONE, 0); set(Q_CUT, c, Q_CUT, 0); }
     }
 
-    // ---- truthiness and ToString ------------------------------------------------
-    bool truthy = false;
-    switch (v.kind) {
-        case V_TRUE: case V_OBJECT: case V_ARRAY: truthy = true; break;
-        case V_NUMBER: truthy = (v.flags & NF_NONZERO) != 0; break;
-        case V_STRING: truthy = v.e > v.s; break;
-        default: truthy = false; break;
-    }
-    if (!coerce_all && !truthy) { res.len = 0; return res; }
-    bool ok = true;
-    switch (v.kind) {
-        case V_UNDEF: case V_ABSENT: put_lit(o, "undefined"); break;
-        case V_NULL: put_lit(o, "null"); break;
-        case V_TRUE: put_lit(o, "true"); break;
-        case V_FALSE: put_lit(o, "false"); break;
-        case V_OBJECT: put_lit(o, "[object Object]"); break;
-        case V_ARRAY: ok = (v.flags & AF_EMPTY) != 0; break;        // [] -> ''; others: Array#join on the host
-        case V_NUMBER:
-            if ((v.flags & NF_NONZERO) && (v.flags & NF_EXP)) ok = false;   // may under/overflow: host decides
-            else ok = emit_number(text, v, o);
-            break;
-        case V_STRING: {
-            const bool is_undefined_word = decode_string(text, v.s, v.e, o);
-            if (kind == SX_KIND_DEFAULT && is_undefined_word) o.n = 0;      // utils.ts:46
-            break;
+    // byte classes: bytes whose columns agree in every state
+    uint32_t n_cls = 0;
+    uint8_t rep[256];
+    for (uint32_t c = 0; c < 256; c++) {
+        uint32_t k = 0;
+        for (; k < n_cls; k++) {
+            bool same = true;
+            for (uint32_t st = 0; st < Q_COUNT && same; st++) same = G[st][c] == G[st][rep[k]];
+            if (same) break;
         }
-        default: break;
+        if (k == n_cls) {
+            if (n_cls == SX_FAST_CLASSES) return 0;
+            rep[n_cls++] = (uint8_t)c;
+        }
+        cls8[c] = (uint8_t)(k * 8u);
     }
-    if (!ok || o.overflow) { res.status = SX_UNSUPPORTED; res.len = 0; return res; }
-    res.len = o.n;
-    return res;
+    for (uint32_t st = 0; st < Q_COUNT; st++)
+        for (uint32_t k = 0; k < SX_FAST_CLASSES; k++) F[st * SX_FAST_CLASSES + k] = k < n_cls ? G[st][rep[k]] : fast_entry(Q_ERR, QSEL_TABLE, 0);
+    return n_cls;
+}
+
+SS_DEV uint32_t permute(uint32_t a, uint32_t b, uint32_t sel) {
+#ifdef __CUDA_ARCH__
+    uint32_t r;   // PTX prmt: bit 3 of a selector digit replicates the sign of the chosen byte (__byte_perm does not promise that)
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+#else
+    const uint64_t v = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (uint32_t i = 0; i < 4; i++) {
+        const uint32_t d = (sel >> (4 * i)) & 15u;
+        uint32_t byte = (uint32_t)(v >> (8 * (d & 7u))) & 0xffu;
+        if (d & 8u) byte = (byte & 0x80u) ? 0xffu : 0u;
+        r |= byte << (8 * i);
+    }
+    return r;
+#endif
+}
+
+SS_DEV uint32_t match_key_plain(const uint8_t *t, uint32_t s, uint32_t e) {
+    const uint32_t len = e - s;
+    if (len != 1u && len != 5u && len != 7u) return KEY_NONE;
+    uint64_t k = 0;
+    for (uint32_t i = 0; i < len; i++) k |= (uint64_t)t[s + i] << (8u * i);
+    return k == 0x0073656369'6f6863ull ? KEY_CHOICES : k == 0x00746e65'746e6f63ull ? KEY_CONTENT
+         : k == 0x000000'61746c6564ull ? KEY_DELTA : k == 0x30ull ? KEY_ZERO : KEY_NONE;
+}
+
+// Returns false if the chunk is left to extract_chunk: more events than `ev_cap`, or nesting deeper than
+// SX_FAST_MAX_DEPTH.  text: 4-byte aligned, n <= SX_FAST_MAX_LEN, readable up to text + n + 8; F, cls8:
+// build_fast_tables(); scratch: SX_FAST_SCRATCH_WORDS(ev_cap) words.
+SS_DEV bool extract_fast(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap, const uint64_t *F,
+                         const uint8_t *cls8, uint32_t *scratch, uint32_t ev_cap, Result *res) {
+    uint32_t pos = 0, end = n;
+    const bool prefixed = n >= 5 && text[0] == 'd' && text[1] == 'a' && text[2] == 't' && text[3] == 'a' && text[4] == ':';
+    if (prefixed) pos = 5;
+
+    // ---- pass 1: grammar only.  Written without branches: each lane of a warp is at a different place in
+    // its own chunk, so any branch here is taken by some lane in nearly every iteration.  A warp of these
+    // runs alone on its scheduler and most instructions wait for the one before: what counts is how few
+    // instructions a byte takes. ----
+    //  - saved[d] holds the ctx of the container d levels up.  Every byte stores the current ctx at its own
+    //    depth (harmless unless the byte opens a container, when that slot becomes live) and reloads the
+    //    slot below, so that a closing bracket finds its parent's ctx in a register.
+    //  - every byte also stores an event word at ev[nev]; only bytes that carry an event advance nev.
+    uint32_t *saved = scratch + 1;                       // saved[-1] is read at depth 0
+    uint32_t *ev = scratch + SX_FAST_STACK_WORDS;
+    uint32_t state = Q_VALUE, ctx = SX_CTX_TOP, popctx = SX_CTX_TOP, depth = 0, max_depth = 0, vs12 = 0, nev = 0, seen = 0;
+    const char *Fb = reinterpret_cast<const char *>(F);
+    auto step = [&](const char *col, uint32_t p) {   // col: the byte's column of the table
+        const uint64_t ent = *reinterpret_cast<const uint64_t *>(col + state * (SX_FAST_CLASSES * 8u));
+        const uint32_t lo = (uint32_t)ent, hi = (uint32_t)(ent >> 32);
+        state = permute(ctx, lo, lo);              // loop-carried: table load -> permute -> address -> table load
+        seen |= lo;
+        const uint32_t dclamp = depth < SX_FAST_MAX_DEPTH + 1u ? depth : SX_FAST_MAX_DEPTH + 1u;   // also catches a wrapped depth
+        saved[dclamp] = ctx;
+        ctx = (int32_t)lo < 0 ? popctx : permute(ctx, hi, hi);   // a bracket of the wrong kind lands in Q_ERR, where nothing matters any more
+        depth += (uint32_t)((int32_t)lo >> 30);
+        max_depth = depth > max_depth && (int32_t)depth > 0 ? depth : max_depth;
+        const uint32_t dnew = depth < SX_FAST_MAX_DEPTH + 1u ? depth : SX_FAST_MAX_DEPTH + 1u;
+        popctx = saved[(int32_t)dnew - 1];
+        vs12 = (lo & (QF_START << 24)) ? (p << 12) : vs12;
+        ev[nev] = (lo & 0x0f000000u) | vs12 | p;
+        nev += (lo & 0x0f000000u) != 0u;
+        nev = nev < ev_cap ? nev : ev_cap;
+    };
+    // the class of a byte does not depend on the state: fetch four bytes ahead of the chain
+    const char *k[4], *kn[4];
+#pragma unroll
+    for (uint32_t j = 0; j < 4; j++) k[j] = Fb + cls8[text[pos + j]];
+    while (pos + 4u <= end) {
+#pragma unroll
+        for (uint32_t j = 0; j < 4; j++) kn[j] = Fb + cls8[text[pos + 4u + j]];
+#pragma unroll
+        for (uint32_t j = 0; j < 4; j++) step(k[j], pos + j);
+#pragma unroll
+        for (uint32_t j = 0; j < 4; j++) k[j] = kn[j];
+        pos += 4u;
+    }
+#pragma unroll
+    for (uint32_t j = 0; j < 3; j++)
+        if (pos + j < end) step(k[j], pos + j);
+    if (state == Q_NZERO || state == Q_NINT || state == Q_NFRAC || state == Q_NEXP) {   // a number may end with the input
+        ev[nev] = (E_NUM << 24) | vs12 | end;
+        nev = nev + 1u < ev_cap ? nev + 1u : ev_cap;
+        state = ctx & 0xffu;
+    }
+    if (nev >= ev_cap || max_depth > SX_FAST_MAX_DEPTH) return false;   // nev stops at ev_cap: the list may have overflowed
+    if (prefixed && (seen & (QF_SPLIT << 24))) return false;            // a second "data:" somewhere unusual
+    if (!prefixed && state == Q_CUT) return false;                      // no split without the prefix: parse it all
+    const bool parsed = state == Q_AFTER_T || (prefixed && state == Q_DONE);   // Q_AFTER_T is only reachable outside every container
+
+    // ---- pass 2: which of the values on the path did the chunk hold? ----
+    Tracked tr;
+    tr.root = tr.choices = tr.elem0 = tr.delta = V_ABSENT;
+    tr.choices_nonempty = false;
+    tr.content.kind = tr.rcontent.kind = V_ABSENT;
+    tr.content.s = tr.content.e = tr.content.flags = 0;
+    tr.rcontent.s = tr.rcontent.e = tr.rcontent.flags = 0;
+    if (parsed) {
+        uint32_t d2 = 0, lastkey = KEY_NONE, last_started = T_NONE;
+        bool root_obj = false, d2_obj = false, act2 = false, act3 = false, act4 = false, first2 = false;
+        for (uint32_t k = 0; k < nev; k++) {
+            const uint32_t e = ev[k], type = (e >> 24) & 15u, vs = (e >> 12) & 0xfffu, p = e & 0xfffu;
+            if (type == E_KEY || type == E_KEY_ESC) {
+                lastkey = type == E_KEY ? match_key_plain(text, vs + 1u, p) : match_key(text, vs + 1u, p, true);
+                continue;
+            }
+            if (type <= E_LIT_N) {
+                const uint32_t slot =
+                    d2 == 0 ? T_ROOT
+                    : d2 == 1 && root_obj && lastkey == KEY_CHOICES ? T_CHOICES
+                    : d2 == 1 && root_obj && lastkey == KEY_CONTENT ? T_RCONTENT
+                    : d2 == 2 && act2 && (d2_obj ? lastkey == KEY_ZERO : first2) ? T_ELEM0
+                    : d2 == 3 && act3 && lastkey == KEY_DELTA ? T_DELTA
+                    : d2 == 4 && act4 && lastkey == KEY_CONTENT ? T_CONTENT
+                    : T_NONE;
+                const uint32_t vk = type == E_OPEN_OBJ ? V_OBJECT : type == E_OPEN_ARR ? V_ARRAY : type == E_STR ? V_STRING
+                                  : type <= E_NUM_CLOSE ? V_NUMBER : type == E_LIT_T ? V_TRUE : type == E_LIT_F ? V_FALSE : V_NULL;
+                // (re)assigned: it and everything below start over (duplicate keys: last wins)
+                if (slot == T_ROOT) tr.root = vk;
+                if (slot == T_CHOICES) {
+                    tr.choices = vk; tr.choices_nonempty = type == E_STR && p > vs + 1u;
+                    tr.elem0 = tr.delta = tr.content.kind = V_ABSENT; act2 = act3 = act4 = false;
+                }
+                if (slot == T_ELEM0) { tr.elem0 = vk; tr.delta = tr.content.kind = V_ABSENT; act3 = act4 = false; }
+                if (slot == T_DELTA) { tr.delta = vk; tr.content.kind = V_ABSENT; act4 = false; }
+                if (slot == T_CONTENT || slot == T_RCONTENT) {
+                    Val v;
+                    v.kind = vk; v.s = v.e = v.flags = 0;
+                    if (type == E_STR) { v.s = vs + 1u; v.e = p; }
+                    if (vk == V_NUMBER) { v.s = vs; v.e = p; v.flags = number_flags(text, vs, p); }
+                    if (slot == T_CONTENT) tr.content = v; else tr.rcontent = v;
+                }
+                if (d2 == 2 && act2 && !d2_obj) first2 = false;
+                last_started = slot;
+                if (type == E_OPEN_OBJ || type == E_OPEN_ARR) {
+                    const bool obj = type == E_OPEN_OBJ;
+                    if (d2 == 0) root_obj = obj;
+                    if (d2 == 1) d2_obj = obj;
+                    d2++;
+                    if (slot == T_CHOICES) { act2 = true; first2 = !obj; }
+                    if (slot == T_ELEM0) act3 = obj;
+                    if (slot == T_DELTA) act4 = obj;
+                }
+            }
+            if (type == E_NUM_CLOSE || type >= E_CLOSE) {
+                if (type == E_CLOSE_EMPTY) {   // "[]": the value that opened it is the most recent one
+                    if (last_started == T_CONTENT && tr.content.kind == V_ARRAY) tr.content.flags |= AF_EMPTY;
+                    if (last_started == T_RCONTENT && tr.rcontent.kind == V_ARRAY) tr.rcontent.flags |= AF_EMPTY;
+                }
+                d2--;
+                if (d2 < 2) act2 = false;
+                if (d2 < 3) act3 = false;
+                if (d2 < 4) act4 = false;
+            }
+        }
+    }
+    *res = finish(text, parsed, false, tr, kind, out, cap);
+    return true;
 }
 
 }  // namespace sx

@@ -70,37 +70,40 @@ __global__ void __launch_bounds__(128) ss_run_commit_kernel(const SsDesc *desc, 
 // OK) and the delta bytes at delta_arena + in_off (the plaintext layout, so no
 // allocation or scratch is needed: every frame slot holds >= max(16, mlen) bytes).
 #define SS_EXTRACT_THREADS 64
-#define SS_EXTRACT_STAGE 384u                      // chunks up to this size are staged in shared memory
-#define SS_EXTRACT_STRIDE (SS_EXTRACT_STAGE + 4u)  // 97 words: lanes hit distinct banks
-#define SS_EXTRACT_SMEM (SX_TABLE_ENTRIES * 2u + SS_EXTRACT_THREADS * SS_EXTRACT_STRIDE)
-// The automaton's transition table (sx::build_table), uploaded once per device by symrelay_create.
-static __device__ __align__(16) uint16_t g_sx_table[SX_TABLE_ENTRIES];
+#define SS_EXTRACT_STAGE 384u    // chunks up to this size are staged in shared memory and take the two-pass extractor
+#define SS_EXTRACT_EVENTS 95u    // events per thread; a chunk with more falls back to the single pass
+// per thread: the staged chunk (+4 bytes the prefix search may read), then the extractor's scratch.  209 words: lanes hit distinct banks
+#define SS_EXTRACT_STRIDE (SS_EXTRACT_STAGE + 4u + 4u * SX_FAST_SCRATCH_WORDS(SS_EXTRACT_EVENTS))
+#define SS_EXTRACT_SMEM (SX_FAST_ENTRIES * 8u + 256u + SS_EXTRACT_THREADS * SS_EXTRACT_STRIDE)
+
+static __device__ __align__(16) uint16_t g_sx_table[SX_TABLE_ENTRIES];   // single-pass automaton (fallback, long chunks)
+static __device__ __align__(16) uint64_t g_sx_fast[SX_FAST_ENTRIES];     // two-pass grammar table, by byte class
+static __device__ __align__(16) uint8_t g_sx_cls[256];
 __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const SsDesc *desc, uint32_t n, const uint8_t *in,
                                                                        const uint4 *states, uint32_t *status,
                                                                        symrelay_delta *delta, uint8_t *delta_arena) {
-    // The automaton consumes its chunk one byte at a time, each step depending on the last: read from
-    // global memory that is ~600 cycles per byte (measured: 72 us for 16,384 chunks of ~216 B).  So each
-    // thread first pulls its chunk into a private slice of shared memory with 16-byte loads that are all
-    // in flight together, and the byte loop then runs against shared memory.
+    // The grammar pass consumes its chunk one byte at a time, each step depending on the last: read from
+    // global memory that is ~600 cycles per byte.  So each thread first pulls its chunk into a private
+    // slice of shared memory with 16-byte loads that are all in flight together, and the byte loop then
+    // runs against shared memory (chunk, class table and grammar table).
     extern __shared__ __align__(16) uint8_t sx_smem[];
-    uint16_t *table = reinterpret_cast<uint16_t *>(sx_smem);
-    uint8_t *sx_stage = sx_smem + SX_TABLE_ENTRIES * 2u;
-    {
-        const uint4 *src = reinterpret_cast<const uint4 *>(g_sx_table);
-        uint4 *dst = reinterpret_cast<uint4 *>(table);
-        for (uint32_t j = threadIdx.x; j < SX_TABLE_ENTRIES * 2u / 16u; j += blockDim.x) dst[j] = src[j];
-    }
-    __syncthreads();
+    uint64_t *fast = reinterpret_cast<uint64_t *>(sx_smem);
+    uint8_t *cls = sx_smem + SX_FAST_ENTRIES * 8u;
+    uint8_t *sx_stage = cls + 256u;
+    // Three things come from global memory and two of them are a dependent chain (descriptor -> chunk and
+    // provider kind): start the chain first, copy the tables while it is in flight.
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const SsDesc d = desc[i];
-    if (!(d.len_flags & SS_F_EXTRACT) || (d.len_flags & SS_F_OPEN)) return;
+    SsDesc d;
+    d.slot = 0; d.in_off = 0; d.out_off = 0; d.len_flags = 0;
+    if (i < n) d = desc[i];
+    const bool mine_to_do = (d.len_flags & SS_F_EXTRACT) && !(d.len_flags & SS_F_OPEN);
     const uint32_t mlen = d.len_flags & 0xffffffu;
-    const uint32_t kind = states[((size_t)d.slot * 2u) * 3u + 2u].w;   // provider kind lives in the tx state's meta word
-    const uint32_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
     const uint8_t *text = in + d.in_off;
-    if (mlen <= SS_EXTRACT_STAGE) {
-        uint8_t *mine = sx_stage + (size_t)threadIdx.x * SS_EXTRACT_STRIDE;
+    uint8_t *mine = sx_stage + (size_t)threadIdx.x * SS_EXTRACT_STRIDE;
+    const bool staged = mine_to_do && mlen <= SS_EXTRACT_STAGE;
+    uint32_t kind = 0;
+    if (mine_to_do) kind = states[((size_t)d.slot * 2u) * 3u + 2u].w;   // provider kind lives in the tx state's meta word
+    if (staged) {
         const uint4 *src = reinterpret_cast<const uint4 *>(text);
         uint32_t *dst = reinterpret_cast<uint32_t *>(mine);
         const uint32_t n16 = (mlen + 15u) >> 4;
@@ -109,9 +112,24 @@ __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const Ss
             const uint4 v = src[b];
             dst[4 * b] = v.x; dst[4 * b + 1] = v.y; dst[4 * b + 2] = v.z; dst[4 * b + 3] = v.w;
         }
-        text = mine;
     }
-    const sx::Result r = sx::extract_chunk(text, mlen, kind, delta_arena + d.in_off, cap, table);
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(g_sx_fast);
+        uint4 *dst = reinterpret_cast<uint4 *>(fast);
+        for (uint32_t j = threadIdx.x; j < SX_FAST_ENTRIES * 8u / 16u; j += blockDim.x) dst[j] = src[j];
+        if (threadIdx.x < 16u) reinterpret_cast<uint4 *>(cls)[threadIdx.x] = reinterpret_cast<const uint4 *>(g_sx_cls)[threadIdx.x];
+    }
+    __syncthreads();
+    if (!mine_to_do) return;
+    const uint32_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
+    sx::Result r;
+    bool done = false;
+    if (staged) {
+        text = mine;
+        done = sx::extract_fast(mine, mlen, kind, delta_arena + d.in_off, cap, fast, cls,
+                                reinterpret_cast<uint32_t *>(mine + SS_EXTRACT_STAGE + 4u), SS_EXTRACT_EVENTS, &r);
+    }
+    if (!done) r = sx::extract_chunk(text, mlen, kind, delta_arena + d.in_off, cap, g_sx_table);
     status[i] = r.status;
     delta[i].off = d.in_off;
     delta[i].len = r.len;
@@ -429,6 +447,12 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
         std::vector<uint16_t> table(SX_TABLE_ENTRIES);
         sx::build_table(table.data());
         CU(ctx, cudaMemcpyToSymbol(g_sx_table, table.data(), SX_TABLE_ENTRIES * sizeof(uint16_t)));
+        std::vector<uint64_t> fast(SX_FAST_ENTRIES);
+        uint8_t cls[256];
+        if (!sx::build_fast_tables(fast.data(), cls)) return fail(ctx, SYMRELAY_EINVAL, "extractor grammar has more than 32 byte classes");
+        CU(ctx, cudaMemcpyToSymbol(g_sx_fast, fast.data(), SX_FAST_ENTRIES * sizeof(uint64_t)));
+        CU(ctx, cudaMemcpyToSymbol(g_sx_cls, cls, 256));
+        CU(ctx, cudaFuncSetAttribute(ss_extract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_EXTRACT_SMEM));
     }
     sh.init_cap = 4096;
     CU(ctx, cudaHostAlloc(&sh.h_init, sizeof(SsInitRec) * sh.init_cap, cudaHostAllocDefault));

@@ -10,6 +10,7 @@
 #include "../../symmetry_b200/csrc/ss_extract.cuh"
 #include "../../symmetry_b200/csrc/ss_runs.cuh"
 
+#include <cstring>
 #include <vector>
 
 static uint32_t emu_arg_flags = 0;   // SsArgs.flags for the next batches (tests flip SS_ARG_STAGE_INPUT)
@@ -70,13 +71,53 @@ extern "C" int emu_run_batch(const symrelay_desc *desc, const symrelay_tile *til
     return 0;
 }
 
+static uint64_t emu_fast_calls = 0, emu_fast_taken = 0;
+extern "C" void emu_extract_fast_counts(uint64_t *calls, uint64_t *taken) { *calls = emu_fast_calls; *taken = emu_fast_taken; }
+
 // The extractor is thread-local code (no warp collectives): call it directly.
 extern "C" uint32_t emu_extract(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap,
                                 uint32_t *len_out) {
     static uint16_t table[SX_TABLE_ENTRIES];
     static bool built = false;
     if (!built) { sx::build_table(table); built = true; }
-    const sx::Result r = sx::extract_chunk(text, n, kind, out, cap, table);
+    // run on a 16-byte aligned copy (as the kernel sees its arena) and once more at an odd address, so
+    // both the word-skipping and the byte-only paths are compared with the oracle
+    static std::vector<uint8_t> buf;
+    buf.assign((size_t)n + 64, 0);
+    uint8_t *al = buf.data() + ((16 - (reinterpret_cast<uintptr_t>(buf.data()) & 15)) & 15);
+    memcpy(al, text, n);
+    const sx::Result r = sx::extract_chunk(al, n, kind, out, cap, table);
+    {
+        static std::vector<uint8_t> buf2, out2;
+        buf2.assign((size_t)n + 64, 0);
+        out2.assign((size_t)cap + 16, 0);
+        uint8_t *od = buf2.data() + ((16 - (reinterpret_cast<uintptr_t>(buf2.data()) & 15)) & 15) + 1;
+        memcpy(od, text, n);
+        const sx::Result r2 = sx::extract_chunk(od, n, kind, out2.data(), cap, table);
+        if (r2.status != r.status || r2.len != r.len || (r.status == 0 && memcmp(out2.data(), out, r.len < cap ? r.len : cap)))
+            return 0xdeadu;   // the two paths disagree: fail the test loudly
+    }
+    {
+        // the two-pass form the kernel runs on staged chunks, with the kernel's event capacity: whenever
+        // it accepts the chunk it has to agree with the single pass byte for byte
+        static uint64_t fast[SX_FAST_ENTRIES];
+        static uint8_t cls[256];
+        static uint32_t n_cls = 0;
+        if (!n_cls) { n_cls = sx::build_fast_tables(fast, cls); if (!n_cls) return 0xdeaeu; }
+        if (n <= SX_FAST_MAX_LEN) {
+            static std::vector<uint8_t> out3;
+            static uint32_t ev[SX_FAST_SCRATCH_WORDS(95u)];   // 95 events, as in the kernel
+            out3.assign((size_t)cap + 16, 0);
+            sx::Result r3;
+            emu_fast_calls++;
+            if (sx::extract_fast(al, n, kind, out3.data(), cap, fast, cls, ev, 95, &r3)) {
+                emu_fast_taken++;
+                if (r3.status != r.status || r3.len != r.len || (r.status == 0 && memcmp(out3.data(), out, r.len < cap ? r.len : cap)))
+                    return 0xdeafu;
+                for (uint32_t i = cap; i < cap + 16; i++) if (out3[i]) return 0xdeb0u;
+            }
+        }
+    }
     *len_out = r.len;
     return r.status;
 }

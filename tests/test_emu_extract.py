@@ -96,3 +96,64 @@ def test_mutation_fuzz(lib, seed):
         for prov in ("ollama", "llamacpp", "litellm"):
             counts[check(lib, prov, bytes(b))] += 1
     assert counts["ok"] > 6000 and counts["unsupported"] < counts["ok"] // 10
+
+
+def test_two_pass_form_covers_the_matrix_and_falls_back(lib, extract_cases):
+    """emu_extract runs the kernel's two-pass extractor next to the single pass on every call and fails
+    with 0xdea* if they disagree; here: the matrix is handled by the two-pass form itself, and chunks
+    with more events than a thread's list holds fall back without changing the answer."""
+    calls, taken = C.c_uint64(), C.c_uint64()
+    lib.emu_extract_fast_counts(C.byref(calls), C.byref(taken))
+    c0, t0 = calls.value, taken.value
+    for c in extract_cases:
+        run(lib, c["provider"], bytes.fromhex(c["chunk"]))
+    lib.emu_extract_fast_counts(C.byref(calls), C.byref(taken))
+    assert calls.value - c0 == len(extract_cases)
+    # deeply nested cases and a second "data:" in an unusual place go to the single pass
+    assert taken.value - t0 >= len(extract_cases) - 50
+    c0, t0 = calls.value, taken.value
+    busy = [b"data: [" + b"[]," * 120 + b"[]]", b'{"content":[' + b"1," * 200 + b"1]}",
+            b'data: {"choices":[{"delta":{"content":"ok"},"x":[' + b"0," * 150 + b"0]}]}"]
+    for chunk in busy:
+        for prov in ("openai", "ollama", "llamacpp"):
+            assert check(lib, prov, chunk) in ("ok", "unsupported")
+    lib.emu_extract_fast_counts(C.byref(calls), C.byref(taken))
+    assert calls.value - c0 == 9 and taken.value == t0      # every one of them overflowed the event list
+    st, got = run(lib, "ollama", busy[2])
+    assert (st, got) == (0, b"ok")
+    # two events in one chunk are split by the grammar itself; "data:" inside a string is not
+    for chunk, fast in ((b'data: {"content":"a"}\n\ndata: {"content":"b"}\n\n', 1), (b'data: {"content":"a data: b"}', 1), (b'{"content":"a data: b"}', 0),
+                        (b'data: 12data: 13', 0), (b'data: truedata:', 1), (b'data: {"content":"\\u00data:"}', 1)):
+        lib.emu_extract_fast_counts(C.byref(calls), C.byref(taken))
+        t0 = taken.value
+        assert check(lib, "llamacpp", chunk) == "ok"
+        lib.emu_extract_fast_counts(C.byref(calls), C.byref(taken))
+        assert taken.value - t0 == fast, chunk
+    # nesting: the two-pass form takes 13 levels, the single pass 64, 65 are left to the host
+    for depth, want, fast in ((13, 0, 1), (14, 0, 0), (64, 0, 0), (65, 4, 0)):
+        lib.emu_extract_fast_counts(C.byref(calls), C.byref(taken))
+        t0 = taken.value
+        st, got = run(lib, "llamacpp", b"data: " + b"[" * depth + b"]" * depth)
+        lib.emu_extract_fast_counts(C.byref(calls), C.byref(taken))
+        assert st == want and taken.value - t0 == fast
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_second_prefix_fuzz(lib, seed):
+    """Pieces of "data:" dropped anywhere in a chunk: the split the reference does (src/utils.ts:22) is
+    handled by the grammar table in the two-pass form and by a look-ahead in the single pass; both have
+    to agree with the oracle wherever the pieces land (inside strings, escapes, numbers, between events)."""
+    rng = random.Random(1000 + seed)
+    pieces = [b"data:", b"data: ", b"data", b"dat", b"da", b"d", b"ddata:", b"dadata:", b"datdata:", b"datadata:",
+              b"\\u00da", b"\\u00data:", b"ta:", b"a:", b'"}\n\ndata: {"content":"z"}']
+    n = 0
+    for _ in range(2500):
+        b = bytearray(rng.choice(SEEDS))
+        for _m in range(rng.choice([1, 1, 2, 3])):
+            pos = rng.randrange(len(b) + 1)
+            b[pos:pos] = rng.choice(pieces)
+        if rng.random() < 0.15:
+            b = b[: rng.randrange(len(b) + 1)]
+        for prov in ("ollama", "llamacpp", "litellm"):
+            n += check(lib, prov, bytes(b)) == "ok"
+    assert n > 7000
