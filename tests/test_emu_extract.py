@@ -72,11 +72,10 @@ SEEDS = [
 ALPHABET = b'{}[]":,\\ \n\tdata:choicesdeltacontent0123456789.-+eEtruefalsenull\xff\xe4\xb8\xc3\xa9u'
 
 
-@pytest.mark.parametrize("seed", range(6))
-def test_mutation_fuzz(lib, seed):
+def mutated_chunks(seed, count):
+    """Seed chunks with a few random byte edits each (shared with the GPU fuzz in test_gpu_extract.py)."""
     rng = random.Random(seed)
-    counts = {"ok": 0, "unsupported": 0}
-    for _ in range(2500):
+    for _ in range(count):
         b = bytearray(rng.choice(SEEDS))
         for _m in range(rng.choice([0, 1, 1, 2, 3, 6])):
             op = rng.randrange(4)
@@ -93,8 +92,32 @@ def test_mutation_fuzz(lib, seed):
                 b[lo:lo] = b[lo:hi][:40]  # duplicate a slice (duplicate keys, repeated events)
         if rng.random() < 0.1:
             b = b[: rng.randrange(len(b) + 1)]  # chunk cut mid-JSON
+        yield bytes(b)
+
+
+SPLIT_PIECES = [b"data:", b"data: ", b"data", b"dat", b"da", b"d", b"ddata:", b"dadata:", b"datdata:", b"datadata:",
+                b"\\u00da", b"\\u00data:", b"ta:", b"a:", b'"}\n\ndata: {"content":"z"}']
+
+
+def split_chunks(seed, count):
+    """Seed chunks with pieces of "data:" dropped anywhere."""
+    rng = random.Random(1000 + seed)
+    for _ in range(count):
+        b = bytearray(rng.choice(SEEDS))
+        for _m in range(rng.choice([1, 1, 2, 3])):
+            pos = rng.randrange(len(b) + 1)
+            b[pos:pos] = rng.choice(SPLIT_PIECES)
+        if rng.random() < 0.15:
+            b = b[: rng.randrange(len(b) + 1)]
+        yield bytes(b)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_mutation_fuzz(lib, seed):
+    counts = {"ok": 0, "unsupported": 0}
+    for b in mutated_chunks(seed, 2500):
         for prov in ("ollama", "llamacpp", "litellm"):
-            counts[check(lib, prov, bytes(b))] += 1
+            counts[check(lib, prov, b)] += 1
     assert counts["ok"] > 6000 and counts["unsupported"] < counts["ok"] // 10
 
 
@@ -143,17 +166,8 @@ def test_second_prefix_fuzz(lib, seed):
     """Pieces of "data:" dropped anywhere in a chunk: the split the reference does (src/utils.ts:22) is
     handled by the grammar table in the two-pass form and by a look-ahead in the single pass; both have
     to agree with the oracle wherever the pieces land (inside strings, escapes, numbers, between events)."""
-    rng = random.Random(1000 + seed)
-    pieces = [b"data:", b"data: ", b"data", b"dat", b"da", b"d", b"ddata:", b"dadata:", b"datdata:", b"datadata:",
-              b"\\u00da", b"\\u00data:", b"ta:", b"a:", b'"}\n\ndata: {"content":"z"}']
     n = 0
-    for _ in range(2500):
-        b = bytearray(rng.choice(SEEDS))
-        for _m in range(rng.choice([1, 1, 2, 3])):
-            pos = rng.randrange(len(b) + 1)
-            b[pos:pos] = rng.choice(pieces)
-        if rng.random() < 0.15:
-            b = b[: rng.randrange(len(b) + 1)]
+    for b in split_chunks(seed, 2500):
         for prov in ("ollama", "llamacpp", "litellm"):
-            n += check(lib, prov, bytes(b)) == "ok"
+            n += check(lib, prov, b) == "ok"
     assert n > 7000

@@ -108,6 +108,45 @@ def test_config5_chat_completions_accumulate(relay):
     assert all(len(c) > 0 for c in completion)
 
 
+@pytest.mark.parametrize("provider", ["ollama", "llamacpp", "litellm"])
+def test_fuzzed_chunks_match_the_oracle(relay, provider):
+    """The emulator tests' mutation and second-"data:" fuzz, here compiled by nvcc and run on the GPU:
+    6,000 chunks in one batch, one stream each, every verdict and delta against oracle/extract.py."""
+    import symmetry_b200 as sb
+    from test_emu_extract import mutated_chunks, split_chunks
+
+    chunks = list(mutated_chunks(11, 4000)) + list(split_chunks(11, 2000))
+    chunks = [c if c else b" " for c in chunks]
+    n = len(chunks)
+    rng = np.random.default_rng(23)
+    keys = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    hdrs = rng.integers(0, 256, (n, 24), dtype=np.uint8)
+    slots = relay.open_streams(keys, hdrs, None, None, provider=sb.provider_kind(provider))
+    st, deltas, wire, w_offs = run_extract_batch(relay, slots, chunks)
+    n_ok = n_throw = n_uns = 0
+    for i, c in enumerate(chunks):
+        code = int(st[i]) & 0xFF
+        want_code, want = ex.extract(provider, c)
+        if code == sb.relay.ST_EXTRACT_UNSUPPORTED:
+            n_uns += 1
+            continue
+        if want_code == ex.THROW:
+            assert code == sb.relay.ST_EXTRACT_THROW, (provider, c)
+            n_throw += 1
+            continue
+        assert code == 0 and deltas[i] == want, (provider, c, code, deltas[i], want)
+        n_ok += 1
+    assert n_ok > 3000 and n_uns < n // 10, (n_ok, n_throw, n_uns)
+    for i in range(0, n, 61):   # sealed frames of accepted chunks are libsodium's; rejected ones left the state alone
+        ref = ls.State(bytes(keys[i]), bytes(hdrs[i]))
+        if int(st[i]) & 0xFF == 0:
+            want = ref.seal_frame(chunks[i])
+            assert bytes(wire[w_offs[i] : w_offs[i] + len(want)]) == want
+        assert relay.export(int(slots[i]))[0] == ref.raw
+    for s_ in slots:
+        relay.close_stream(int(s_))
+
+
 def test_extract_flag_needs_delta_buffers(relay):
     import symmetry_b200 as sb
 
