@@ -287,7 +287,25 @@ struct symrelay_ctx {
     bool pdl = true;   // SYMRELAY_PDL=0 turns programmatic dependent launch off
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
     uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
+    // SYMRELAY_PROF=1: where a host batch spends its time (printed by symrelay_destroy)
+    bool prof = false;
+    double prof_t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint64_t prof_n = 0;
 };
+
+static inline double prof_now() {
+    struct timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return (double)t.tv_sec * 1e6 + 1e-3 * (double)t.tv_nsec;
+}
+#define PROF_MARK(ctx, k)                                        \
+    do {                                                         \
+        if ((ctx)->prof) {                                       \
+            const double prof_t1 = prof_now();                   \
+            (ctx)->prof_t[k] += prof_t1 - prof_t0;               \
+            prof_t0 = prof_t1;                                   \
+        }                                                        \
+    } while (0)
 
 static bool is_library_pinned(const symrelay_ctx *ctx, const void *p, uint64_t bytes) {
     const uintptr_t a = reinterpret_cast<uintptr_t>(p);
@@ -518,6 +536,7 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (!ctx->opts.max_batch_frames) ctx->opts.max_batch_frames = 131072;
     ctx->opts.stage_bytes = align_up(ctx->opts.stage_bytes, 256);
     if (ctx->opts.flags & SYMRELAY_OPT_NO_ZERO_COPY) ctx->zero_copy_max = 0;
+    { const char *e = getenv("SYMRELAY_PROF"); ctx->prof = e && e[0] == '1'; }
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE_DEV")) ctx->device_arg_flags = atoi(m) ? (SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT) : 0u;
@@ -543,6 +562,12 @@ static void sched_free(symrelay_ctx *ctx, int g);
 
 void symrelay_destroy(symrelay_ctx *ctx) {
     if (!ctx) return;
+    if (ctx->prof && ctx->prof_n) {
+        const char *names[8] = {"recycle", "plan", "checks", "ctrl copy", "launch", "event record", "wait", ""};
+        fprintf(stderr, "symrelay host batch profile over %llu batches (us per batch):", (unsigned long long)ctx->prof_n);
+        for (int k = 0; k < 7; k++) fprintf(stderr, " %s %.2f", names[k], ctx->prof_t[k] / (double)ctx->prof_n);
+        fprintf(stderr, "\n");
+    }
     for (int g = 0; g < ctx->n_gpus; g++) { shard_free(ctx->shard[g]); sched_free(ctx, g); }
     delete ctx;
 }
@@ -779,11 +804,13 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         return fail(ctx, SYMRELAY_EINVAL, "arena (%llu in / %llu out bytes) exceeds stage_bytes %llu",
                     (unsigned long long)in_bytes, (unsigned long long)out_bytes, (unsigned long long)ctx->opts.stage_bytes);
     if ((in_bytes & 15u) || (out_bytes & 15u)) return fail(ctx, SYMRELAY_EINVAL, "arena sizes must be multiples of 16");
+    double prof_t0 = ctx->prof ? prof_now() : 0.0;
     CU(ctx, set_device(sh.dev));
     const int64_t seq = sh.next_ticket_seq++;
     Stage &st = sh.stages[(size_t)(seq % (int64_t)sh.stages.size())];
     int rc = finish_stage(ctx, sh, st);  // recycle: the batch that used this stage P submissions ago
     if (rc) return rc;
+    PROF_MARK(ctx, 0);
 
     // control block: tiles ‖ descs, planned straight into pinned memory
     symrelay_tile *h_tiles = reinterpret_cast<symrelay_tile *>(st.h_ctrl);
@@ -792,6 +819,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     chk.in_bytes = in_bytes; chk.out_bytes = out_bytes; chk.max_streams = ctx->opts.max_streams;
     const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk, &chk);
     if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
+    PROF_MARK(ctx, 1);
     // bounds / ownership checks (computed by the planner's first pass over the descriptors)
     uint32_t bad = chk.out_of_bounds;
     const uint32_t any_flags = chk.any_flags, out_overlap = chk.out_overlap;
@@ -823,8 +851,10 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (extract && !st.d_delta_arena) CU(ctx, cudaMalloc(&st.d_delta_arena, ctx->opts.stage_bytes));
     if (runs && !st.d_run_nonce) CU(ctx, cudaMalloc(&st.d_run_nonce, (size_t)ctx->opts.max_batch_frames * sizeof(uint4)));
     const size_t tiles_bytes = align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
+    PROF_MARK(ctx, 2);
     memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
     const size_t ctrl_bytes = tiles_bytes + (size_t)n * sizeof(symrelay_desc);
+    PROF_MARK(ctx, 3);
 
     // Small batches whose arenas are library-pinned run ZERO-COPY: one launch reads descriptors and
     // payload straight from pinned host memory over PCIe and writes wire bytes and status straight back
@@ -845,7 +875,10 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
                                       (ctx->stage_input ? (SS_ARG_STAGE_INPUT | (out_overlap ? 0u : SS_ARG_STAGE_OUTPUT)) : 0u),
                           runs ? st.d_run_nonce : nullptr, &sh);
         if (rc) return rc;
+        PROF_MARK(ctx, 4);
         CU(ctx, cudaEventRecord(st.ev_out, sh.s_k));
+        PROF_MARK(ctx, 5);
+        ctx->prof_n++;
         ctx->zero_copy_batches++;
         st.busy = true;
         st.n = n;
@@ -901,7 +934,12 @@ int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket) {
     const int64_t seq = ticket >> 3;
     if (seq >= sh.next_ticket_seq) return fail(ctx, SYMRELAY_ENOENT, "ticket not issued");
     Stage &st = sh.stages[(size_t)(seq % (int64_t)sh.stages.size())];
-    if (st.busy && st.ticket == ticket) return finish_stage(ctx, sh, st);
+    if (st.busy && st.ticket == ticket) {
+        double prof_t0 = ctx->prof ? prof_now() : 0.0;
+        const int rc = finish_stage(ctx, sh, st);
+        PROF_MARK(ctx, 6);
+        return rc;
+    }
     return 0;  // already recycled => already finished
 }
 
