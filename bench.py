@@ -46,9 +46,10 @@ def workload(name: str, n_gpus: int):
     elif name == "c3":
         total = 65536
         lens = synth.power_law_lens(total)[: total // n_gpus]
-        if os.environ.get("BENCH_C3_SORTED"):
-            lens = np.sort(lens)
-        desc = "configs[2]: 65,536 streams, power-law frames 32 B-16 KiB (alpha 1.2), sharded by slot"
+        desc = "configs[2]: 65,536 streams, power-law frames 32 B-16 KiB (alpha 1.2), sharded by slot, frames in arrival order"
+        if os.environ.get("BENCH_C3_SORTED", "0") not in ("", "0"):
+            lens = np.sort(lens)     # what a gather step that buckets frames by size would hand over
+            desc = desc.replace("frames in arrival order", "frames bucketed by size")
         scaling = "strong"
     elif name == "c4":
         lens = np.full(16384, 65536, dtype=np.int64)
@@ -737,7 +738,7 @@ def run_c5(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20000)
+    ap.add_argument("--steps", type=int, default=None, help="default: 20000 for c2, 200 for c3, 64 for c4, 360 for c5")
     ap.add_argument("--warmup", type=int, default=200)
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
@@ -748,6 +749,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (huge workloads)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step directly (no CUDA graph)")
     args = ap.parse_args()
+    if args.steps is None:   # a step of c3/c4/c5 is 10-400x a step of c2
+        args.steps = {"c2": 20000, "c3": 200, "c4": 64, "c5": 360}.get(args.workload, 20000)
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":
