@@ -296,3 +296,28 @@ def test_two_gpus_in_one_context_shard_by_slot():
             want = {}
         for i in (0, 1, n - 2, n - 1):
             assert r.export(slots[i])[0] == refs[i].raw
+        # the extractor's tables are per GPU: chunks of streams on either GPU give the oracle's deltas
+        import batch_util as bu
+        from oracle import extract as ex
+        from symmetry_b200 import synth
+
+        ekeys, ehdrs = synth.stream_keys(256, first=5000)
+        eslots = [int(s) for s in r.open_streams(ekeys, ehdrs, None, None, provider=sb.PROVIDER_OLLAMA)]
+        chunks = [synth.chat_chunks(3, seed=9, stream_id=i)[1] for i in range(256)]
+        for g in (0, 1):
+            idx = [i for i in range(256) if eslots[i] % 2 == g]
+            assert idx
+            lens = [len(chunks[i]) for i in idx]
+            p_offs, p_bytes = bu.plain_layout(lens)
+            w_offs, w_bytes = bu.wire_layout(lens)
+            plain, wire, darena = r.alloc_pinned(p_bytes), r.alloc_pinned(w_bytes), r.alloc_pinned(p_bytes)
+            plain[:] = 0
+            for i, o in zip(idx, p_offs):
+                plain[o : o + len(chunks[i])] = np.frombuffer(chunks[i], dtype=np.uint8)
+            delta = np.zeros(len(idx), dtype=sb.DELTA_DTYPE)
+            d = bu.make_descs([eslots[i] for i in idx], lens, p_offs, w_offs, extract=True)
+            st = r.batch_host(d, plain, wire, delta=delta, delta_arena=darena)
+            assert (st == 0).all()
+            for k, i in enumerate(idx):
+                off, ln = int(delta[k]["off"]), int(delta[k]["len"])
+                assert bytes(darena[off : off + ln]) == ex.extract("ollama", chunks[i])[1]
