@@ -247,7 +247,10 @@ SYMRELAY_API int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *des
 /* Pipelined form of the same call: returns a ticket (>= 0) at once; buffers
  * must stay valid until symrelay_batch_wait(ticket) returns.  Batches execute
  * in submission order, so consecutive batches may carry consecutive frames of
- * the same streams. */
+ * the same streams.  The out arena, status and delta are valid only after
+ * symrelay_batch_wait(ticket) has returned: a pipelined small batch keeps its
+ * results on the device until the next batch's kernel (or the wait itself)
+ * posts them to the host, and the whole out arena is written, gaps included. */
 SYMRELAY_API int64_t symrelay_batch_submit(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, const uint8_t *in,
                               uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
                               symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes);

@@ -98,7 +98,23 @@ struct SsArgs {
     uint32_t *status;
     uint32_t flags;
     const uint4 *run_nonce;   // scratch: per-descriptor nonce for SS_F_RUN frames (written by ss_run_nonce_kernel)
+    // Write-back of the PREVIOUS batch (host pipeline only, see submit_locked): that batch left its wire
+    // bytes and statuses in device staging; this kernel posts them to the caller's host memory once the
+    // previous kernel is complete, and the stores land while this batch computes.
+    const uint4 *wb_src = nullptr;
+    uint4 *wb_dst = nullptr;
+    uint32_t wb_n16 = 0;
+    const uint32_t *wb_status_src = nullptr;
+    uint32_t *wb_status_dst = nullptr;
+    uint32_t wb_n_status = 0;
 };
+
+// Every warp of the grid takes a stripe.  Call after ss_pdl_wait().
+SS_DEV void ss_write_back(const SsArgs &a, uint32_t warp, uint32_t n_warps, uint32_t lane) {
+    if (!a.wb_n16) return;
+    for (uint32_t i = warp * 32u + lane; i < a.wb_n16; i += n_warps * 32u) a.wb_dst[i] = a.wb_src[i];
+    for (uint32_t i = warp * 32u + lane; i < a.wb_n_status; i += n_warps * 32u) a.wb_status_dst[i] = a.wb_status_src[i];
+}
 
 // ---------------------------------------------------------------- ChaCha20 --
 // Double rounds unrolled per loop trip.  1 keeps the kernels' code inside the
@@ -465,6 +481,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
         if (valid && is_open && b_first == 0u) ss_load_mac(src + mlen, wmac);
     }
     ss_pdl_wait();   // from here on we touch what the previous kernel may have written
+    if (!BULK) ss_write_back(a, tile_idx, a.n_tiles, lane);
 
     // A frame the extractor refused (TypeError in the reference, or a shape it leaves to the host)
     // is not sealed: provider.ts:243-248 throws before peer.write(chunk).
@@ -835,6 +852,7 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx) {
     d.slot = d.in_off = d.out_off = d.len_flags = 0;
     if (valid) d = a.desc[tile.first + lane];
     ss_pdl_wait();
+    ss_write_back(a, tile_idx, a.n_tiles, lane);
     const uint32_t lf = d.len_flags;
     if (valid && (lf & SS_F_EXTRACT) && !(lf & SS_F_OPEN) && a.status[tile.first + lane] != SS_ST_OK) valid = false;
     if (!valid) return;
