@@ -14,12 +14,12 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsymrelay.so")
-SOURCES = ["symrelay.cu"]
-HEADERS = ["ss_core.cuh", "plan.h", os.path.join("..", "..", "include", "symrelay.h")]
+SOURCES = ["symrelay.cu", "plan_scan_avx2.cpp"]
+HEADERS = ["ss_core.cuh", "plan.h", "plan_scan_avx2.cpp", os.path.join("..", "..", "include", "symrelay.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
-    "-O3", "-lineinfo", "-std=c++17",
+    "-O3", "-lineinfo", "-std=c++17", "-DSYMRELAY_HAVE_AVX2_SCAN",
     "-Xcompiler", "-fPIC,-O3,-fvisibility=hidden",
     "-shared", "-cudart", "static", "-Xlinker", "--exclude-libs,ALL",
     "-Xptxas", "-v",

@@ -7,6 +7,7 @@
 // a frame with more than 30 payload blocks gets a bulk tile of its own.
 #pragma once
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/symrelay.h"
 
@@ -45,20 +46,13 @@ struct symrelay_plan_check {
     uint32_t out_overlap;     // output rows (16 B) not strictly increasing in descriptor order
 };
 
-static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles,
-                                           uint32_t max_tiles, uint32_t *n_bulk_out,
-                                           symrelay_plan_check *chk = nullptr) {
-    static thread_local std::vector<uint32_t> ncv;
-    if (ncv.size() < 3u * (size_t)n) ncv.resize(3u * (size_t)n);
-    uint32_t *nc = ncv.data();
-    uint32_t *row_lo = nc + n, *row_hi = nc + 2u * (size_t)n;   // output rows in 16-byte units
-    // pass 1: no loop-carried dependency, so the compiler vectorises it
-    // (all 32-bit: offsets are uint32 and arenas are capped just below 4 GiB, so `off > size - need` cannot wrap)
+// Pass 1 of the planner.  No loop-carried dependency and all 32-bit (offsets are uint32 and arenas are
+// capped just below 4 GiB, so `off > size - need` cannot wrap).  out: bad, oob, any_flags, nc_min, nc_max,
+// overlap (output rows of 16 bytes not strictly increasing in descriptor order).
+static inline void symrelay_plan_scan_scalar(const symrelay_desc *desc, uint32_t n, uint32_t *nc, uint32_t *row_lo,
+                                             uint32_t *row_hi, uint32_t in_bytes, uint32_t out_bytes, uint32_t max_streams,
+                                             uint32_t out[6]) {
     uint32_t bad = 0, oob = 0, any_flags = 0, nc_min = 0xffffffffu, nc_max = 0;
-    const uint64_t cap = 0xffffffffull;
-    const uint32_t in_bytes = (uint32_t)(chk && chk->in_bytes < cap ? chk->in_bytes : cap);
-    const uint32_t out_bytes = (uint32_t)(chk && chk->out_bytes < cap ? chk->out_bytes : cap);
-    const uint32_t max_streams = chk ? chk->max_streams : 0xffffffffu;
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t lf = desc[i].len_flags, in_off = desc[i].in_off, out_off = desc[i].out_off;
         const uint32_t mlen = lf & SYMRELAY_LEN_MASK;
@@ -77,12 +71,40 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
         row_lo[i] = out_off >> 4;
         row_hi[i] = (out_off >> 4) + (((out_off & 15u) + need_out + 15u) >> 4);
     }
-    if (chk) {
-        // output rows strictly increasing in descriptor order?  (plain arrays: vectorises without gathers)
-        uint32_t overlap = 0;
-        for (uint32_t i = 1; i < n; i++) overlap |= (uint32_t)(row_lo[i] < row_hi[i - 1]);
-        chk->out_of_bounds = oob; chk->any_flags = any_flags; chk->out_overlap = overlap;
-    }
+    uint32_t overlap = 0;   // plain arrays: vectorises without gathers
+    for (uint32_t i = 1; i < n; i++) overlap |= (uint32_t)(row_lo[i] < row_hi[i - 1]);
+    out[0] = bad; out[1] = oob; out[2] = any_flags; out[3] = nc_min; out[4] = nc_max; out[5] = overlap;
+}
+
+// The library links plan_scan_avx2.cpp (SYMRELAY_HAVE_AVX2_SCAN) and uses it where the CPU has AVX2.
+#ifdef SYMRELAY_HAVE_AVX2_SCAN
+extern "C" void symrelay_plan_scan_avx2(const symrelay_desc *desc, uint32_t n, uint32_t *nc, uint32_t *row_lo, uint32_t *row_hi,
+                                        uint32_t in_bytes, uint32_t out_bytes, uint32_t max_streams, uint32_t out[6]);
+extern "C" int symrelay_plan_scan_has_avx2(void);
+#endif
+static inline void symrelay_plan_scan(const symrelay_desc *desc, uint32_t n, uint32_t *nc, uint32_t *row_lo, uint32_t *row_hi,
+                                      uint32_t in_bytes, uint32_t out_bytes, uint32_t max_streams, uint32_t out[6]) {
+#ifdef SYMRELAY_HAVE_AVX2_SCAN
+    static const int have = symrelay_plan_scan_has_avx2() && !getenv("SYMRELAY_NO_AVX2");   // the variable is a kill switch
+    if (have) { symrelay_plan_scan_avx2(desc, n, nc, row_lo, row_hi, in_bytes, out_bytes, max_streams, out); return; }
+#endif
+    symrelay_plan_scan_scalar(desc, n, nc, row_lo, row_hi, in_bytes, out_bytes, max_streams, out);
+}
+
+static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles,
+                                           uint32_t max_tiles, uint32_t *n_bulk_out,
+                                           symrelay_plan_check *chk = nullptr) {
+    static thread_local std::vector<uint32_t> ncv;
+    if (ncv.size() < 3u * (size_t)n) ncv.resize(3u * (size_t)n);
+    uint32_t *nc = ncv.data();
+    uint32_t *row_lo = nc + n, *row_hi = nc + 2u * (size_t)n;   // output rows in 16-byte units
+    // pass 1: validation, block counts, output rows
+    const uint64_t cap = 0xffffffffull;
+    uint32_t scan[6];
+    symrelay_plan_scan(desc, n, nc, row_lo, row_hi, (uint32_t)(chk && chk->in_bytes < cap ? chk->in_bytes : cap),
+                       (uint32_t)(chk && chk->out_bytes < cap ? chk->out_bytes : cap), chk ? chk->max_streams : 0xffffffffu, scan);
+    const uint32_t bad = scan[0], oob = scan[1], any_flags = scan[2], nc_min = scan[3], nc_max = scan[4];
+    if (chk) { chk->out_of_bounds = oob; chk->any_flags = any_flags; chk->out_overlap = scan[5]; }
     if (bad) return SYMRELAY_EINVAL;
     uint64_t n_tiles = 0;
     uint32_t n_bulk = 0;

@@ -68,3 +68,18 @@ def test_product_never_imports_the_oracle():
                     src = f.read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), fn
                 assert "ssref_" not in src and "libss_emu" not in src and "nacl" not in src, fn
+
+
+def test_avx2_descriptor_scan_matches_the_scalar_loop(tmp_path):
+    """The host planner's first pass has an AVX2 form (symmetry_b200/csrc/plan_scan_avx2.cpp) that the library
+    picks at run time; tests/emu/scan_check.cpp runs it against the scalar loop of plan.h on 20,000 random
+    batches with misaligned, oversized, out-of-bounds and overlapping descriptors mixed in."""
+    import subprocess
+
+    exe = str(tmp_path / "scan_check")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emu", "scan_check.cpp"),
+                    os.path.join(ROOT, "symmetry_b200", "csrc", "plan_scan_avx2.cpp")], check=True)
+    res = subprocess.run([exe], capture_output=True, text=True)
+    if res.returncode == 77:
+        pytest.skip("this CPU has no AVX2")
+    assert res.returncode == 0, res.stdout + res.stderr
