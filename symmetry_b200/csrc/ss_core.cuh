@@ -394,12 +394,14 @@ SS_DEV void ss_load_mac(const uint8_t *p, uint32_t w[4]) {
 // --------------------------------------------------------------- the tile ---
 // One warp processes one tile.  BULK == false: up to 16 small frames packed in
 // the warp, one pass.  BULK == true: one frame of any size, lanes stride by 32.
+// `given`: the tile itself when the launch carried the tile list in its parameters (small host batches:
+// one dependent read over PCIe fewer), else it is read from a.tiles.
 template <bool BULK>
-SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx) {
+SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_pdl_launch_dependents();   // the next batch's kernel may start its own prologue now
     if (!(a.flags & SS_ARG_INPUT_INDEPENDENT)) ss_pdl_wait();   // descriptors may come from the previous kernel
-    const SsTile tile = a.tiles[tile_idx];
+    const SsTile tile = given ? *given : a.tiles[tile_idx];
     const uint32_t nfr = BULK ? 1u : (tile.n_kind & 0xffffu);
 
     // ---- lane -> (frame f, first lane st of that frame) ---------------------
@@ -841,11 +843,11 @@ SS_DEV void ss_thread_window(uint32_t acc[5], uint32_t w[16], uint32_t q, uint32
     ss_phorner(acc, w, (uint32_t)nbytes, r);
 }
 
-SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx) {
+SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_pdl_launch_dependents();
     if (!(a.flags & SS_ARG_INPUT_INDEPENDENT)) ss_pdl_wait();
-    const SsTile tile = a.tiles[tile_idx];
+    const SsTile tile = given ? *given : a.tiles[tile_idx];
     const uint32_t nfr = tile.n_kind & 0xffffu;
     bool valid = lane < nfr;
     SsDesc d;

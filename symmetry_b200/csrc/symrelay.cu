@@ -42,6 +42,21 @@ __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_kernel(Ss
     else ss_process_tile<false>(a, warp);
 }
 
+// The same kernel for small host batches: the tile list rides in the launch parameters (constant bank), so a
+// warp does not start with a read of host memory that only tells it where its descriptors are.  Zero-copy
+// batches begin with three dependent reads over PCIe (tile -> descriptors -> payload); this removes the first.
+#define SS_INLINE_TILES 448u   // 3.5 KB: with SsArgs under the 4 KB parameter limit
+struct SsTileBlock {
+    SsTile t[SS_INLINE_TILES];
+};
+__global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_inline_kernel(SsArgs a, SsTileBlock tb) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= a.n_tiles) return;
+    const SsTile tile = tb.t[warp];
+    if (tile.n_kind & (1u << 17)) ss_process_thread_tile(a, warp, &tile);
+    else ss_process_tile<false>(a, warp, &tile);
+}
+
 // Bulk tiles: one frame per warp, lanes stride over its 64-byte blocks.
 // a.tiles already points at the first bulk tile.
 #ifndef SS_BULK_MIN_BLOCKS
@@ -303,6 +318,7 @@ struct symrelay_ctx {
     uint64_t zero_copy_max = 1ull << 20;                   // in+out bytes up to which a batch runs zero-copy
     uint64_t zero_copy_batches = 0, staged_batches = 0;
     bool pdl = true;   // SYMRELAY_PDL=0 turns programmatic dependent launch off
+    bool inline_tiles = true;   // SYMRELAY_INLINE_TILES=0: small host batches read their tile list from memory like all others
     bool defer_wb = true;   // SYMRELAY_DEFER=0: pipelined zero-copy batches write their results to the host themselves
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
     uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
@@ -386,7 +402,7 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
                         uint32_t n_tiles, uint32_t n_bulk, const uint8_t *d_in, uint8_t *d_out, uint4 *d_states,
                         uint32_t *d_status, symrelay_delta *d_delta, uint8_t *d_delta_arena, cudaStream_t stream,
                         uint32_t arg_flags = 0, uint4 *d_run_nonce = nullptr, Shard *fork = nullptr,
-                        const Stage *write_back = nullptr) {
+                        const Stage *write_back = nullptr, const symrelay_tile *host_tiles = nullptr) {
     const uint32_t n_packed = n_tiles - n_bulk;
     if (d_run_nonce) {
         ss_run_nonce_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
@@ -448,7 +464,22 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
         }
         const uint32_t threads = n_packed <= 148u * 8u ? 32u : 128u;  // few tiles: one warp per SM sub-partition
         const uint32_t wpb = threads / 32u;
-        CU(ctx, launch_pdl(ss_packed_kernel, (n_packed + wpb - 1) / wpb, threads, stream, pdl && !side, a));
+        if (host_tiles && n_packed <= SS_INLINE_TILES && ctx->inline_tiles) {
+            static thread_local SsTileBlock tb;
+            memcpy(tb.t, host_tiles, (size_t)n_packed * sizeof(SsTile));
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((n_packed + wpb - 1) / wpb);
+            cfg.blockDim = dim3(threads);
+            cfg.stream = stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = (pdl && !side) ? 1 : 0;
+            CU(ctx, cudaLaunchKernelEx(&cfg, ss_packed_inline_kernel, a, tb));
+        } else {
+            CU(ctx, launch_pdl(ss_packed_kernel, (n_packed + wpb - 1) / wpb, threads, stream, pdl && !side, a));
+        }
         ctx->launches++;
     }
     if (side) CU(ctx, cudaStreamWaitEvent(stream, fork->ev_join, 0));
@@ -573,6 +604,7 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (ctx->opts.flags & SYMRELAY_OPT_NO_ZERO_COPY) ctx->zero_copy_max = 0;
     { const char *e = getenv("SYMRELAY_PROF"); ctx->prof = e && e[0] == '1'; }
     { const char *e = getenv("SYMRELAY_DEFER"); if (e && e[0] == '0') ctx->defer_wb = false; }
+    { const char *e = getenv("SYMRELAY_INLINE_TILES"); if (e && e[0] == '0') ctx->inline_tiles = false; }
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE_DEV")) ctx->device_arg_flags = atoi(m) ? (SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT) : 0u;
@@ -954,7 +986,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
                           reinterpret_cast<const symrelay_tile *>(k_ctrl), (uint32_t)n_tiles, n_bulk, k_in,
                           defer ? st.d_out : out, sh.d_states, defer ? st.d_status : st.h_status,
                           extract ? st.h_delta : nullptr, extract ? delta_arena : nullptr, sh.s_k, flags,
-                          runs ? st.d_run_nonce : nullptr, &sh, carry);
+                          runs ? st.d_run_nonce : nullptr, &sh, carry, reinterpret_cast<const symrelay_tile *>(k_ctrl));
         if (rc) return rc;
         PROF_MARK(ctx, 4);
         CU(ctx, cudaEventRecord(st.ev_out, sh.s_k));

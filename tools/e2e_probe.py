@@ -15,7 +15,8 @@ from symmetry_b200 import synth  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 mlen = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 for zc in (True, False):
-    with sb.SymRelay(gpu_ids=(0,), max_streams=4 * n, zero_copy=zc) as r:
+    DEPTH = int(os.environ.get("PROBE_DEPTH", "4"))
+    with sb.SymRelay(gpu_ids=(0,), max_streams=4 * n, zero_copy=zc, pipeline_depth=max(DEPTH, 2)) as r:
         keys, hdrs = synth.stream_keys(n)
         slots = r.open_streams(keys, hdrs, keys, hdrs)
         lens = [mlen] * n
@@ -66,10 +67,10 @@ for zc in (True, False):
         dd = bu.make_descs(slots, lens, p_offs, w_offs)
         st2 = np.zeros(16 * n, dtype=np.uint32)
         subs = C.c_double(0)
-        secs = drv.e2e_ring_run(r.ctx, dd.ctypes.data, n, ring.ctypes.data, slot_bytes, P, P, Wb, 16, 4, 0, K,
+        secs = drv.e2e_ring_run(r.ctx, dd.ctypes.data, n, ring.ctypes.data, slot_bytes, P, P, Wb, 16, DEPTH, 0, K,
                                 st2.ctypes.data, C.byref(subs))
         assert secs > 0, secs
-        print(f"   C driver: pipelined {secs/K*1e6:.1f} us/batch (submit calls {subs.value/K*1e6:.1f} us/batch)")
+        print(f"   C driver (depth {DEPTH}): pipelined {secs/K*1e6:.1f} us/batch (submit calls {subs.value/K*1e6:.1f} us/batch)")
         print(f"zero_copy={zc} n={n} mlen={mlen}: submit call p50 {np.median(lat[:,0]):.1f} us, round trip p50 "
               f"{np.median(lat[:,1]):.1f} us p99 {np.percentile(lat[:,1],99):.1f} us; pipelined {dt/K*1e6:.1f} us/batch "
               f"(submit calls {sub/K*1e6:.1f} us/batch)")
