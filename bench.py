@@ -268,7 +268,7 @@ def run_ours(args):
     n = len(lens)
     lay = Layout(lens)
     K, W = args.steps, args.warmup
-    D_DEV, D_E2E = 1, 4
+    D_DEV, D_E2E = 1, int(os.environ.get("BENCH_E2E_DEPTH", "6"))
     stage_bytes = max(64 << 20, (lay.in_bytes + 4095) // 4096 * 4096)
     relay = sb.SymRelay(gpu_ids=(local,), max_streams=max(4 * n, 4096), pipeline_depth=D_E2E,
                         stage_bytes=stage_bytes, max_batch_frames=max(2 * n, 4096))

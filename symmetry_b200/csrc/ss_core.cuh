@@ -107,7 +107,18 @@ struct SsArgs {
     const uint32_t *wb_status_src = nullptr;
     uint32_t *wb_status_dst = nullptr;
     uint32_t wb_n_status = 0;
+    unsigned long long *dbg_ts = nullptr;   // SYMRELAY_TS=1 (diagnostics): {kernel start, past the dependency wait, end} of warp 0
 };
+
+SS_DEV void ss_dbg_stamp(const SsArgs &a, uint32_t tile_idx, uint32_t lane, uint32_t which) {
+#ifndef SS_HOST_EMU
+    if (a.dbg_ts && tile_idx == 0 && lane == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.dbg_ts[which] = t;
+    }
+#endif
+}
 
 // Every warp of the grid takes a stripe.  Call after ss_pdl_wait().
 SS_DEV void ss_write_back(const SsArgs &a, uint32_t warp, uint32_t n_warps, uint32_t lane) {
@@ -399,6 +410,7 @@ SS_DEV void ss_load_mac(const uint8_t *p, uint32_t w[4]) {
 template <bool BULK>
 SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
+    ss_dbg_stamp(a, tile_idx, lane, 0);
     ss_pdl_launch_dependents();   // the next batch's kernel may start its own prologue now
     if (!(a.flags & SS_ARG_INPUT_INDEPENDENT)) ss_pdl_wait();   // descriptors may come from the previous kernel
     const SsTile tile = given ? *given : a.tiles[tile_idx];
@@ -482,7 +494,9 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
         if (valid && is_open && b_first == 1u) hw = *reinterpret_cast<const uint32_t *>(in_base + in_off);
         if (valid && is_open && b_first == 0u) ss_load_mac(src + mlen, wmac);
     }
+    ss_dbg_stamp(a, tile_idx, lane, 1);
     ss_pdl_wait();   // from here on we touch what the previous kernel may have written
+    ss_dbg_stamp(a, tile_idx, lane, 2);
     if (!BULK) ss_write_back(a, tile_idx, a.n_tiles, lane);
 
     // A frame the extractor refused (TypeError in the reference, or a shape it leaves to the host)
@@ -821,6 +835,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
                 if (lane + 32u * i < ow_pieces) g[lane + 32u * i] = stage[lane + 32u * i];
         }
     }
+    ss_dbg_stamp(a, tile_idx, lane, 3);
 }
 
 // ------------------------------------------------------ thread-per-frame tile --

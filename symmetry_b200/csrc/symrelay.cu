@@ -291,6 +291,8 @@ struct Shard {
     std::vector<uint8_t> h_sx_fast;
     cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;
     int pending_wb = -1;                           // stage whose results still sit in device staging
+    unsigned long long *d_ts = nullptr;            // SYMRELAY_TS=1: 4 time stamps per batch, 4096 batches round-robin
+    uint64_t ts_n = 0;
     cudaStream_t s_aux = nullptr;                  // bulk tiles run here, next to the packed tiles of the same batch
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::vector<Stage> stages;
@@ -454,6 +456,7 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     if (n_packed) {
         a.tiles = reinterpret_cast<const SsTile *>(d_tiles);
         a.n_tiles = n_packed;
+        if (fork && fork->d_ts) a.dbg_ts = fork->d_ts + 4u * (size_t)(fork->ts_n++ % 4096u);
         if (write_back) {   // this kernel also posts the previous batch's results to the host
             a.wb_src = reinterpret_cast<const uint4 *>(write_back->d_out);
             a.wb_dst = reinterpret_cast<uint4 *>(write_back->user_out);
@@ -554,6 +557,7 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
         CU(ctx, cudaEventCreateWithFlags(&st.ev_k, cudaEventDisableTiming));
         CU(ctx, cudaEventCreateWithFlags(&st.ev_out, cudaEventDisableTiming));
     }
+    if (getenv("SYMRELAY_TS")) { CU(ctx, cudaMalloc(&sh.d_ts, 4096u * 4u * 8u)); CU(ctx, cudaMemset(sh.d_ts, 0, 4096u * 4u * 8u)); }
     CU(ctx, cudaMalloc(&sh.d_sx_fast, SX_TABLES_BYTES));
     CU(ctx, cudaMemcpy(sh.d_sx_fast, sh.h_sx_fast.data(), SX_TABLES_BYTES, cudaMemcpyHostToDevice));
     return 0;
@@ -563,6 +567,25 @@ static void shard_free(Shard &sh) {
     if (sh.dev < 0) return;
     set_device(sh.dev);
     if (sh.s_k) cudaStreamSynchronize(sh.s_k);
+    if (sh.d_ts && sh.ts_n > 64) {   // diagnostics: how consecutive host batches overlap on the GPU
+        std::vector<unsigned long long> ts(4096u * 4u);
+        cudaMemcpy(ts.data(), sh.d_ts, ts.size() * 8u, cudaMemcpyDeviceToHost);
+        const uint64_t last = sh.ts_n - 1, first = last >= 2048 ? last - 2047 : 1;
+        double pre = 0, wait = 0, post = 0, period = 0, lead = 0;
+        uint64_t cnt = 0;
+        for (uint64_t k = first + 1; k <= last; k++) {
+            const unsigned long long *c = &ts[4u * (k % 4096u)], *p = &ts[4u * ((k - 1) % 4096u)];
+            if (!c[0] || !p[0] || c[3] < c[0]) continue;
+            pre += (double)(c[1] - c[0]); wait += (double)(c[2] - c[1]); post += (double)(c[3] - c[2]);
+            period += (double)(c[3] - p[3]); lead += (double)((long long)(p[3] - c[0]));
+            cnt++;
+        }
+        if (cnt)
+            fprintf(stderr, "symrelay kernel timeline over %llu batches (us, warp 0): reads before the wait %.2f, waiting %.2f, after the wait %.2f; "
+                    "end to end %.2f per batch; a kernel starts %.2f before its predecessor ends\n",
+                    (unsigned long long)cnt, pre / cnt * 1e-3, wait / cnt * 1e-3, post / cnt * 1e-3, period / cnt * 1e-3, lead / cnt * 1e-3);
+    }
+    cudaFree(sh.d_ts);
     if (sh.s_out) cudaStreamSynchronize(sh.s_out);
     for (Stage &st : sh.stages) {
         cudaFree(st.d_ctrl); cudaFreeHost(st.h_ctrl); cudaFree(st.d_in); cudaFree(st.d_out);
