@@ -578,7 +578,7 @@ def run_ours(args):
                 "h2d_bytes_per_step": lay.in_bytes + 2 * n * 16 + len(tiles_full) * 8,
                 "d2h_bytes_per_step": lay.out_bytes + 2 * n * 4, "steps": K2,
                 "ms_per_step": (e2e_sec / K2 * 1e3) if K2 else None,
-                "path": "symrelay_batch_submit/wait on pinned host arenas, pipeline depth 4, host clock; loop driver: " + e2e_driver},
+                "path": "symrelay_batch_submit/wait on pinned host arenas, pipeline depth " + str(D_E2E) + ", host clock; loop driver: " + e2e_driver},
         "gpu_launches": int(gpu_launches),
         "launches_per_step": launches_per_step,
         "clocks": clk,
