@@ -296,6 +296,66 @@ def test_pipelined_submit_keeps_chain_order(relay):
             assert bytes(wires[k][w_offs[i] : w_offs[i] + lens[i] + 20]) == want, (k, i)
 
 
+def test_deferred_write_back_in_mixed_pipelines(relay):
+    """A pipelined small batch leaves its results on the device until the next kernel on the stream (or the
+    wait) posts them to the host.  Here every hand-over is exercised: small after small (carried), small
+    before a batch with bulk tiles (carried by its packed kernel), before a bulk-only batch (flushed), before
+    a batch on pageable memory (flushed, staged DMA path), waits in and out of submission order, and a wait
+    with nothing behind it.  Every wire byte must be libsodium's, in chain order."""
+    rng = random.Random(44)
+    n = 96
+    keys = [rng.randbytes(32) for _ in range(n)]
+    hdrs = [rng.randbytes(24) for _ in range(n)]
+    karr = np.frombuffer(b"".join(keys), dtype=np.uint8).reshape(n, 32)
+    harr = np.frombuffer(b"".join(hdrs), dtype=np.uint8).reshape(n, 24)
+    slots = relay.open_streams(karr, harr, None, None)
+    refs = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+    kinds = {
+        "small": lambda: [rng.choice([0, 1, 63, 64, 65, 200, 700]) for _ in range(n)],
+        "mixed": lambda: [rng.choice([64, 200, 2500, 5000]) for _ in range(n)],
+        "bulk": lambda: [rng.choice([2000, 3000, 4096]) for _ in range(n)],
+    }
+    plan = [("small", True, "later"), ("small", True, "later"), ("mixed", True, "later"), ("small", True, "now"),
+            ("small", True, "later"), ("bulk", True, "later"), ("small", True, "later"), ("small", False, "later"),
+            ("small", True, "later"), ("small", True, "later"), ("small", True, "reverse"), ("small", True, "now")]
+    inflight = []   # (ticket, lens, plain, wire, stat, w_offs, p_offs)
+
+    def check(item):
+        _, lens, plain, wire, stat, w_offs, p_offs = item
+        assert (stat == 0).all()
+        for i in range(n):
+            want = refs[i].seal_frame(bytes(plain[p_offs[i] : p_offs[i] + lens[i]]))
+            assert bytes(wire[w_offs[i] : w_offs[i] + lens[i] + 20]) == want
+
+    done = []
+    for kind, pinned, when in plan:
+        lens = kinds[kind]()
+        p_offs, p_bytes = bu.plain_layout(lens)
+        w_offs, w_bytes = bu.wire_layout(lens)
+        if pinned:
+            plain, wire = relay.alloc_pinned(p_bytes), relay.alloc_pinned(w_bytes)
+        else:
+            plain, wire = bu.aligned_zeros(p_bytes), bu.aligned_zeros(w_bytes)
+        plain[:] = np.frombuffer(rng.randbytes(p_bytes), dtype=np.uint8)
+        wire[:] = 0xEE
+        stat = np.full(n, 0xFF, dtype=np.uint32)
+        t = relay.submit(bu.make_descs(slots, lens, p_offs, w_offs), plain, p_bytes, wire, w_bytes, stat)
+        inflight.append((t, lens, plain, wire, stat, w_offs, p_offs))
+        if when == "now":          # everything submitted so far, oldest first
+            for item in inflight:
+                relay.wait(item[0])
+            done += inflight
+            inflight = []
+        elif when == "reverse":    # newest first: the older tickets are then already complete
+            for item in reversed(inflight):
+                relay.wait(item[0])
+            done += inflight
+            inflight = []
+    assert not inflight
+    for item in done:              # reference chains advance in submission order
+        check(item)
+
+
 def test_zero_copy_and_staged_paths_agree():
     """The same pinned-arena batches through both host paths give identical wire bytes and states."""
     import symmetry_b200 as sb
