@@ -282,6 +282,10 @@ struct Stage {
     int wb_by = -1;               // stage whose ev_out covers the write-back; -1: not issued yet
     uint8_t *user_out = nullptr;
     uint64_t out_bytes = 0;
+    // Bucketed planning (large staged batches): the kernels saw the descriptors sorted by block count;
+    // perm[k] = the caller's index of sorted descriptor k, applied to statuses and deltas on completion.
+    std::vector<uint32_t> perm;
+    bool permuted = false;
 };
 
 struct Shard {
@@ -321,6 +325,7 @@ struct symrelay_ctx {
     uint64_t zero_copy_batches = 0, staged_batches = 0;
     bool pdl = true;   // SYMRELAY_PDL=0 turns programmatic dependent launch off
     bool inline_tiles = true;   // SYMRELAY_INLINE_TILES=0: small host batches read their tile list from memory like all others
+    bool bucket = true;     // SYMRELAY_BUCKET=0: large staged batches are planned in the caller's descriptor order
     bool defer_wb = true;   // SYMRELAY_DEFER=0: pipelined zero-copy batches write their results to the host themselves
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
     uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
@@ -627,6 +632,7 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (ctx->opts.flags & SYMRELAY_OPT_NO_ZERO_COPY) ctx->zero_copy_max = 0;
     { const char *e = getenv("SYMRELAY_PROF"); ctx->prof = e && e[0] == '1'; }
     { const char *e = getenv("SYMRELAY_DEFER"); if (e && e[0] == '0') ctx->defer_wb = false; }
+    { const char *e = getenv("SYMRELAY_BUCKET"); if (e && e[0] == '0') ctx->bucket = false; }
     { const char *e = getenv("SYMRELAY_INLINE_TILES"); if (e && e[0] == '0') ctx->inline_tiles = false; }
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
@@ -910,8 +916,15 @@ static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st) {
         st.deferred = false;
     } else
     CU(ctx, cudaEventSynchronize(st.ev_out));
-    if (st.user_status) memcpy(st.user_status, st.h_status, (size_t)st.n * 4u);
-    if (st.user_delta) memcpy(st.user_delta, st.h_delta, (size_t)st.n * sizeof(symrelay_delta));
+    if (st.permuted) {
+        const uint32_t *perm = st.perm.data();
+        if (st.user_status) for (uint32_t k = 0; k < st.n; k++) st.user_status[perm[k]] = st.h_status[k];
+        if (st.user_delta) for (uint32_t k = 0; k < st.n; k++) st.user_delta[perm[k]] = st.h_delta[k];
+        st.permuted = false;
+    } else {
+        if (st.user_status) memcpy(st.user_status, st.h_status, (size_t)st.n * 4u);
+        if (st.user_delta) memcpy(st.user_delta, st.h_delta, (size_t)st.n * sizeof(symrelay_delta));
+    }
     st.busy = false;
     return 0;
 }
@@ -939,7 +952,18 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     uint32_t n_bulk = 0;
     symrelay_plan_check chk;
     chk.in_bytes = in_bytes; chk.out_bytes = out_bytes; chk.max_streams = ctx->opts.max_streams;
-    const int64_t n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk, &chk);
+    // Large batches bound for the DMA pipeline are planned bucketed (plan.h): descriptors sorted by block count
+    // on their way into the control block.  The tile area is then sized for the worst case (one tile per frame).
+    int64_t n_tiles = -2;
+    bool bucketed = false;
+    const size_t bucket_tiles_bytes = align_up((size_t)n * sizeof(symrelay_tile), 16);
+    if (ctx->bucket && n >= 4096u && in_bytes + out_bytes > ctx->zero_copy_max) {
+        if (st.perm.size() < n) st.perm.resize(n);
+        n_tiles = symrelay_plan_bucketed(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk, &chk,
+                                         reinterpret_cast<symrelay_desc *>(st.h_ctrl + bucket_tiles_bytes), st.perm.data());
+        bucketed = n_tiles >= 0;
+    }
+    if (n_tiles == -2) n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk, &chk);
     if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
     PROF_MARK(ctx, 1);
     // bounds / ownership checks (computed by the planner's first pass over the descriptors)
@@ -972,9 +996,10 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         return fail(ctx, SYMRELAY_EINVAL, "SYMRELAY_F_EXTRACT needs delta and delta_arena");
     if (extract && !st.d_delta_arena) CU(ctx, cudaMalloc(&st.d_delta_arena, ctx->opts.stage_bytes));
     if (runs && !st.d_run_nonce) CU(ctx, cudaMalloc(&st.d_run_nonce, (size_t)ctx->opts.max_batch_frames * sizeof(uint4)));
-    const size_t tiles_bytes = align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
+    const size_t tiles_bytes = bucketed ? bucket_tiles_bytes : align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
     PROF_MARK(ctx, 2);
-    memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
+    if (!bucketed) memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
+    st.permuted = bucketed;
     const size_t ctrl_bytes = tiles_bytes + (size_t)n * sizeof(symrelay_desc);
     PROF_MARK(ctx, 3);
 

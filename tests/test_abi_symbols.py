@@ -83,3 +83,15 @@ def test_avx2_descriptor_scan_matches_the_scalar_loop(tmp_path):
     if res.returncode == 77:
         pytest.skip("this CPU has no AVX2")
     assert res.returncode == 0, res.stdout + res.stderr
+
+
+def test_bucketed_planner_covers_every_descriptor_once(tmp_path):
+    """Large host batches are planned bucketed (descriptors sorted by block count, closed-form tiles, a
+    permutation for the statuses): tests/emu/bucket_check.cpp validates the plan of 131,072 power-law frames."""
+    import subprocess
+
+    exe = str(tmp_path / "bucket_check")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emu", "bucket_check.cpp"),
+                    os.path.join(ROOT, "symmetry_b200", "csrc", "plan_scan_avx2.cpp")], check=True)
+    res = subprocess.run([exe], capture_output=True, text=True)
+    assert res.returncode == 0 and "valid=1" in res.stdout, res.stdout + res.stderr

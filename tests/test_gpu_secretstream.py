@@ -356,6 +356,37 @@ def test_deferred_write_back_in_mixed_pipelines(relay):
         check(item)
 
 
+def test_bucketed_host_batches_hand_statuses_back_in_caller_order(relay):
+    """Large staged batches are sorted by size inside the library; statuses (and the bytes) must still belong
+    to the caller's descriptor i: frames in arrival order, forged frames at known indices on the open side."""
+    rng = random.Random(77)
+    n = 12000
+    keys = np.frombuffer(rng.randbytes(32 * n), dtype=np.uint8).reshape(n, 32)
+    hdrs = np.frombuffer(rng.randbytes(24 * n), dtype=np.uint8).reshape(n, 24)
+    slots = relay.open_streams(keys, hdrs, keys, hdrs)
+    lens = [rng.choice([0, 5, 64, 64, 64, 130, 200, 700, 1900, 2500, 9000]) for _ in range(n)]
+    p_offs, p_bytes = bu.plain_layout(lens)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    assert p_bytes + w_bytes > (1 << 20)
+    plain, wire, back = relay.alloc_pinned(p_bytes), relay.alloc_pinned(w_bytes), relay.alloc_pinned(p_bytes)
+    plain[:] = np.frombuffer(rng.randbytes(p_bytes), dtype=np.uint8)
+    st = relay.batch_host(bu.make_descs(slots, lens, p_offs, w_offs), plain, wire)
+    assert (st == 0).all()
+    for i in range(0, n, 211):
+        ref = ls.State(bytes(keys[i]), bytes(hdrs[i]))
+        want = ref.seal_frame(bytes(plain[p_offs[i] : p_offs[i] + lens[i]]))
+        assert bytes(wire[w_offs[i] : w_offs[i] + lens[i] + 20]) == want, i
+    forged = sorted(rng.sample(range(n), 40))
+    for i in forged:
+        wire[w_offs[i] + 3 + (lens[i] + 17) // 2] ^= 0x20     # somewhere in tag | ciphertext | mac
+    st = relay.batch_host(bu.make_descs(slots, lens, w_offs, p_offs, open_=True), wire, back)
+    bad = [i for i in range(n) if (int(st[i]) & 0xFF) != 0]
+    assert bad == forged
+    for i in range(0, n, 97):
+        if i not in forged:
+            assert (back[p_offs[i] : p_offs[i] + lens[i]] == plain[p_offs[i] : p_offs[i] + lens[i]]).all(), i
+
+
 def test_zero_copy_and_staged_paths_agree():
     """The same pinned-arena batches through both host paths give identical wire bytes and states."""
     import symmetry_b200 as sb
