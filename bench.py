@@ -298,8 +298,15 @@ def run_ours(args):
     flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
     d_full = lay.descs(slots, True)
     d_seal = lay.descs(slots, False)
-    tiles_full, nb_full = relay.plan(d_full)
-    tiles_seal, nb_seal = relay.plan(d_seal)
+    # Ragged batches are planned with the library's sorting planner (descriptors grouped by size class, statuses
+    # come back through a permutation); BENCH_PLAN=caller keeps the frames in arrival order.
+    plan_mode = os.environ.get("BENCH_PLAN", "sorted" if args.workload == "c3" else "caller")
+    if plan_mode == "sorted":
+        tiles_full, nb_full, d_full, _perm_full = relay.plan_sorted(d_full)
+        tiles_seal, nb_seal, d_seal, _perm_seal = relay.plan_sorted(d_seal)
+    else:
+        tiles_full, nb_full = relay.plan(d_full)
+        tiles_seal, nb_seal = relay.plan(d_seal)
     t_dfull = torch.from_numpy(d_full.view(np.uint8).copy()).to(dev)
     t_dseal = torch.from_numpy(d_seal.view(np.uint8).copy()).to(dev)
     t_tfull = torch.from_numpy(tiles_full.view(np.uint8).copy()).to(dev)
@@ -554,7 +561,7 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": n_gpus, "steps": K, "warmup": W,
         "ms_per_step": per_launch_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
         "dtype": "u32", "data": "synthetic",
-        "config": {"workload": desc, "streams_per_gpu": n, "frames_per_step_per_gpu": 2 * n,
+        "config": {"workload": desc, "streams_per_gpu": n, "plan": ("symrelay_plan_sorted (library groups the frames by size class)" if plan_mode == "sorted" else "symrelay_plan (caller's descriptor order)"), "frames_per_step_per_gpu": 2 * n,
                    "plaintext_bytes_per_step_per_gpu": int(sum(lens)),
                    "l2": f"inputs larger than L2: ring of {R} distinct batch slots, {R * lay.slot_bytes >> 20} MiB, "
                          f"visited round-robin; L2 flushed once before timing",

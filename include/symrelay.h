@@ -192,6 +192,16 @@ SYMRELAY_API int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_
  * (call with tiles == NULL to size), or SYMRELAY_EINVAL for a bad descriptor. */
 SYMRELAY_API int64_t symrelay_plan(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles, uint32_t max_tiles,
                       uint32_t *n_bulk_out);
+/* The same for callers of the device entry points whose frames arrive in any order: writes the
+ * descriptors SORTED by ChaCha20 block count to sorted_out[n] (a batch holds at most one frame per
+ * (slot, direction), so any order is legal), tiles each size class in closed form and returns the
+ * permutation: sorted_out[k] == desc[perm_out[k]], and the status word of sorted descriptor k belongs
+ * to the caller's frame perm_out[k].  Upload sorted_out, not desc.  Packs BASELINE config 3 into
+ * 9,054 tiles instead of 19,441.  Returns the tile count (tiles == NULL sizes and writes nothing),
+ * SYMRELAY_EINVAL for a bad descriptor or a batch with SYMRELAY_F_RUN frames (their order is the
+ * chain: use symrelay_plan).  No counterpart in the reference (one frame per call there). */
+SYMRELAY_API int64_t symrelay_plan_sorted(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles, uint32_t max_tiles,
+                             uint32_t *n_bulk_out, symrelay_desc *sorted_out, uint32_t *perm_out);
 /* Validates one descriptor's alignment and length rules; 0 or SYMRELAY_EINVAL. */
 SYMRELAY_API int symrelay_desc_check(const symrelay_desc *d);
 

@@ -16,7 +16,7 @@ SO_PATH = os.environ.get("SYMRELAY_SO") or os.path.join(HERE, "libsymrelay.so")
 EXPORTS = (
     "symrelay_abi_version", "symrelay_create", "symrelay_destroy", "symrelay_last_error", "symrelay_strerror",
     "symrelay_launch_count", "symrelay_stream_open", "symrelay_stream_open_batch", "symrelay_stream_close",
-    "symrelay_stream_export", "symrelay_plan", "symrelay_desc_check", "symrelay_batch_device",
+    "symrelay_stream_export", "symrelay_plan", "symrelay_plan_sorted", "symrelay_desc_check", "symrelay_batch_device",
     "symrelay_batch_host", "symrelay_batch_submit", "symrelay_batch_wait", "symrelay_alloc_pinned",
     "symrelay_free_pinned", "symrelay_probe_int_peak", "symrelay_submit_seal", "symrelay_submit_open",
     "symrelay_flush", "symrelay_poll", "symrelay_poll_wait", "symrelay_release", "symrelay_sched_stats",
@@ -78,6 +78,8 @@ def load() -> C.CDLL:
     L.symrelay_stream_export.argtypes = [vp, u32, vp, vp]
     L.symrelay_plan.restype = i64
     L.symrelay_plan.argtypes = [vp, u32, vp, u32, C.POINTER(u32)]
+    L.symrelay_plan_sorted.restype = i64
+    L.symrelay_plan_sorted.argtypes = [vp, u32, vp, u32, C.POINTER(u32), vp, vp]
     L.symrelay_desc_check.restype = ci
     L.symrelay_desc_check.argtypes = [vp]
     L.symrelay_batch_device.restype = ci

@@ -795,6 +795,14 @@ int64_t symrelay_plan(const symrelay_desc *desc, uint32_t n, symrelay_tile *tile
     return symrelay_plan_inline(desc, n, tiles, max_tiles, n_bulk_out);
 }
 
+int64_t symrelay_plan_sorted(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles, uint32_t max_tiles,
+                             uint32_t *n_bulk_out, symrelay_desc *sorted_out, uint32_t *perm_out) {
+    if (!desc && n) return SYMRELAY_EINVAL;
+    if (tiles && (!sorted_out || !perm_out)) return SYMRELAY_EINVAL;
+    const int64_t r = symrelay_plan_bucketed(desc, n, tiles, max_tiles, n_bulk_out, nullptr, sorted_out, perm_out);
+    return r == -2 ? (int64_t)SYMRELAY_EINVAL : r;
+}
+
 int symrelay_desc_check(const symrelay_desc *d) { return d ? symrelay_desc_check_inline(d) : SYMRELAY_EINVAL; }
 
 // ---- batches --------------------------------------------------------------------

@@ -144,6 +144,18 @@ class SymRelay:
         self._check(self.lib.symrelay_plan(_ptr(descs), len(descs), _ptr(tiles), need, C.byref(nb)))
         return tiles[:need], nb.value
 
+    def plan_sorted(self, descs: np.ndarray):
+        """(tiles, n_bulk, sorted descriptors, perm): descriptors grouped by size for the device entry points;
+        the status of sorted descriptor k belongs to descs[perm[k]]."""
+        nb = C.c_uint32(0)
+        need = self._check(self.lib.symrelay_plan_sorted(_ptr(descs), len(descs), None, 0, C.byref(nb), None, None))
+        tiles = np.zeros(max(1, need), dtype=TILE_DTYPE)
+        sorted_descs = np.zeros(len(descs), dtype=descs.dtype)
+        perm = np.zeros(len(descs), dtype=np.uint32)
+        self._check(self.lib.symrelay_plan_sorted(_ptr(descs), len(descs), _ptr(tiles), need, C.byref(nb),
+                                                  _ptr(sorted_descs), _ptr(perm)))
+        return tiles[:need], nb.value, sorted_descs, perm
+
     def batch_host(self, descs: np.ndarray, arena_in: np.ndarray, arena_out: np.ndarray,
                    status: np.ndarray | None = None, delta: np.ndarray | None = None,
                    delta_arena: np.ndarray | None = None) -> np.ndarray:

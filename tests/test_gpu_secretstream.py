@@ -266,6 +266,56 @@ def test_device_resident_batch_on_torch_stream(relay):
         assert (back[o : o + L] == plain[o : o + L]).all()
 
 
+def test_sorting_planner_on_the_device_path(relay):
+    """symrelay_plan_sorted: descriptors grouped by size class for the device entry points; wire bytes are
+    libsodium's and the status of sorted descriptor k belongs to the caller's frame perm[k] (forged frames)."""
+    import torch
+
+    rng = random.Random(19)
+    lens = pc.power_law_lens(rng, 9000) + [64] * 300 + [40000, 70000]
+    rng.shuffle(lens)
+    n = len(lens)
+    karr = np.frombuffer(rng.randbytes(32 * n), dtype=np.uint8).reshape(n, 32)
+    harr = np.frombuffer(rng.randbytes(24 * n), dtype=np.uint8).reshape(n, 24)
+    slots = relay.open_streams(karr, harr, karr, harr)
+    p_offs, p_bytes = bu.plain_layout(lens)
+    w_offs, w_bytes = bu.wire_layout(lens)
+    plain = np.frombuffer(rng.randbytes(p_bytes), dtype=np.uint8).copy()
+    dev = torch.device("cuda:0")
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def run(descs, t_in, out_bytes):
+        tiles, n_bulk, sorted_descs, perm = relay.plan_sorted(descs)
+        assert sorted(perm.tolist()) == list(range(n)) and (sorted_descs == descs[perm]).all()
+        assert len(tiles) < len(relay.plan(descs)[0])            # it packs better than the caller's order
+        t_desc = torch.from_numpy(sorted_descs.view(np.uint8).copy()).to(dev)
+        t_tiles = torch.from_numpy(tiles.view(np.uint8).copy()).to(dev)
+        t_out = torch.zeros(out_bytes, dtype=torch.uint8, device=dev)
+        t_status = torch.full((n,), 0xFF, dtype=torch.int32, device=dev)
+        relay.batch_device(t_desc.data_ptr(), n, t_tiles.data_ptr(), len(tiles), n_bulk, t_in.data_ptr(), t_out.data_ptr(),
+                           t_status.data_ptr(), stream=stream)
+        torch.cuda.synchronize()
+        status = np.empty(n, dtype=np.int64)
+        status[perm] = t_status.cpu().numpy() & 0xFF          # back to the caller's order
+        return t_out, status
+
+    t_wire, st = run(bu.make_descs(slots, lens, p_offs, w_offs), torch.from_numpy(plain).to(dev), w_bytes)
+    assert (st == 0).all()
+    wire = t_wire.cpu().numpy()
+    for i in list(range(0, n, 131)) + [lens.index(70000), lens.index(40000)]:
+        want = ls.State(bytes(karr[i]), bytes(harr[i])).seal_frame(bytes(plain[p_offs[i] : p_offs[i] + lens[i]]))
+        assert bytes(wire[w_offs[i] : w_offs[i] + lens[i] + 20]) == want, i
+    forged = sorted(rng.sample(range(n), 25))
+    for i in forged:
+        wire[w_offs[i] + 3] ^= 1
+    t_back, st = run(bu.make_descs(slots, lens, w_offs, p_offs, open_=True), torch.from_numpy(wire).to(dev), p_bytes)
+    assert [i for i in range(n) if st[i] != 0] == forged
+    back = t_back.cpu().numpy()
+    for i in range(0, n, 53):
+        if i not in forged:
+            assert (back[p_offs[i] : p_offs[i] + lens[i]] == plain[p_offs[i] : p_offs[i] + lens[i]]).all()
+
+
 def test_pipelined_submit_keeps_chain_order(relay):
     """Consecutive batches carry consecutive frames of the same streams (MAC chain)."""
     rng = random.Random(10)
