@@ -314,6 +314,8 @@ def test_sorting_planner_on_the_device_path(relay):
     for i in range(0, n, 53):
         if i not in forged:
             assert (back[p_offs[i] : p_offs[i] + lens[i]] == plain[p_offs[i] : p_offs[i] + lens[i]]).all()
+    for s_ in slots:
+        relay.close_stream(int(s_))
 
 
 def test_pipelined_submit_keeps_chain_order(relay):
@@ -435,6 +437,8 @@ def test_bucketed_host_batches_hand_statuses_back_in_caller_order(relay):
     for i in range(0, n, 97):
         if i not in forged:
             assert (back[p_offs[i] : p_offs[i] + lens[i]] == plain[p_offs[i] : p_offs[i] + lens[i]]).all(), i
+    for s_ in slots:
+        relay.close_stream(int(s_))
 
 
 def test_zero_copy_and_staged_paths_agree():
@@ -484,7 +488,7 @@ def test_bad_arguments_are_rejected(relay):
     with pytest.raises(sb.RelayError):
         relay.batch_host(d, bu.aligned_zeros(128), bu.aligned_zeros(128))  # misaligned plaintext
     with pytest.raises(sb.RelayError):
-        relay.export(99999)  # not open
+        relay.export((1 << 17) - 1)  # not open (the last slot of this relay; the tests above never get that far)
     k, h = bytes(32), bytes(24)
     slot = relay.open_stream(k, h, k, h)
     relay.close_stream(slot)
