@@ -58,6 +58,8 @@ extern "C" {
 #define SYMRELAY_ST_EXTRACT_THROW 3u      /* the reference would throw a TypeError here (utils.ts:38-50) */
 #define SYMRELAY_ST_EXTRACT_UNSUPPORTED 4u /* value shape outside the GPU extractor's domain: use the JS helper */
 #define SYMRELAY_ST_RETRY 5u /* frame of a run behind a failed or REKEY frame: not processed, resubmit it */
+#define SYMRELAY_ST_FAILED 6u /* per-frame front end only: the batch this frame sat in was refused as a whole
+                                (symrelay_last_error() says why); nothing was sealed or opened, state untouched */
 #define SYMRELAY_ST_PENDING 0xffu
 #define SYMRELAY_STATUS_CODE(s) ((s) & 0xffu)
 #define SYMRELAY_STATUS_TAG(s) (((s) >> 8) & 0xffu)
@@ -90,7 +92,11 @@ enum symrelay_provider {
  *         plaintext  -> out + out_off (out_off % 16 == 0)
  * A batch holds at most ONE frame per (slot, direction): frames of one stream
  * are MAC-chained and go into consecutive batches
- * -- except inbound runs marked SYMRELAY_F_RUN, whose chain is on the wire.
+ * -- except inbound runs marked SYMRELAY_F_RUN, whose chain is on the wire
+ * (at most 64 frames per run).  The host-buffer entry points check both rules
+ * and refuse the batch (SYMRELAY_EINVAL); the device entry points cannot read
+ * the descriptors, there a frame beyond 64 in its run, or a SYMRELAY_F_RUN frame
+ * given to symrelay_batch_device (no scratch), completes with SYMRELAY_ST_RETRY.
  * Arenas must be readable up to the next 16-byte boundary past each frame.
  */
 typedef struct symrelay_desc {
@@ -177,9 +183,11 @@ SYMRELAY_API int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, 
 SYMRELAY_API int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_keys, const uint8_t *tx_inits,
                                const uint8_t *rx_keys, const uint8_t *rx_inits, int init_len, int provider_kind,
                                uint32_t *slots_out);
-/* Wipes the slot's keys on the device and frees the slot.  Close only after every frame submitted for the
- * slot has completed: a frame still in flight would be sealed with the wiped state.  Host batches that name a
- * closed slot are refused (SYMRELAY_ENOENT). */
+/* Wipes the slot's keys on the device, forgets its half-received inbound frame (symrelay_rx_feed) and frees
+ * the slot.  Close only after every frame submitted for the slot has completed: a frame still in flight would
+ * be sealed with the wiped state.  The per-frame front end enforces that: while one of the slot's frames sits
+ * in a batch that is filling or in flight the call returns SYMRELAY_EAGAIN (flush, poll, close again).  Host
+ * batches that name a closed slot are refused (SYMRELAY_ENOENT). */
 SYMRELAY_API int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot);
 /* Copies the live libsodium-compatible 52-byte states back (either may be NULL). */
 SYMRELAY_API int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_t tx_state[SYMRELAY_STATEBYTES],
@@ -234,11 +242,11 @@ SYMRELAY_API int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, co
  * SYMRELAY_STATIC_RUN_MAX (65,536) descriptors per call -- larger batches are refused with
  * SYMRELAY_EINVAL and a message naming the limit.  The call itself performs no cudaMalloc, cudaFree
  * or other allocating call; all inputs and outputs are still the caller's device buffers.
- * The first call on each GPU looks up the array's device address (one-time set-up): make that first
- * call before starting any stream capture.  All calls on a GPU share the one array and it keeps the
- * previous call's contents: nothing in it needs clearing (each call's pre-pass rewrites every entry
- * its kernels read), but two calls whose kernels overlap on the GPU (different streams) race on it --
- * issue them on one stream or otherwise order them. */
+ * The array's device address is looked up once per GPU inside symrelay_create (with that GPU
+ * current), so no call of this function does set-up work.  All calls on a GPU share the one array
+ * and it keeps the previous call's contents: nothing in it needs clearing (each call's pre-pass
+ * rewrites every entry its kernels read), but two calls whose kernels overlap on the GPU (different
+ * streams) race on it -- issue them on one stream or otherwise order them. */
 #define SYMRELAY_STATIC_RUN_MAX 65536u
 SYMRELAY_API int symrelay_batch_device_runs_static(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc,
                                                    uint32_t n, const symrelay_tile *d_tiles, uint32_t n_tiles,

@@ -15,7 +15,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsymrelay.so")
 SOURCES = ["symrelay.cu", "plan_scan_avx2.cpp"]
-HEADERS = ["ss_core.cuh", "plan.h", "plan_scan_avx2.cpp", os.path.join("..", "..", "include", "symrelay.h")]
+# everything symrelay.cu includes: stale() rebuilds when any of them is newer than the .so
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".inc"))) + [
+    os.path.join("..", "..", "include", "symrelay.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -81,6 +81,7 @@ SS_DEV void ss_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #define SS_ST_OK 0u
 #define SS_ST_BAD_MAC 1u
 #define SS_ST_RETRY 5u
+#define SS_RUN_CAP 64u   // frames of one stream per batch that can be opened as a run (== SS_RUN_MAX in ss_runs.cuh)
 
 struct SsDesc {
     uint32_t slot, in_off, out_off, len_flags;
@@ -502,6 +503,14 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     // A frame the extractor refused (TypeError in the reference, or a shape it leaves to the host)
     // is not sealed: provider.ts:243-248 throws before peer.write(chunk).
     if (lane < nfr && (d_lf & SS_F_EXTRACT) && !(d_lf & SS_F_OPEN)) d_skip = a.status[tile.first + lane] != SS_ST_OK;
+    // A run frame without a speculative nonce -- the entry point got no scratch, or the frame sits beyond
+    // SS_RUN_MAX in its run (the pre-pass flags those) -- is not opened: RETRY, state untouched.
+    if (lane < nfr && (d_lf & (SS_F_RUN | SS_F_OPEN)) == (SS_F_RUN | SS_F_OPEN)) {
+        if (!a.run_nonce || a.run_nonce[tile.first + lane].w >= SS_RUN_CAP) {
+            d_skip = 1;
+            a.status[tile.first + lane] = SS_ST_RETRY;
+        }
+    }
     if (ss_shfl(d_skip, f)) valid = false;
 
     uint32_t k[8], nn[3], meta = 0;
@@ -872,6 +881,11 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
     ss_write_back(a, tile_idx, a.n_tiles, lane);
     const uint32_t lf = d.len_flags;
     if (valid && (lf & SS_F_EXTRACT) && !(lf & SS_F_OPEN) && a.status[tile.first + lane] != SS_ST_OK) valid = false;
+    if (valid && (lf & (SS_F_RUN | SS_F_OPEN)) == (SS_F_RUN | SS_F_OPEN) &&
+        (!a.run_nonce || a.run_nonce[tile.first + lane].w >= SS_RUN_CAP)) {   // see ss_process_tile
+        a.status[tile.first + lane] = SS_ST_RETRY;
+        valid = false;
+    }
     if (!valid) return;
     const uint32_t mlen = lf & 0xffffffu;
     const bool is_open = (lf & SS_F_OPEN) != 0;

@@ -18,7 +18,7 @@
 #pragma once
 #include "ss_core.cuh"
 
-#define SS_RUN_MAX 64u   // frames of one stream per batch
+#define SS_RUN_MAX SS_RUN_CAP   // frames of one stream per batch (64)
 
 SS_DEV void ss_wire_mac8(const uint8_t *in, const SsDesc &d, uint32_t &m0, uint32_t &m1) {
     const uint8_t *p = in + d.in_off + 4u + (d.len_flags & 0xffffffu);
@@ -48,6 +48,8 @@ SS_DEV void ss_run_nonce(const SsDesc *desc, uint32_t n, const uint8_t *in, cons
         n1 ^= m0; n2 ^= m1;
         p++;
     }
+    // p == SS_RUN_MAX: at least that many frames precede this one, its nonce would be truncated.  The tile
+    // kernels read .w, leave such a frame alone and report RETRY (resubmit it in the next batch).
     uint4 o;
     o.x = s2.x + p; o.y = n1; o.z = n2; o.w = p;
     run_nonce[i] = o;
@@ -66,10 +68,10 @@ SS_DEV void ss_run_commit(const SsDesc *desc, uint32_t n, const uint8_t *in, uin
     uint32_t k[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
     uint32_t nn[3] = {s2.x, s2.y, s2.z};
     bool live = true, rekeyed = false;
-    for (uint32_t j = i, p = 0; j < n && p < SS_RUN_MAX; j++, p++) {
+    for (uint32_t j = i, p = 0; j < n; j++, p++) {
         const SsDesc e = desc[j];
         if (j != i && !ss_same_run(desc[j - 1], e)) break;
-        if (!live) { status[j] = SS_ST_RETRY; continue; }
+        if (!live || p >= SS_RUN_MAX) { status[j] = SS_ST_RETRY; live = false; continue; }
         const uint32_t st = status[j];
         if ((st & 0xffu) != SS_ST_OK) { live = false; continue; }   // keeps its BAD_MAC; the stream is dead there
         uint32_t m0, m1;

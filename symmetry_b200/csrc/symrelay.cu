@@ -257,6 +257,21 @@ __global__ void __launch_bounds__(256) ss_probe_imad_kernel(uint32_t *out, int i
     if (acc == 0x12345ull) out[0] = (uint32_t)acc;
 }
 
+// ---- run batches without any allocation -------------------------------------------------------
+// Who needs this: a provider usually shares its GPU with the model server it relays for (Ollama,
+// llama.cpp ...), which has claimed nearly all of HBM before the relay receives its first bulk
+// segment; an allocation for run scratch made at that moment can simply fail.  And the caller is
+// Node's event-loop thread: cudaMalloc/cudaFree synchronise the whole device, which would stall
+// every connection's batch in flight.  For those callers the nonce scratch of a run batch lives in
+// this fixed array instead of caller- or library-allocated memory.  Cost: 1 MiB of HBM on every
+// GPU that loads the library, held until the process exits, and a hard cap on the batch size
+// (SYMRELAY_STATIC_RUN_MAX descriptors, the one definition in include/symrelay.h).
+// In host code `g_run_nonce_static` is only a handle for the runtime, not an address a kernel can
+// use: shard_init() looks the device address up once per GPU, right after making that GPU current,
+// and keeps it in Shard::d_run_static.
+static __device__ __align__(256) uint4 g_run_nonce_static[SYMRELAY_STATIC_RUN_MAX];
+static_assert(sizeof(uint4) * SYMRELAY_STATIC_RUN_MAX == (1u << 20), "the header promises 1 MiB per GPU");
+
 // --------------------------------------------------------------- host side --
 namespace {
 
@@ -292,6 +307,9 @@ struct Shard {
     int dev = -1;
     uint4 *d_states = nullptr;
     uint4 *d_sx_fast = nullptr;            // extractor tables (SX_TABLES_BYTES), allocated last in shard_init
+    uint4 *d_run_static = nullptr;         // device address of g_run_nonce_static on this GPU (symrelay_batch_device_runs_static)
+    std::vector<uint32_t> slot_stamp;      // [slot*2+dir] -> stamp of the last host batch that named it (duplicate check)
+    uint32_t stamp = 0;
     std::vector<uint8_t> h_sx_fast;
     cudaStream_t s_in = nullptr, s_k = nullptr, s_out = nullptr;
     int pending_wb = -1;                           // stage whose results still sit in device staging
@@ -328,6 +346,7 @@ struct symrelay_ctx {
     bool bucket = true;     // SYMRELAY_BUCKET=0: large staged batches are planned in the caller's descriptor order
     bool defer_wb = true;   // SYMRELAY_DEFER=0: pipelined zero-copy batches write their results to the host themselves
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
+    uint64_t inject_refusal = 0;   // SYMRELAY_INJECT_REFUSAL=k: the front end's k-th batch is refused (tests of the error path)
     uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
     // SYMRELAY_PROF=1: where a host batch spends its time (printed by symrelay_destroy)
     bool prof = false;
@@ -379,13 +398,13 @@ static int fail(symrelay_ctx *ctx, int code, const char *fmt, ...) {
 
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
-// cudaSetDevice on every call showed up in the per-batch host cost; remember it per thread.
-static thread_local int t_cur_dev = -1;
+// cudaSetDevice on every call showed up in the per-batch host cost, so it is skipped when the runtime
+// says the device is current already.  The question goes to the runtime every time (cudaGetDevice is a
+// thread-local read): other CUDA users on the thread -- torch, another addon -- switch devices behind us.
 static inline cudaError_t set_device(int dev) {
-    if (t_cur_dev == dev) return cudaSuccess;
-    const cudaError_t e = cudaSetDevice(dev);
-    if (e == cudaSuccess) t_cur_dev = dev;
-    return e;
+    int cur = -1;
+    if (cudaGetDevice(&cur) == cudaSuccess && cur == dev) return cudaSuccess;
+    return cudaSetDevice(dev);
 }
 
 // Launch with the programmatic-dependent-launch attribute so that consecutive batches overlap:
@@ -522,7 +541,15 @@ uint64_t symrelay_launch_count(symrelay_ctx *ctx) { return ctx ? ctx->launches.l
 
 static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     sh.dev = dev;
-    CU(ctx, set_device(dev));
+    CU(ctx, cudaSetDevice(dev));
+    {   // with `dev` current: the address of the fixed run scratch on this GPU (no allocation involved)
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_run_nonce_static);
+        if (e != cudaSuccess || !p)
+            return fail(ctx, SYMRELAY_ECUDA, "cudaGetSymbolAddress(run scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+        sh.d_run_static = reinterpret_cast<uint4 *>(p);
+    }
+    sh.slot_stamp.assign((size_t)ctx->opts.max_streams * 2u, 0u);
     const size_t table_bytes = (size_t)ctx->opts.max_streams * 2u * 48u;
     CU(ctx, cudaMalloc(&sh.d_states, table_bytes));
     CU(ctx, cudaMemset(sh.d_states, 0, table_bytes));
@@ -634,6 +661,7 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     { const char *e = getenv("SYMRELAY_DEFER"); if (e && e[0] == '0') ctx->defer_wb = false; }
     { const char *e = getenv("SYMRELAY_BUCKET"); if (e && e[0] == '0') ctx->bucket = false; }
     { const char *e = getenv("SYMRELAY_INLINE_TILES"); if (e && e[0] == '0') ctx->inline_tiles = false; }
+    if (const char *m = getenv("SYMRELAY_INJECT_REFUSAL")) ctx->inject_refusal = strtoull(m, nullptr, 10);
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE_DEV")) ctx->device_arg_flags = atoi(m) ? (SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT) : 0u;
@@ -670,6 +698,8 @@ void symrelay_destroy(symrelay_ctx *ctx) {
 }
 
 // ---- streams ------------------------------------------------------------------
+static int sched_slot_busy(symrelay_ctx *ctx, uint32_t slot);     // scheduler_impl.inc
+static void sched_slot_reset(symrelay_ctx *ctx, uint32_t slot);
 static int push_init_recs(symrelay_ctx *ctx, Shard &sh, uint32_t n) {
     CU(ctx, set_device(sh.dev));
     CU(ctx, cudaMemcpyAsync(sh.d_init, sh.h_init, sizeof(SsInitRec) * n, cudaMemcpyHostToDevice, sh.s_k));
@@ -709,6 +739,7 @@ int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_
         slots_out[i] = ctx->free_slots[g].back();
         ctx->free_slots[g].pop_back();
         ctx->slot_state[slots_out[i]] = 1;
+        sched_slot_reset(ctx, slots_out[i]);
         g = (g + 1) % ctx->n_gpus;
     }
     for (int gi = 0; gi < ctx->n_gpus; gi++) {
@@ -750,6 +781,7 @@ int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, const uint8_t
     const uint32_t slot = ctx->free_slots[g].back();
     ctx->free_slots[g].pop_back();
     ctx->slot_state[slot] = 1;
+    sched_slot_reset(ctx, slot);
     Shard &sh = ctx->shard[g];
     fill_rec(&sh.h_init[0], slot, 0, tx_key, tx_init, tx_init_len, (uint32_t)provider_kind);
     fill_rec(&sh.h_init[1], slot, 1, rx_key, rx_init, rx_init_len, (uint32_t)provider_kind);
@@ -763,11 +795,14 @@ int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot) {
     if (!ctx) return SYMRELAY_EINVAL;
     std::lock_guard<std::mutex> lk(ctx->mu);
     if (slot >= ctx->opts.max_streams || !ctx->slot_state[slot]) return fail(ctx, SYMRELAY_ENOENT, "slot %u not open", slot);
+    if (sched_slot_busy(ctx, slot))
+        return fail(ctx, SYMRELAY_EAGAIN, "slot %u still has frames in a batch that is filling or in flight: flush, poll, then close", slot);
     Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
     fill_rec(&sh.h_init[0], slot, 0, nullptr, nullptr, 0, 0);
     fill_rec(&sh.h_init[1], slot, 1, nullptr, nullptr, 0, 0);
     int rc = push_init_recs(ctx, sh, 2);  // wipes the key material on the device
     if (rc) return rc;
+    sched_slot_reset(ctx, slot);   // a half-received frame of the old connection must not eat the next one's bytes
     ctx->slot_state[slot] = 0;
     ctx->free_slots[slot % (uint32_t)ctx->n_gpus].push_back(slot);
     return 0;
@@ -836,53 +871,20 @@ int symrelay_batch_device_runs(symrelay_ctx *ctx, int gpu_index, const symrelay_
                         nullptr, (cudaStream_t)cuda_stream, 0u, reinterpret_cast<uint4 *>(d_scratch));
 }
 
-// ---- run batches without any allocation -------------------------------------------------------
-// Who needs this: a provider usually shares its GPU with the model server it relays for (Ollama,
-// llama.cpp ...), which has claimed nearly all of HBM before the relay receives its first bulk
-// segment; an allocation for run scratch made at that moment can simply fail.  And the caller is
-// Node's event-loop thread: cudaMalloc/cudaFree synchronise the whole device, which would stall
-// every connection's batch in flight.  For those callers the nonce scratch of a run batch lives in
-// this fixed array instead of caller- or library-allocated memory.  Cost: 1 MiB of HBM on every
-// GPU that loads the library, held until the process exits, and a hard cap on the batch size.
-#define SYMRELAY_STATIC_RUN_FRAMES 65536u
-static __device__ __align__(256) uint4 g_run_nonce_static[SYMRELAY_STATIC_RUN_FRAMES];
-
-// In host code `g_run_nonce_static` is only a handle for the runtime, not an address a kernel can
-// use, so the device address is looked up once per device (with that device current) and cached.
-static uint4 *g_run_nonce_static_ptr[64];
-static std::mutex g_run_nonce_static_mu;
-
-static int static_run_scratch(symrelay_ctx *ctx, int dev, uint4 **out) {
-    if (dev < 0 || dev >= 64) return fail(ctx, SYMRELAY_EINVAL, "device ordinal %d out of range", dev);
-    std::lock_guard<std::mutex> lk(g_run_nonce_static_mu);
-    if (!g_run_nonce_static_ptr[dev]) {
-        uint4 *ptr = nullptr;
-        const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_run_nonce_static);
-        if (e != cudaSuccess || !ptr)
-            return fail(ctx, SYMRELAY_ECUDA, "cudaGetSymbolAddress(run scratch) failed on device %d: %s", dev,
-                        cudaGetErrorString(e));
-        g_run_nonce_static_ptr[dev] = ptr;
-    }
-    *out = g_run_nonce_static_ptr[dev];
-    return 0;
-}
-
 int symrelay_batch_device_runs_static(symrelay_ctx *ctx, int gpu_index, const symrelay_desc *d_desc, uint32_t n,
                                       const symrelay_tile *d_tiles, uint32_t n_tiles, uint32_t n_bulk_tiles,
                                       const uint8_t *d_in, uint8_t *d_out, uint32_t *d_status, void *cuda_stream) {
     if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
     if (n == 0 || n_tiles == 0) return 0;
-    if (n > SYMRELAY_STATIC_RUN_FRAMES)
+    if (n > SYMRELAY_STATIC_RUN_MAX)
         return fail(ctx, SYMRELAY_EINVAL,
                     "symrelay_batch_device_runs_static: %u descriptors exceed the built-in scratch of %u; split the "
-                    "batch or use symrelay_batch_device_runs with your own scratch", n, SYMRELAY_STATIC_RUN_FRAMES);
+                    "batch or use symrelay_batch_device_runs with your own scratch", n, SYMRELAY_STATIC_RUN_MAX);
     if (!d_desc || !d_tiles || !d_in || !d_out || !d_status || n_bulk_tiles > n_tiles)
         return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_device_runs_static: null pointer or bad tile counts");
     Shard &sh = ctx->shard[gpu_index];
     CU(ctx, set_device(sh.dev));
-    uint4 *scratch = nullptr;
-    const int rc = static_run_scratch(ctx, sh.dev, &scratch);
-    if (rc) return rc;
+    uint4 *scratch = sh.d_run_static;   // resolved by symrelay_create with this GPU current
     // Nothing in the array has to start at zero: the nonce pre-pass of this call writes every entry that
     // this call's tile kernels read (entries of non-run descriptors keep stale values and are never read).
     return launch_tiles(ctx, d_desc, n, d_tiles, n_tiles, n_bulk_tiles, d_in, d_out, sh.d_states, d_status, nullptr,
@@ -981,11 +983,29 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (ng > 1)
         for (uint32_t i = 0; i < n; i++) bad |= (uint32_t)((int)(desc[i].slot % ng) != gpu_index);
     if (bad) return fail(ctx, SYMRELAY_EINVAL, "a descriptor points outside its arena, names a slot beyond max_streams, or a slot that is not on gpu %d", gpu_index);
-    {   // a closed slot holds an all-zero key: sealing with it must be impossible, not merely wrong
+    {   // a closed slot holds an all-zero key: sealing with it must be impossible, not merely wrong.  The same
+        // walk enforces the chain rule of the header: at most one frame per (slot, direction) in a batch --
+        // a second one would race the first on the nonce chain in HBM and both would "succeed" -- except
+        // inbound runs (consecutive F_OPEN|F_RUN descriptors of one slot), and those at most 64 long.
         const uint8_t *open_slot = ctx->slot_state.data();
-        uint32_t closed = 0;
-        for (uint32_t i = 0; i < n; i++) closed |= (uint32_t)(open_slot[desc[i].slot] == 0);
+        uint32_t *stamp = sh.slot_stamp.data();
+        if (++sh.stamp == 0u) { std::fill(sh.slot_stamp.begin(), sh.slot_stamp.end(), 0u); sh.stamp = 1u; }
+        const uint32_t now = sh.stamp, runf = SYMRELAY_F_OPEN | SYMRELAY_F_RUN;
+        uint32_t closed = 0, dup = 0, run_len = 1, too_long = 0, prev_slot = 0xffffffffu, prev_lf = 0;
+        for (uint32_t i = 0; i < n; i++) {
+            const uint32_t slot = desc[i].slot, lf = desc[i].len_flags;
+            closed |= (uint32_t)(open_slot[slot] == 0);
+            const uint32_t idx = slot * 2u + ((lf >> 26) & 1u);
+            const bool cont = slot == prev_slot && (lf & runf) == runf && (prev_lf & runf) == runf;
+            dup |= (uint32_t)(stamp[idx] == now && !cont);
+            stamp[idx] = now;
+            run_len = cont ? run_len + 1u : 1u;
+            too_long |= (uint32_t)(run_len > SS_RUN_MAX);
+            prev_slot = slot; prev_lf = lf;
+        }
         if (closed) return fail(ctx, SYMRELAY_ENOENT, "a descriptor names a slot that is not open");
+        if (dup) return fail(ctx, SYMRELAY_EINVAL, "two frames of one (slot, direction) in a batch: a stream's frames are MAC-chained, put them in consecutive batches (or mark inbound ones SYMRELAY_F_RUN)");
+        if (too_long) return fail(ctx, SYMRELAY_EINVAL, "a run of more than %u SYMRELAY_F_RUN frames of one slot", SS_RUN_MAX);
     }
     bool extract = false;
     const bool runs = (any_flags & SYMRELAY_F_RUN) != 0;

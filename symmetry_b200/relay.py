@@ -24,7 +24,7 @@ F_OPEN = 0x04000000
 F_EXTRACT = 0x08000000
 F_RUN = 0x10000000
 LEN_MASK = 0x00FFFFFF
-ST_OK, ST_BAD_MAC, ST_TOO_SHORT, ST_EXTRACT_THROW, ST_EXTRACT_UNSUPPORTED, ST_RETRY = 0, 1, 2, 3, 4, 5
+ST_OK, ST_BAD_MAC, ST_TOO_SHORT, ST_EXTRACT_THROW, ST_EXTRACT_UNSUPPORTED, ST_RETRY, ST_FAILED = 0, 1, 2, 3, 4, 5, 6
 EAGAIN = -11
 PROVIDER_DEFAULT, PROVIDER_OLLAMA, PROVIDER_LLAMACPP = 0, 1, 2
 STATEBYTES, HEADERBYTES, KEYBYTES, WIRE_OVERHEAD = 52, 24, 32, 20
@@ -250,8 +250,7 @@ class SymRelay:
                                  d_out: int, d_status: int, stream: int = 0, gpu_index: int = 0):
         """batch_device_runs for callers that cannot allocate (the GPU is full of model weights, or the
         caller is an event-loop thread that must not trigger cudaMalloc's device-wide sync): the nonce
-        scratch is a fixed 1 MiB array inside the library, so n is capped at 65,536 descriptors.  The
-        first call on a GPU does a one-time address look-up (do it before any stream capture); calls
+        scratch is a fixed 1 MiB array inside the library, so n is capped at 65,536 descriptors.  Calls
         share the array, so keep them ordered on one stream."""
         self._check(self.lib.symrelay_batch_device_runs_static(self.ctx, gpu_index, d_desc, n, d_tiles, n_tiles, n_bulk,
                                                                d_in, d_out, d_status, stream))

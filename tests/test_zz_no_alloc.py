@@ -60,6 +60,32 @@ def _run_batch(relay, call, slots, owner, wires, lens):
     return t_out.cpu().numpy(), t_status.cpu().numpy().astype(np.uint32), p_offs
 
 
+def _assert_call_allocates_nothing(relay, slots):
+    """The property in the entry point's name: the driver's free-memory figure is the same before and
+    after a call (buffers are prepared first, outside the window; torch's allocator is not involved)."""
+    import torch
+
+    dev = torch.device("cuda:0")
+    k, h = bytes(32), bytes(24)
+    w = ls.State(k, h).seal_frame(b"probe")        # forged for these slots: the call runs, the frames fail, no state moves
+    descs = bu.make_descs([slots[0], slots[0]], [5, 5], [12, 44], [0, 16], open_=True, run=True)
+    tiles, n_bulk = relay.plan(descs)
+    arena = np.zeros(96, dtype=np.uint8)
+    arena[12:12 + len(w)] = np.frombuffer(w, dtype=np.uint8)
+    arena[44:44 + len(w)] = np.frombuffer(w, dtype=np.uint8)
+    t = [torch.from_numpy(x.view(np.uint8).copy()).to(dev) for x in (descs, tiles, arena)]
+    t_out = torch.zeros(32, dtype=torch.uint8, device=dev)
+    t_st = torch.full((2,), 0xFF, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(dev)        # cudaMemGetInfo
+    relay.batch_device_runs_static(t[0].data_ptr(), 2, t[1].data_ptr(), len(tiles), n_bulk, t[2].data_ptr(),
+                                   t_out.data_ptr(), t_st.data_ptr(), stream=torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(dev)
+    assert free1 == free0, f"the allocation-free entry point changed free device memory by {free0 - free1} bytes"
+    assert ((t_st.cpu().numpy() & 0xFF) != 0).all()   # forged frames: refused, chains untouched
+
+
 def test_static_scratch_entry_point_matches_the_existing_one_twice_in_a_row():
     import symmetry_b200 as sb
 
@@ -78,6 +104,8 @@ def test_static_scratch_entry_point_matches_the_existing_one_twice_in_a_row():
             owner, wires, lens = _scenario(rng, n_streams, senders)
             out_a, st_a, p_offs = _run_batch(relay, "existing", slots_a, owner, wires, lens)
             out_b, st_b, _ = _run_batch(relay, "static", slots_b, owner, wires, lens)
+            if call_no == 1:
+                _assert_call_allocates_nothing(relay, slots_b)
             assert (st_a == st_b).all(), f"status words differ on call {call_no}"
             assert (out_a == out_b).all(), f"plaintext differs on call {call_no}"
             # and both are what sequential libsodium pulls give; frames held back behind a REKEY are
