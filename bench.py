@@ -1,7 +1,8 @@
 #!/usr/bin/env python3
 """bench.py -- batched secretstream seal+open throughput on B200(s).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c1|c3|c4|c5|c4sweep]
+                    [--impl ours|reference] [--sub c4,c3|none]
 
 A "step" is one pass of the relay hot path over one batch: every stream seals
 one outbound frame AND opens one inbound frame (one mixed batch = one kernel
@@ -9,9 +10,12 @@ launch per tile class).  Default workload = BASELINE.json configs[1]: 1,024
 concurrent streams x 64 B token-delta frames, batched seal+open on 1 B200.
 `value` is device-resident (inputs already in HBM); `e2e` goes through the
 C ABI's host-buffer batch call with pinned host arenas, H2D and D2H inside the
-timed region.  `--impl reference` times the reference's CPU path for the same
-workload: real libsodium (the C library under sodium-native) driven by the C
-loop in oracle/cpu_bench.c on all host cores.  Prints ONE JSON line.
+timed region.  The default line also carries `c4` and `c3` sub-objects (the
+bulk roofline probe and the ragged 65,536-stream batch sharded over the N
+ranks), measured in the same run, device-resident.  `--impl reference` times
+the reference's CPU path for the same workload: real libsodium (the C library
+under sodium-native) driven by the C loop in oracle/cpu_bench.c on all host
+cores.  Prints ONE JSON line.
 """
 from __future__ import annotations
 
@@ -33,31 +37,33 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 L2_BYTES = 126 << 20
 METRIC = "sealed_frames_per_sec"
+DEFAULT_STEPS = {"c2": 20000, "c3": 200, "c4": 64, "c5": 360, "c1": 20, "c4sweep": 8}
+SUB_STEPS = {"c4": 24, "c3": 120}          # steps of the sub-lines riding on the default line
 
 
 # ------------------------------------------------------------------ workload --
-def workload(name: str, n_gpus: int):
-    from symmetry_b200 import synth
+def workload(name: str, n_gpus: int, rank: int = 0):
+    """(lens of this rank's streams, description, scaling, first stream id of this rank)."""
+    from symmetry_b200 import shard, synth
 
     if name == "c2":
         lens = np.full(1024, 64, dtype=np.int64)
         desc = "configs[1]: 1,024 concurrent streams x 64 B token-delta frames, batched seal+open"
-        scaling = "weak"
-    elif name == "c3":
+        return lens, desc, "weak", rank * 1024
+    if name == "c3":
         total = 65536
-        lens = synth.power_law_lens(total)[: total // n_gpus]
-        desc = "configs[2]: 65,536 streams, power-law frames 32 B-16 KiB (alpha 1.2), sharded by slot, frames in arrival order"
+        lo, hi = shard.shard_streams(total, n_gpus, rank)      # connections shard by key; no data-path collective
+        lens = synth.power_law_lens(total)[lo:hi]
+        desc = "configs[2]: 65,536 streams, power-law frames 32 B-16 KiB (alpha 1.2), sharded by connection over the GPUs, frames in arrival order"
         if os.environ.get("BENCH_C3_SORTED", "0") not in ("", "0"):
             lens = np.sort(lens)     # what a gather step that buckets frames by size would hand over
             desc = desc.replace("frames in arrival order", "frames bucketed by size")
-        scaling = "strong"
-    elif name == "c4":
+        return lens, desc, "strong", lo
+    if name == "c4":
         lens = np.full(16384, 65536, dtype=np.int64)
         desc = "configs[3]: bulk 64 KiB frames, 16,384 streams per round (1 GiB), seal+open"
-        scaling = "weak"
-    else:
-        raise SystemExit(f"unknown workload {name}")
-    return lens, desc, scaling
+        return lens, desc, "weak", rank * 16384
+    raise SystemExit(f"unknown workload {name}")
 
 
 class Layout:
@@ -65,11 +71,14 @@ class Layout:
     and writes wire_i ‖ recovered_{i-D} into slot i+D at offset P."""
 
     def __init__(self, lens):
-        import batch_util as bu
-
-        self.lens = [int(x) for x in lens]
-        self.p_offs, self.P = bu.plain_layout(self.lens)
-        self.w_offs, self.Wb = bu.wire_layout(self.lens)
+        lens = np.asarray(lens, dtype=np.int64)
+        self.lens = lens
+        pw = np.maximum(16, (lens + 15) & ~15)
+        ww = (12 + lens + 20 + 15) & ~15
+        self.p_offs = np.concatenate([[0], np.cumsum(pw)[:-1]]).astype(np.int64) if len(lens) else np.zeros(0, np.int64)
+        self.w_offs = (np.concatenate([[0], np.cumsum(ww)[:-1]]) + 12).astype(np.int64) if len(lens) else np.zeros(0, np.int64)
+        self.P = int(pw.sum())
+        self.Wb = int(ww.sum())
         self.in_bytes = self.P + self.Wb
         self.out_bytes = self.Wb + self.P
         self.slot_bytes = self.P + self.Wb + self.P
@@ -80,23 +89,49 @@ class Layout:
         seal = bu.make_descs(slots, self.lens, self.p_offs, self.w_offs)
         if not with_open:
             return seal
-        opn = bu.make_descs(slots, self.lens, [self.P + o for o in self.w_offs], [self.Wb + o for o in self.p_offs],
-                            open_=True)
+        opn = bu.make_descs(slots, self.lens, self.P + self.w_offs, self.Wb + self.p_offs, open_=True)
         return np.concatenate([seal, opn])
 
 
 def algorithmic_bytes(lens) -> int:
     """2*mlen + 92 per frame (seal and open alike)."""
-    return int(sum(2 * int(L) + 92 for L in lens))
+    lens = np.asarray(lens, dtype=np.int64)
+    return int((2 * lens + 92).sum())
 
 
 def int_ops(lens) -> int:
     """992 * nC + 70 * nP per frame."""
-    t = 0
-    for L in lens:
-        L = int(L)
-        t += 992 * (2 + (L + 63) // 64) + 70 * ((80 + L + L % 16 + 15) // 16)
-    return t
+    L = np.asarray(lens, dtype=np.int64)
+    return int((992 * (2 + (L + 63) // 64) + 70 * ((80 + L + L % 16 + 15) // 16)).sum())
+
+
+def ring_slots(lay: Layout) -> int:
+    return int(min(2048, max(4, math.ceil(2 * L2_BYTES / max(lay.slot_bytes, 1)))))
+
+
+def make_config(name: str, n_gpus: int, K: int, no_graph: bool, plan_mode: str) -> dict:
+    """The ONE description of the workload both arms print (the driver compares the two dicts)."""
+    lens, desc, scaling, _ = workload(name, n_gpus, 0)
+    lay = Layout(lens)
+    R = ring_slots(lay)
+    n_replays = 0 if no_graph else K // R
+    return {
+        "workload": desc, "n_gpus": n_gpus, "streams_per_gpu": int(len(lens)),
+        "frames_per_step_per_gpu": 2 * int(len(lens)), "plaintext_bytes_per_step_per_gpu": int(lens.sum()),
+        "step": "every stream seals one frame and opens one frame (mixed batch); both chains run through all steps",
+        "plan": ("symrelay_plan_sorted (library groups the frames by size class)" if plan_mode == "sorted"
+                 else "symrelay_plan (caller's descriptor order)"),
+        "l2": f"GPU arm: inputs larger than L2 -- ring of {R} distinct batch slots, {R * lay.slot_bytes >> 20} MiB, visited "
+              f"round-robin, L2 flushed once before timing; CPU arm: ring of 4 batch slots in host memory",
+        "launch": ("GPU arm: direct launches" if no_graph else
+                   f"GPU arm: {n_replays} replays of a CUDA graph holding {R} steps + one graph of the last {K - n_replays * R} "
+                   "steps, each replayed once untimed first (graph upload)")
+                  + "; CPU arm: a pool of host threads started and warmed before the timed steps",
+    }
+
+
+def plan_mode_for(name: str) -> str:
+    return os.environ.get("BENCH_PLAN", "sorted" if name == "c3" else "caller")
 
 
 # -------------------------------------------------------------------- clocks --
@@ -149,7 +184,8 @@ class ClockSampler:
 
 # --------------------------------------------------------------- CPU baseline --
 def cpu_run(lens, steps, warmup, threads, prefer="reference"):
-    """Times seal+open of one frame per stream per step on host cores.  Returns (seconds for `steps`, kind)."""
+    """Times seal+open of one frame per stream per step on host cores: `warmup` untimed steps and then
+    `steps` timed ones on the same pool of threads.  Returns (seconds for `steps`, kind)."""
     from oracle import secretstream as ss_port
     from symmetry_b200 import synth
 
@@ -180,15 +216,9 @@ def cpu_run(lens, steps, warmup, threads, prefer="reference"):
     p_off = np.asarray(lay.p_offs, dtype=np.uint64)
     w_off = np.asarray(lay.w_offs, dtype=np.uint64)
     lens32 = np.asarray(lens, dtype=np.uint32)
-
-    def go(k):
-        return lib.cpub_run(push, pull, tx.ctypes.data, rx.ctypes.data, n, plain.ctypes.data, p_off.ctypes.data,
-                            lens32.ctypes.data, lay.P, wire.ctypes.data, w_off.ctypes.data, lay.Wb, ring, k, 1, 1,
-                            threads)
-
-    if warmup:
-        assert go(warmup) >= 0
-    sec = go(steps)
+    sec = lib.cpub_run(push, pull, tx.ctypes.data, rx.ctypes.data, n, plain.ctypes.data, p_off.ctypes.data,
+                       lens32.ctypes.data, lay.P, wire.ctypes.data, w_off.ctypes.data, lay.Wb, ring, steps, warmup, 1, 1,
+                       threads)
     assert sec >= 0, "CPU path reported a failed pull"
     assert (tx == rx).all(), "CPU seal/open chains diverged"
     return sec, kind
@@ -217,15 +247,19 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    lens, desc, scaling = workload(args.workload, 1)
+    name = args.workload if args.workload in ("c2", "c3", "c4") else "c2"
+    lens, desc, scaling, _ = workload(name, 1)
     if scaling == "weak" and args.gpus > 1:
         lens = np.tile(lens, args.gpus)      # same whole-job batch as our arm at N GPUs (per-GPU work is fixed)
     threads = host_threads()
     # bound the run: a step is the same batch, but never let warmup+steps exceed ~2 minutes
-    probe, kind = cpu_run(lens, 1, 0, threads)
-    max_steps = max(1, int(120.0 / max(probe, 1e-6)))
+    probe, kind = cpu_run(lens, 2, 1, threads)
+    max_steps = max(1, int(120.0 / max(probe / 2, 1e-6)))
     steps = min(args.steps, max_steps)
-    warm = min(args.warmup, max(1, max_steps // 10))
+    # The pool warms up on the same threads before the timed steps; a short timed region (the driver's
+    # --steps 20 is about a millisecond of CPU work) needs more warm-up than --warmup to reach the steady
+    # state the long cpu_baseline sample of the other arm measures, so warm for at least ~50 ms.
+    warm = max(args.warmup, min(max_steps, int(0.05 / max(probe / 2, 1e-9))))
     sec, kind = cpu_run(lens, steps, warm, threads)
     frames = len(lens) * steps
     val = frames / sec
@@ -233,12 +267,12 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": sec / steps * 1e3, "higher_is_better": True,
         "scaling": scaling, "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": desc, "streams": len(lens), "frames_per_step": 2 * len(lens),
-                   "plaintext_bytes_per_step": int(sum(lens))},
+        "config": make_config(name, args.gpus, args.steps, args.no_graph, plan_mode_for(name)),
         "gb_per_s": float(sum(lens)) * steps / sec / 1e9,
         "cpu_baseline": {"value": val, "unit": "frames/s", "cores": threads, "kind": kind,
-                         "sample": f"{steps} steps of the full batch (seal+open, {len(lens)} streams), "
-                                   f"libsodium 1.0.20 (PyNaCl build) via oracle/cpu_bench.c, {cpu_model()}"},
+                         "sample": f"{steps} steps of the whole-job batch (seal+open, {len(lens)} streams) after {warm} "
+                                   f"warm-up steps on the same thread pool, libsodium 1.0.20 (PyNaCl build) via "
+                                   f"oracle/cpu_bench.c, {cpu_model()}"},
         "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -246,61 +280,81 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------- ours --
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
+class Job:
+    """torch.distributed plumbing shared by the legs of one run."""
 
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device(f"cuda:{self.local}"))
+        self.n_gpus = max(self.world, 1)
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device(f"cuda:{self.local}")
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x: float) -> float:
+        from symmetry_b200 import shard
+
+        return shard.max_over_ranks(x, self.dist if self.world > 1 else None, self.dev)
+
+    def sum_over_ranks(self, x: float) -> float:
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+def measure_device(job: Job, name: str, K: int, W: int, no_graph: bool, relay=None, keep_relay=False, custom=None):
+    """Device-resident leg of one workload: K timed steps (CUDA events on the launching stream, barrier +
+    synchronize on both sides, max over ranks), then the spot check against libsodium.  Returns a dict."""
     import symmetry_b200 as sb
     from oracle import libsodium as ls
     from symmetry_b200 import synth
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
-    n_gpus = max(world, 1)
-    torch.cuda.set_device(local)
-    dev = torch.device(f"cuda:{local}")
-
-    lens, desc, scaling = workload(args.workload, n_gpus)
+    torch = job.torch
+    dev = job.dev
+    if custom is not None:          # (lens, description, scaling, keys, headers): the size sweep brings its own
+        lens, desc, scaling, keys, hdrs = custom
+    else:
+        lens, desc, scaling, first = workload(name, job.n_gpus, job.rank)
+        keys, hdrs = synth.stream_keys(len(lens), first=first)
     n = len(lens)
     lay = Layout(lens)
-    K, W = args.steps, args.warmup
-    D_DEV, D_E2E = 1, int(os.environ.get("BENCH_E2E_DEPTH", "6"))
-    stage_bytes = max(64 << 20, (lay.in_bytes + 4095) // 4096 * 4096)
-    relay = sb.SymRelay(gpu_ids=(local,), max_streams=max(4 * n, 4096), pipeline_depth=D_E2E,
-                        stage_bytes=stage_bytes, max_batch_frames=max(2 * n, 4096))
-    keys, hdrs = synth.stream_keys(n, first=rank * n)
+    D = 1
+    own_relay = relay is None
+    if own_relay:
+        relay = sb.SymRelay(gpu_ids=(job.local,), max_streams=max(2 * n, 4096), pipeline_depth=1, stage_bytes=1 << 20,
+                            max_batch_frames=4096)
     sample = sorted(set([0, 1, n // 2, n - 1] + [int(i) for i in np.argsort(lens)[-2:]]))
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    def max_over_ranks(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # ---------------- device-resident run: `value` ---------------------------
     slots = relay.open_streams(keys, hdrs, keys, hdrs)
-    R = int(min(2048, max(4, math.ceil(2 * L2_BYTES / lay.slot_bytes))))
+    R = ring_slots(lay)
     ring = torch.empty(R * lay.slot_bytes, dtype=torch.uint8, device=dev)
     gen = torch.Generator(device=dev)
-    gen.manual_seed(1234 + rank)
+    gen.manual_seed(1234 + job.rank)
     ring.random_(0, 256, generator=gen)
     flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
     d_full = lay.descs(slots, True)
     d_seal = lay.descs(slots, False)
     # Ragged batches are planned with the library's sorting planner (descriptors grouped by size class, statuses
     # come back through a permutation); BENCH_PLAN=caller keeps the frames in arrival order.
-    plan_mode = os.environ.get("BENCH_PLAN", "sorted" if args.workload == "c3" else "caller")
+    plan_mode = plan_mode_for(name)
     if plan_mode == "sorted":
         tiles_full, nb_full, d_full, _perm_full = relay.plan_sorted(d_full)
         tiles_seal, nb_seal, d_seal, _perm_seal = relay.plan_sorted(d_seal)
@@ -318,7 +372,7 @@ def run_ours(args):
     def dev_step(i, full=True):
         stream = torch.cuda.current_stream().cuda_stream
         src = base + (i % R) * lay.slot_bytes
-        dst = base + ((i + D_DEV) % R) * lay.slot_bytes + lay.P
+        dst = base + ((i + D) % R) * lay.slot_bytes + lay.P
         if full:
             relay.batch_device(t_dfull.data_ptr(), 2 * n, t_tfull.data_ptr(), len(tiles_full), nb_full, src, dst,
                                t_status.data_ptr(), stream=stream)
@@ -330,11 +384,11 @@ def run_ours(args):
     ring_plain_host = {}
     ring_view = ring.view(R, lay.slot_bytes)
     for s in sample:
-        o, L = lay.p_offs[s], lay.lens[s]
+        o, L = int(lay.p_offs[s]), int(lay.lens[s])
         ring_plain_host[s] = ring_view[:, o:o + L].cpu().numpy().copy()
 
     step_no = 0
-    for _ in range(D_DEV):                      # priming: seal only (no inbound frames exist yet)
+    for _ in range(D):                      # priming: seal only (no inbound frames exist yet)
         dev_step(step_no, full=False)
         step_no += 1
     for _ in range(W):
@@ -343,11 +397,11 @@ def run_ours(args):
     # The inner loop is launch-bound, so R consecutive steps (one lap of the ring) are captured in a
     # CUDA graph and replayed; the remaining K % R steps are launched directly.  Every step is still
     # its own kernel launch (graph node).
-    n_replays = 0 if args.no_graph else K // R
+    n_replays = 0 if no_graph else K // R
     n_rem = K - n_replays * R
     graph = graph_rem = None
     launches_per_lap = launches_rem = 0
-    if not args.no_graph:
+    if not no_graph:
         while step_no % R:                       # extra untimed warm-up so a lap starts at slot 0
             dev_step(step_no)
             step_no += 1
@@ -380,8 +434,7 @@ def run_ours(args):
                 step_no += 1
         torch.cuda.synchronize()
     flush.zero_()                                # evict whatever set-up left in L2
-    clocks = ClockSampler(local)
-    barrier()
+    job.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = relay.launches
     t_w0 = time.perf_counter()
@@ -397,46 +450,137 @@ def run_ours(args):
             dev_step(step_no)
             step_no += 1
     e1.record()
-    barrier()
+    job.barrier()
     t_w1 = time.perf_counter()
-    dev_ms = max_over_ranks(e0.elapsed_time(e1))
+    dev_ms = job.max_over_ranks(e0.elapsed_time(e1))
     gpu_launches = relay.launches - launches0 + n_replays * launches_per_lap + (launches_rem if graph_rem is not None else 0)
     total_steps = step_no
 
     # parity spot-check of the timed run against libsodium (tx chain, rx chain, last wire, recovered plaintext)
     st = t_status.cpu().numpy()
-    assert (st == 0).all(), "non-OK frame status in the last timed step"
+    assert (st == 0).all(), f"{name}: non-OK frame status in the last timed step"
     last = total_steps - 1
-    wire_slot = ring_view[(last + D_DEV) % R].cpu().numpy()
+    wire_slot = ring_view[(last + D) % R].cpu().numpy()
     for s in sample:
         ref = ls.State(bytes(keys[s]), bytes(hdrs[s]))
         rx_expect = None
         w = None
         for i in range(total_steps):
-            if i == total_steps - D_DEV:
+            if i == total_steps - D:
                 rx_expect = ref.raw
             w = ref.seal_frame(bytes(ring_plain_host[s][i % R]))
         tx_state, rx_state = relay.export(int(slots[s]))
-        assert tx_state == ref.raw, f"tx chain of stream {s} differs from libsodium after {total_steps} frames"
-        assert rx_state == rx_expect, f"rx chain of stream {s} differs from libsodium"
-        o = lay.P + lay.w_offs[s]
-        assert bytes(wire_slot[o:o + len(w)]) == w, f"last wire frame of stream {s} differs from libsodium"
-        ro = lay.P + lay.Wb + lay.p_offs[s]
-        assert bytes(wire_slot[ro:ro + lay.lens[s]]) == bytes(ring_plain_host[s][(last - D_DEV) % R]), "recovered plaintext"
+        assert tx_state == ref.raw, f"{name}: tx chain of stream {s} differs from libsodium after {total_steps} frames"
+        assert rx_state == rx_expect, f"{name}: rx chain of stream {s} differs from libsodium"
+        o = lay.P + int(lay.w_offs[s])
+        assert bytes(wire_slot[o:o + len(w)]) == w, f"{name}: last wire frame of stream {s} differs from libsodium"
+        ro = lay.P + lay.Wb + int(lay.p_offs[s])
+        assert bytes(wire_slot[ro:ro + int(lay.lens[s])]) == bytes(ring_plain_host[s][(last - D) % R]), "recovered plaintext"
 
-    # integer roofline denominators, measured on this GPU right now
-    arx_tops, imad_tops = relay.probe_int_peak(0)
+    arx_tops, imad_tops = relay.probe_int_peak(0)    # integer roofline denominators, measured on this GPU right now
+    del ring, flush, ring_view
+    torch.cuda.empty_cache()
+    if own_relay and not keep_relay:
+        relay.close()
+        relay = None
+
+    # whole-job figures: every rank's units over the slowest rank's time
+    dev_s = dev_ms * 1e-3
+    frames_all = job.sum_over_ranks(float(n)) * K
+    plain_all = job.sum_over_ranks(float(lens.sum())) * K
+    alg_bytes = algorithmic_bytes(lens) * 2              # this rank's launch: seal + open
+    ops = int_ops(lens) * 2
+    hbm_peak, hbm_src = hbm_peak_gbs()
+    per_step_ms = dev_ms / K
+    achieved_gbs = alg_bytes / (per_step_ms * 1e-3) / 1e9
+    achieved_tops = ops / (per_step_ms * 1e-3) / 1e12
+    res = {
+        "workload": desc, "scaling": scaling, "steps": K, "ms_per_step": per_step_ms,
+        "value": frames_all / dev_s, "unit": "frames/s", "gb_per_s": plain_all / dev_s / 1e9,
+        "streams_per_gpu": n,
+        "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                     "kernel": "ss_packed_kernel" if nb_full == 0 else ("ss_bulk_kernel" if nb_full == len(tiles_full)
+                                                                        else "ss_packed_kernel + ss_bulk_kernel (concurrent)"),
+                     "algorithmic_bytes_per_launch": alg_bytes,
+                     "note": "the path is integer-ALU bound (SURVEY 8(d)); see alu_roofline.  traffic: measured only "
+                             "under ncu, see traffic_ncu"},
+        "alu_roofline": {"bound": "int_alu", "achieved": achieved_tops, "peak": arx_tops, "unit": "Tint-op/s",
+                         "frac": achieved_tops / arx_tops, "int_ops_per_launch": ops,
+                         "peak_source": "symrelay_probe_int_peak (ChaCha ARX mix, measured now)",
+                         "imad_wide_tops": imad_tops},
+        "gpu_launches": int(gpu_launches), "launches_per_step": launches_per_step,
+        "parity": "timed run spot-checked against libsodium: tx/rx chains, last wire frames, recovered plaintext: ok",
+    }
+    tn = traffic_ncu(name)
+    if tn:
+        res["roofline"]["traffic_ncu"] = tn
+    extra = {"lens": lens, "lay": lay, "keys": keys, "hdrs": hdrs, "sample": sample, "window": (t_w0, t_w1),
+             "relay": relay, "n_tiles_full": len(tiles_full), "plan_mode": plan_mode, "R": R}
+    return res, extra
+
+
+def traffic_ncu(name: str):
+    """DRAM bytes per launch of the dominant kernel from a separate `ncu --set full` capture (never measured in a
+    timed run): {"bytes": ..., "source": file under profiles/}; None when no capture of this round is committed."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get(name)
+        return t if isinstance(t, dict) else None
+    except Exception:
+        return None
+
+
+def pcie_peaks(job: Job):
+    """(h2d GB/s, d2h GB/s): pinned 64 MiB cudaMemcpyAsync each way, best of 5, CUDA events."""
+    torch = job.torch
+    nbytes = 64 << 20
+    h = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    d = torch.empty(nbytes, dtype=torch.uint8, device=job.dev)
+    best = [1e30, 1e30]
+    for rep in range(6):
+        for k in (0, 1):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if k == 0:
+                d.copy_(h, non_blocking=True)
+            else:
+                h.copy_(d, non_blocking=True)
+            e1.record()
+            torch.cuda.synchronize()
+            if rep:
+                best[k] = min(best[k], e0.elapsed_time(e1))
+    return nbytes / (best[0] * 1e-3) / 1e9, nbytes / (best[1] * 1e-3) / 1e9
+
+
+def run_ours(args):
+    import symmetry_b200 as sb
+    from oracle import libsodium as ls
+
+    job = Job()
+    torch = job.torch
+    name = args.workload
+    K, W = args.steps, args.warmup
+    D_E2E = int(os.environ.get("BENCH_E2E_DEPTH", "6"))
+    lens, desc, scaling, first = workload(name, job.n_gpus, job.rank)
+    n = len(lens)
+    lay0 = Layout(lens)
+    stage_bytes = max(64 << 20, (lay0.in_bytes + 4095) // 4096 * 4096)
+    relay = sb.SymRelay(gpu_ids=(job.local,), max_streams=max(4 * n, 4096), pipeline_depth=D_E2E,
+                        stage_bytes=stage_bytes, max_batch_frames=max(2 * n, 4096))
+    clocks = ClockSampler(job.local)
+    res, x = measure_device(job, name, K, W, args.no_graph, relay=relay)
+    lay, keys, hdrs, sample = x["lay"], x["keys"], x["hdrs"], x["sample"]
+    windows = [x["window"]]
 
     # ---------------- end-to-end through host arenas: `e2e` -------------------
-    del ring, flush
-    torch.cuda.empty_cache()
     slots2 = relay.open_streams(keys, hdrs, keys, hdrs)
     R2 = max(2 * D_E2E + 2, 8)
     if args.no_e2e:
         R2 = 1
     hring = relay.alloc_pinned(R2 * lay.slot_bytes)
-    hring[:] = np.random.default_rng(99 + rank).integers(0, 256, hring.size, dtype=np.uint8)
-    hplain = {s: [bytes(hring[j * lay.slot_bytes + lay.p_offs[s]: j * lay.slot_bytes + lay.p_offs[s] + lay.lens[s]])
+    hring[:] = np.random.default_rng(99 + job.rank).integers(0, 256, hring.size, dtype=np.uint8)
+    hplain = {s: [bytes(hring[j * lay.slot_bytes + int(lay.p_offs[s]): j * lay.slot_bytes + int(lay.p_offs[s]) + int(lay.lens[s])])
                   for j in range(R2)] for s in sample}
     e_full = lay.descs(slots2, True)
     e_seal = lay.descs(slots2, False)
@@ -466,11 +610,12 @@ def run_ours(args):
         e2e_step(i2)
         i2 += 1
     e2e_drain()
-    barrier()
+    job.barrier()
     # The timed loop is driven from C (tools/e2e_driver.c, a plain caller of the public C ABI, as the
-    # N-API addon would be): per batch it calls symrelay_batch_wait(ticket[i-4]) then
+    # N-API addon would be): per batch it calls symrelay_batch_wait(ticket[i-depth]) then
     # symrelay_batch_submit(...) on the same ring -- the calls e2e_step() makes, minus the interpreter.
     e2e_driver = "python"
+    batch_lat = None
     t0 = time.perf_counter()
     if K2 and not args.py_e2e:
         from symmetry_b200 import build as sbuild
@@ -496,30 +641,57 @@ def run_ours(args):
         e2e_drain()
         torch.cuda.synchronize()
         t1 = time.perf_counter()
-    e2e_sec = max_over_ranks(t1 - t0)
-    clk = clocks.stop([(t_w0, t_w1), (t0, t1)])
+    e2e_sec = job.max_over_ranks(t1 - t0)
+    windows.append((t0, t1))
+    clk = clocks.stop(windows)
     for j in sorted({i % R2 for i in range(max(0, i2 - K2), i2)} if K2 else set()):
         assert (hstat[j] == 0).all(), "non-OK status in the e2e run"
+    # per-batch latency of the synchronous call over a 1,000-deep chain ("batch latency p50/p99")
+    if K2 and not args.py_e2e and job.rank == 0 and name == "c2":
+        drv.e2e_sync_latency.restype = C.c_int
+        drv.e2e_sync_latency.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64,
+                                         C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
+        nlat = 1000
+        lat_ns = np.zeros(nlat, dtype=np.uint64)
+        stat_all[:] = 0xFF
+        rc = drv.e2e_sync_latency(relay.ctx, e_full.ctypes.data, 2 * n, hbase, lay.slot_bytes, lay.in_bytes, lay.P,
+                                  lay.out_bytes, R2, D_E2E, i2, nlat, stat_all.ctypes.data, lat_ns.ctypes.data)
+        assert rc == 0, f"sync latency driver failed: {rc}"
+        i2 += nlat
+        batch_lat = {"batches": nlat, "p50_us": float(np.percentile(lat_ns, 50)) / 1e3,
+                     "p99_us": float(np.percentile(lat_ns, 99)) / 1e3, "mean_us": float(lat_ns.mean()) / 1e3,
+                     "what": "symrelay_batch_host round trip (host arenas in, results visible to the host) of one "
+                             "2,048-frame batch, 1,000 consecutive batches on the same chains, one in flight"}
     for s in (sample if K2 else []):
         ref = ls.State(bytes(keys[s]), bytes(hdrs[s]))
         for i in range(i2):
             w = ref.seal_frame(hplain[s][i % R2])
         assert relay.export(int(slots2[s]))[0] == ref.raw, "e2e tx chain differs from libsodium"
-        o = ((i2 - 1 + D_E2E) % R2) * lay.slot_bytes + lay.P + lay.w_offs[s]
+        o = ((i2 - 1 + D_E2E) % R2) * lay.slot_bytes + lay.P + int(lay.w_offs[s])
         assert bytes(hring[o:o + len(w)]) == w, "e2e last wire frame differs from libsodium"
+    relay.close()
+    relay = None
+    h2d_peak, d2h_peak = pcie_peaks(job)
 
-    if rank != 0:
-        relay.close()
-        if world > 1:
-            dist.destroy_process_group()
+    # ---------------- sub-lines: the other single-kernel claims, measured in this same run ----------
+    subs = {}
+    for sub in ([] if args.sub in ("", "none") else args.sub.split(",")):
+        if sub == name:
+            continue
+        r, _ = measure_device(job, sub, SUB_STEPS.get(sub, 32), max(3, min(W, 8)), args.no_graph)
+        r["config"] = make_config(sub, job.n_gpus, r["steps"], args.no_graph, plan_mode_for(sub))
+        subs[sub] = r
+
+    if job.rank != 0:
+        job.close()
         return
 
     # ---------------- CPU baseline on this box's host cores (rank 0, N=1) -----
     cpu = None
-    if world == 1 and not args.no_cpu:
+    if job.world == 1 and not args.no_cpu:
         threads = host_threads()
-        probe, kind = cpu_run(lens, 2, 0, threads)
-        per_step_cpu_s = probe / 2 * threads           # CPU-seconds of work per step
+        probe, kind = cpu_run(lens, 4, 2, threads)
+        per_step_cpu_s = probe / 4 * threads           # CPU-seconds of work per step
         cpu_steps = int(min(max(4, 15.0 / max(per_step_cpu_s, 1e-9)), 200000))
         sec, kind = cpu_run(lens, cpu_steps, max(1, cpu_steps // 20), threads)
         sec1, _ = cpu_run(lens, max(1, cpu_steps // threads), 1, 1)
@@ -531,75 +703,50 @@ def run_ours(args):
 
     # ---------------- p50 added relay latency (the metric's third figure), rank 0 at N=1 ----------
     latency = None
-    if world == 1 and not args.no_latency:
+    if job.world == 1 and not args.no_latency:
         try:
             sys.path.insert(0, os.path.join(ROOT, "tools"))
             import latency_bench
 
-            relay.close()
-            relay = None
             latency = latency_bench.run(streams=65536, rate=2e6, nbytes=200, seconds=1.0, flush_us=100)
         except Exception as e:  # the headline numbers do not depend on it
             latency = {"error": repr(e)}
 
-    frames_per_step = n                                  # sealed frames; each step also opens n frames
-    dev_s = dev_ms * 1e-3
-    value = n_gpus * frames_per_step * K / dev_s
-    alg_bytes = algorithmic_bytes(lens) * 2              # seal + open
-    ops = int_ops(lens) * 2
-    hbm_peak, hbm_src = hbm_peak_gbs()
-    per_launch_ms = dev_ms / K
-    achieved_gbs = alg_bytes / (per_launch_ms * 1e-3) / 1e9
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        try:
-            traffic = json.load(open(tpath)).get(args.workload)
-        except Exception:
-            traffic = None
+    h2d = lay.in_bytes + 2 * n * 16 + x["n_tiles_full"] * 8
+    d2h = lay.out_bytes + 2 * n * 4
+    e2e_ms = (e2e_sec / K2 * 1e3) if K2 else None
+    e2e = {"value": (job.n_gpus * n * K2 / e2e_sec) if K2 else None, "unit": "frames/s",
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": K2, "ms_per_step": e2e_ms,
+           "path": "symrelay_batch_submit/wait on pinned host arenas, pipeline depth " + str(D_E2E) +
+                   ", host clock; loop driver: " + e2e_driver}
+    if K2:
+        # PCIe is full duplex: the bound for a step is the slower direction at that direction's measured peak
+        t_bound = max(h2d / (h2d_peak * 1e9), d2h / (d2h_peak * 1e9))
+        e2e["roofline"] = {"bound": "pcie", "achieved": (h2d + d2h) / (e2e_ms * 1e-3) / 1e9, "unit": "GB/s",
+                           "peak": (h2d + d2h) / t_bound / 1e9, "frac": t_bound / (e2e_ms * 1e-3),
+                           "h2d_peak_gbs": h2d_peak, "d2h_peak_gbs": d2h_peak,
+                           "peak_source": "pinned 64 MiB cudaMemcpyAsync each way, measured in this run; peak = both "
+                                          "directions' bytes over the slower direction's time at its peak (full duplex)"}
+    if batch_lat:
+        e2e["batch_latency"] = batch_lat
     line = {
-        "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": n_gpus, "steps": K, "warmup": W,
-        "ms_per_step": per_launch_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+        "metric": METRIC, "value": res["value"], "unit": "frames/s", "n_gpus": job.n_gpus, "steps": K, "warmup": W,
+        "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
         "dtype": "u32", "data": "synthetic",
-        "config": {"workload": desc, "streams_per_gpu": n, "plan": ("symrelay_plan_sorted (library groups the frames by size class)" if plan_mode == "sorted" else "symrelay_plan (caller's descriptor order)"), "frames_per_step_per_gpu": 2 * n,
-                   "plaintext_bytes_per_step_per_gpu": int(sum(lens)),
-                   "l2": f"inputs larger than L2: ring of {R} distinct batch slots, {R * lay.slot_bytes >> 20} MiB, "
-                         f"visited round-robin; L2 flushed once before timing",
-                   "step": "every stream seals one frame and opens one frame (mixed batch)",
-                   "launch": ("direct launches" if args.no_graph else
-                              f"{n_replays} replays of a CUDA graph holding {R} steps + one graph of the last {n_rem} steps, "
-                              "each replayed once untimed first (graph upload)")},
-        "gb_per_s": n_gpus * float(sum(lens)) * K / dev_s / 1e9,
-        "opened_frames_per_sec": value,
-        "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved_gbs / hbm_peak, "traffic": traffic,
-                     "peak_source": hbm_src,
-                     "kernel": "ss_packed_kernel" if nb_full == 0 else "ss_bulk_kernel",
-                     "algorithmic_bytes_per_launch": alg_bytes,
-                     "note": "the path is integer-ALU bound (SURVEY 8(d)); see alu_roofline"},
-        "alu_roofline": {"bound": "int_alu", "achieved": ops / (per_launch_ms * 1e-3) / 1e12,
-                         "peak": arx_tops, "unit": "Tint-op/s", "frac": ops / (per_launch_ms * 1e-3) / 1e12 / arx_tops,
-                         "int_ops_per_launch": ops, "peak_source": "symrelay_probe_int_peak (ChaCha ARX mix, measured now)",
-                         "imad_wide_tops": imad_tops},
-        "e2e": {"value": (n_gpus * frames_per_step * K2 / e2e_sec) if K2 else None, "unit": "frames/s",
-                "h2d_bytes_per_step": lay.in_bytes + 2 * n * 16 + len(tiles_full) * 8,
-                "d2h_bytes_per_step": lay.out_bytes + 2 * n * 4, "steps": K2,
-                "ms_per_step": (e2e_sec / K2 * 1e3) if K2 else None,
-                "path": "symrelay_batch_submit/wait on pinned host arenas, pipeline depth " + str(D_E2E) + ", host clock; loop driver: " + e2e_driver},
-        "gpu_launches": int(gpu_launches),
-        "launches_per_step": launches_per_step,
-        "clocks": clk,
-        "parity": "timed run spot-checked against libsodium: tx/rx chains, last wire frames, recovered plaintext",
+        "config": make_config(name, job.n_gpus, K, args.no_graph, x["plan_mode"]),
+        "gb_per_s": res["gb_per_s"], "opened_frames_per_sec": res["value"],
+        "roofline": res["roofline"], "alu_roofline": res["alu_roofline"], "e2e": e2e,
+        "gpu_launches": res["gpu_launches"], "launches_per_step": res["launches_per_step"],
+        "clocks": clk, "parity": res["parity"],
     }
+    for k, v in subs.items():
+        line[k] = v
     if cpu:
         line["cpu_baseline"] = cpu
     if latency:
         line["latency"] = latency
     print(json.dumps(line), flush=True)
-    if relay is not None:
-        relay.close()
-    if world > 1:
-        dist.destroy_process_group()
+    job.close()
 
 
 def hbm_peak_gbs():
@@ -749,6 +896,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=200)
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sub", default=None, help="sub-lines carried by the default (c2) line: 'c4,c3' (default) or 'none'")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-latency", action="store_true", help="skip the p50 added-latency leg (64k streams, Poisson)")
@@ -757,13 +905,23 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every step directly (no CUDA graph)")
     args = ap.parse_args()
     if args.steps is None:   # a step of c3/c4/c5 is 10-400x a step of c2
-        args.steps = {"c2": 20000, "c3": 200, "c4": 64, "c5": 360}.get(args.workload, 20000)
+        args.steps = DEFAULT_STEPS.get(args.workload, 20000)
+    if args.sub is None:
+        args.sub = "c4,c3" if args.workload == "c2" else "none"
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "c5":
         run_c5(args)
+    elif args.workload == "c1":
+        import bench_extra
+
+        bench_extra.run_c1(args)
+    elif args.workload == "c4sweep":
+        import bench_extra
+
+        bench_extra.run_c4_sweep(args)
     else:
         run_ours(args)
 

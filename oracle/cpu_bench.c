@@ -54,21 +54,18 @@ typedef struct {
     uint8_t *wire;          /* step s, stream i at wire + (s % ring) * wire_step + wire_off[i]; len+20 bytes */
     const uint64_t *wire_off;
     uint64_t wire_step;
-    uint32_t ring, steps;
+    uint32_t ring, steps, warmup;
     int do_seal, do_open;
     int threads;
     volatile int failures;
+    pthread_barrier_t start, stop;
 } cpub_job;
 
 typedef struct { cpub_job *job; int tid; } cpub_arg;
 
-static void *worker(void *p) {
-    cpub_arg *a = (cpub_arg *)p;
-    cpub_job *j = a->job;
-    uint32_t lo = (uint32_t)((uint64_t)j->n_streams * a->tid / j->threads);
-    uint32_t hi = (uint32_t)((uint64_t)j->n_streams * (a->tid + 1) / j->threads);
+static int run_steps(cpub_job *j, uint32_t lo, uint32_t hi, uint32_t first, uint32_t count) {
     int bad = 0;
-    for (uint32_t s = 0; s < j->steps; s++) {
+    for (uint32_t s = first; s < first + count; s++) {
         uint64_t po = (uint64_t)(s % j->ring) * j->plain_step, wo = (uint64_t)(s % j->ring) * j->wire_step;
         for (uint32_t i = lo; i < hi; i++) {
             uint32_t len = j->lens[i];
@@ -87,31 +84,81 @@ static void *worker(void *p) {
             }
         }
     }
+    return bad;
+}
+
+/* The pool is up, has run the warm-up steps on its own streams (caches, branch predictors and the
+ * chains are warm) and meets the timing thread at a barrier on both sides of the timed steps: thread
+ * start-up is set-up, not relay work, and must not be inside a region that may only last a millisecond. */
+static void *worker(void *p) {
+    cpub_arg *a = (cpub_arg *)p;
+    cpub_job *j = a->job;
+    uint32_t lo = (uint32_t)((uint64_t)j->n_streams * a->tid / j->threads);
+    uint32_t hi = (uint32_t)((uint64_t)j->n_streams * (a->tid + 1) / j->threads);
+    int bad = run_steps(j, lo, hi, 0, j->warmup);
+    pthread_barrier_wait(&j->start);
+    bad |= run_steps(j, lo, hi, j->warmup, j->steps);
+    pthread_barrier_wait(&j->stop);
     if (bad) j->failures = 1;
     return NULL;
 }
 
-/* Returns elapsed seconds (wall, CLOCK_MONOTONIC) for `steps` passes; <0 on failure. */
+/* Returns elapsed seconds (wall, CLOCK_MONOTONIC) for `steps` passes after `warmup` untimed passes on
+ * the same threads; <0 on failure. */
 double cpub_run(void *push, void *pull, uint8_t *tx_states, uint8_t *rx_states, uint32_t n_streams,
                 const uint8_t *plain, const uint64_t *plain_off, const uint32_t *lens, uint64_t plain_step,
                 uint8_t *wire, const uint64_t *wire_off, uint64_t wire_step, uint32_t ring, uint32_t steps,
-                int do_seal, int do_open, int threads) {
-    cpub_job job = {(push_fn)push, (pull_fn)pull, tx_states, rx_states, n_streams, plain, plain_off, lens,
-                    plain_step, wire, wire_off, wire_step, ring ? ring : 1, steps, do_seal, do_open,
-                    threads < 1 ? 1 : threads, 0};
+                uint32_t warmup, int do_seal, int do_open, int threads) {
+    cpub_job job;
+    memset(&job, 0, sizeof job);
+    job.push = (push_fn)push; job.pull = (pull_fn)pull; job.tx_states = tx_states; job.rx_states = rx_states;
+    job.n_streams = n_streams; job.plain = plain; job.plain_off = plain_off; job.lens = lens;
+    job.plain_step = plain_step; job.wire = wire; job.wire_off = wire_off; job.wire_step = wire_step;
+    job.ring = ring ? ring : 1; job.steps = steps; job.warmup = warmup; job.do_seal = do_seal; job.do_open = do_open;
+    job.threads = threads < 1 ? 1 : threads;
     if ((uint32_t)job.threads > n_streams) job.threads = (int)n_streams;
     if (job.threads < 1) job.threads = 1;
+    pthread_barrier_init(&job.start, NULL, (unsigned)job.threads + 1u);
+    pthread_barrier_init(&job.stop, NULL, (unsigned)job.threads + 1u);
     pthread_t *th = (pthread_t *)calloc((size_t)job.threads, sizeof *th);
     cpub_arg *args = (cpub_arg *)calloc((size_t)job.threads, sizeof *args);
-    struct timespec t0, t1;
-    clock_gettime(CLOCK_MONOTONIC, &t0);
     for (int t = 0; t < job.threads; t++) {
         args[t].job = &job; args[t].tid = t;
         pthread_create(&th[t], NULL, worker, &args[t]);
     }
-    for (int t = 0; t < job.threads; t++) pthread_join(th[t], NULL);
+    struct timespec t0, t1;
+    pthread_barrier_wait(&job.start);
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    pthread_barrier_wait(&job.stop);
     clock_gettime(CLOCK_MONOTONIC, &t1);
+    for (int t = 0; t < job.threads; t++) pthread_join(th[t], NULL);
+    pthread_barrier_destroy(&job.start);
+    pthread_barrier_destroy(&job.stop);
     free(th); free(args);
     if (job.failures) return -1.0;
+    return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+}
+
+/* BASELINE config 1 on one core: ONE connection, its frames pushed (secret-stream `_write`) and pulled
+ * (`_incoming`) strictly in sequence, `reps` passes over the n chunks in `blob` (offsets off[0..n]).
+ * scratch must hold the longest chunk + 20 bytes.  Returns seconds, <0 on a failed pull. */
+double cpub_chain_run(void *push_p, void *pull_p, uint8_t *tx_state, uint8_t *rx_state, const uint8_t *blob,
+                      const uint32_t *off, uint32_t n, uint32_t reps, uint8_t *scratch) {
+    push_fn push = (push_fn)push_p;
+    pull_fn pull = (pull_fn)pull_p;
+    int bad = 0;
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (uint32_t r = 0; r < reps; r++)
+        for (uint32_t i = 0; i < n; i++) {
+            const uint32_t len = off[i + 1] - off[i], m = len + 17;
+            unsigned char tag;
+            memcpy(scratch + 4, blob + off[i], len);
+            scratch[0] = (uint8_t)m; scratch[1] = (uint8_t)(m >> 8); scratch[2] = (uint8_t)(m >> 16);
+            bad |= push(tx_state, scratch + 3, NULL, scratch + 4, len, NULL, 0, 0);
+            bad |= pull(rx_state, scratch + 4, NULL, &tag, scratch + 3, (unsigned long long)len + 17, NULL, 0);
+        }
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    if (bad) return -1.0;
     return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
 }

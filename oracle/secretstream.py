@@ -52,7 +52,10 @@ def lib() -> C.CDLL:
         L.ssref_open_frame.restype = C.c_int
         L.cpub_run.restype = C.c_double
         L.cpub_run.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, u32, C.c_void_p, C.c_void_p,
-                               C.c_void_p, u64, C.c_void_p, C.c_void_p, u64, u32, u32, C.c_int, C.c_int, C.c_int]
+                               C.c_void_p, u64, C.c_void_p, C.c_void_p, u64, u32, u32, u32, C.c_int, C.c_int, C.c_int]
+        L.cpub_chain_run.restype = C.c_double
+        L.cpub_chain_run.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, u32, u32,
+                                     C.c_void_p]
         _lib = L
     return _lib
 

@@ -53,3 +53,59 @@ double e2e_ring_run(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, ui
     free(tickets);
     return t1 - t0;
 }
+
+/* Per-batch latency of the synchronous call: `steps` consecutive symrelay_batch_host calls on the same ring and
+ * the same chains, one batch in flight; lat_ns[i] = wall time of call i (host arenas in -> results visible to the
+ * host).  SURVEY.md 8(d), C2: "batch latency (p50/p99)".  Same argument meaning as e2e_ring_run. */
+static uint64_t now_ns(void) {
+    struct timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return (uint64_t)t.tv_sec * 1000000000ull + (uint64_t)t.tv_nsec;
+}
+
+int e2e_sync_latency(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, uint8_t *ring_base, uint64_t slot_bytes,
+                     uint64_t in_bytes, uint64_t out_off, uint64_t out_bytes, uint32_t ring, uint32_t depth,
+                     uint64_t first_step, uint32_t steps, uint32_t *status /* ring x n */, uint64_t *lat_ns) {
+    for (uint64_t i = first_step; i < first_step + steps; i++) {
+        const uint64_t a = now_ns();
+        const int rc = symrelay_batch_host(ctx, desc, n, ring_base + (i % ring) * slot_bytes, in_bytes,
+                                           ring_base + ((i + depth) % ring) * slot_bytes + out_off, out_bytes,
+                                           status + (size_t)(i % ring) * n, NULL, NULL, 0);
+        if (rc) return rc;
+        lat_ns[i - first_step] = now_ns() - a;
+    }
+    return 0;
+}
+
+/* BASELINE config 1 restated for the library: ONE connection, its frames strictly in
+ * sequence through the per-frame ABI exactly as the relay loop issues them (src/provider.ts:234-262):
+ * symrelay_submit_seal(chunk[, F_EXTRACT]) -> flush -> wait for its completion -> release, then the next chunk.
+ * chunks are concatenated in `blob` with offsets off[0..n]; extract[i] != 0 marks the body chunks.
+ * Returns seconds for `reps` passes over the n chunks, or a negative SYMRELAY_E* code; *n_deltas counts delta bytes. */
+double c1_run(symrelay_ctx *ctx, uint32_t slot, const uint8_t *blob, const uint32_t *off, const uint8_t *extract,
+              uint32_t n, uint32_t reps, uint64_t *delta_bytes) {
+    symrelay_completion c[4];
+    uint64_t db = 0;
+    const double t0 = now();
+    for (uint32_t r = 0; r < reps; r++)
+        for (uint32_t i = 0; i < n; i++) {
+            const int64_t t = symrelay_submit_seal(ctx, slot, blob + off[i], off[i + 1] - off[i],
+                                                   extract[i] ? SYMRELAY_F_EXTRACT : 0u);
+            if (t < 0) return (double)t;
+            int rc = symrelay_flush(ctx);
+            if (rc) return (double)rc;
+            int k = 0;
+            while (k == 0) {
+                k = symrelay_poll_wait(ctx, c, 4);
+                if (k < 0) return (double)k;
+            }
+            if (k != 1 || c[0].ticket != t) return (double)SYMRELAY_EINVAL;
+            const uint32_t code = SYMRELAY_STATUS_CODE(c[0].status);
+            if (code != SYMRELAY_ST_OK) return -(double)(2000 + code);
+            db += c[0].delta_len;
+            symrelay_release(ctx, t);
+        }
+    const double t1 = now();
+    if (delta_bytes) *delta_bytes = db;
+    return t1 - t0;
+}
