@@ -58,7 +58,8 @@ typedef struct {
     int do_seal, do_open;
     int threads;
     volatile int failures;
-    pthread_barrier_t start, stop;
+    int arrived;             /* workers that finished their warm-up */
+    double *t_start, *t_end; /* per worker */
 } cpub_job;
 
 typedef struct { cpub_job *job; int tid; } cpub_arg;
@@ -88,17 +89,26 @@ static int run_steps(cpub_job *j, uint32_t lo, uint32_t hi, uint32_t first, uint
 }
 
 /* The pool is up, has run the warm-up steps on its own streams (caches, branch predictors and the
- * chains are warm) and meets the timing thread at a barrier on both sides of the timed steps: thread
- * start-up is set-up, not relay work, and must not be inside a region that may only last a millisecond. */
+ * chains are warm) and lines up at a spinning barrier before the timed steps: thread start-up and
+ * futex wake-ups are set-up, not relay work, and must not be inside a region that may only last a
+ * millisecond.  Every worker stamps its own start and end; the job's time is last end - first start. */
+static double mono_now(void) {
+    struct timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec;
+}
+
 static void *worker(void *p) {
     cpub_arg *a = (cpub_arg *)p;
     cpub_job *j = a->job;
     uint32_t lo = (uint32_t)((uint64_t)j->n_streams * a->tid / j->threads);
     uint32_t hi = (uint32_t)((uint64_t)j->n_streams * (a->tid + 1) / j->threads);
     int bad = run_steps(j, lo, hi, 0, j->warmup);
-    pthread_barrier_wait(&j->start);
+    __atomic_add_fetch(&j->arrived, 1, __ATOMIC_SEQ_CST);
+    while (__atomic_load_n(&j->arrived, __ATOMIC_ACQUIRE) < j->threads) __builtin_ia32_pause();
+    j->t_start[a->tid] = mono_now();
     bad |= run_steps(j, lo, hi, j->warmup, j->steps);
-    pthread_barrier_wait(&j->stop);
+    j->t_end[a->tid] = mono_now();
     if (bad) j->failures = 1;
     return NULL;
 }
@@ -118,25 +128,23 @@ double cpub_run(void *push, void *pull, uint8_t *tx_states, uint8_t *rx_states, 
     job.threads = threads < 1 ? 1 : threads;
     if ((uint32_t)job.threads > n_streams) job.threads = (int)n_streams;
     if (job.threads < 1) job.threads = 1;
-    pthread_barrier_init(&job.start, NULL, (unsigned)job.threads + 1u);
-    pthread_barrier_init(&job.stop, NULL, (unsigned)job.threads + 1u);
     pthread_t *th = (pthread_t *)calloc((size_t)job.threads, sizeof *th);
     cpub_arg *args = (cpub_arg *)calloc((size_t)job.threads, sizeof *args);
+    job.t_start = (double *)calloc((size_t)job.threads, sizeof(double));
+    job.t_end = (double *)calloc((size_t)job.threads, sizeof(double));
     for (int t = 0; t < job.threads; t++) {
         args[t].job = &job; args[t].tid = t;
         pthread_create(&th[t], NULL, worker, &args[t]);
     }
-    struct timespec t0, t1;
-    pthread_barrier_wait(&job.start);
-    clock_gettime(CLOCK_MONOTONIC, &t0);
-    pthread_barrier_wait(&job.stop);
-    clock_gettime(CLOCK_MONOTONIC, &t1);
-    for (int t = 0; t < job.threads; t++) pthread_join(th[t], NULL);
-    pthread_barrier_destroy(&job.start);
-    pthread_barrier_destroy(&job.stop);
-    free(th); free(args);
+    for (int t = 0; t < job.threads; t++) pthread_join(th[t], NULL);   /* the caller sleeps: every core belongs to a worker */
+    double first = job.t_start[0], last = job.t_end[0];
+    for (int t = 1; t < job.threads; t++) {
+        if (job.t_start[t] < first) first = job.t_start[t];
+        if (job.t_end[t] > last) last = job.t_end[t];
+    }
+    free(th); free(args); free(job.t_start); free(job.t_end);
     if (job.failures) return -1.0;
-    return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+    return last - first;
 }
 
 /* BASELINE config 1 on one core: ONE connection, its frames pushed (secret-stream `_write`) and pulled
