@@ -561,7 +561,7 @@ def run_ours(args):
     torch = job.torch
     name = args.workload
     K, W = args.steps, args.warmup
-    D_E2E = int(os.environ.get("BENCH_E2E_DEPTH", "6"))
+    D_E2E = int(os.environ.get("BENCH_E2E_DEPTH", "12"))
     lens, desc, scaling, first = workload(name, job.n_gpus, job.rank)
     n = len(lens)
     lay0 = Layout(lens)
@@ -647,7 +647,7 @@ def run_ours(args):
     for j in sorted({i % R2 for i in range(max(0, i2 - K2), i2)} if K2 else set()):
         assert (hstat[j] == 0).all(), "non-OK status in the e2e run"
     # per-batch latency of the synchronous call over a 1,000-deep chain ("batch latency p50/p99")
-    if K2 and not args.py_e2e and job.rank == 0 and name == "c2":
+    if K2 and not args.py_e2e and job.rank == 0 and name == "c2" and os.environ.get("BENCH_SYNC_LAT", "1") != "0":
         drv.e2e_sync_latency.restype = C.c_int
         drv.e2e_sync_latency.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64,
                                          C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]

@@ -44,6 +44,9 @@ struct symrelay_plan_check {
     uint32_t out_of_bounds;   // some frame leaves its arena or names a slot >= max_streams
     uint32_t any_flags;       // OR of all len_flags
     uint32_t out_overlap;     // output rows (16 B) not strictly increasing in descriptor order
+    // set by symrelay_plan_inline when every frame has one block count and the tiles follow in closed form:
+    // `uniform_thread` thread-per-frame tiles of 32 frames, then packed tiles of `uniform_per` frames (0: not uniform)
+    uint32_t uniform_per, uniform_thread;
 };
 
 // Pass 1 of the planner.  No loop-carried dependency and all 32-bit (offsets are uint32 and arenas are
@@ -104,7 +107,7 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
     symrelay_plan_scan(desc, n, nc, row_lo, row_hi, (uint32_t)(chk && chk->in_bytes < cap ? chk->in_bytes : cap),
                        (uint32_t)(chk && chk->out_bytes < cap ? chk->out_bytes : cap), chk ? chk->max_streams : 0xffffffffu, scan);
     const uint32_t bad = scan[0], oob = scan[1], any_flags = scan[2], nc_min = scan[3], nc_max = scan[4];
-    if (chk) { chk->out_of_bounds = oob; chk->any_flags = any_flags; chk->out_overlap = scan[5]; }
+    if (chk) { chk->out_of_bounds = oob; chk->any_flags = any_flags; chk->out_overlap = scan[5]; chk->uniform_per = chk->uniform_thread = 0; }
     if (bad) return SYMRELAY_EINVAL;
     uint64_t n_tiles = 0;
     uint32_t n_bulk = 0;
@@ -126,6 +129,7 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
             n_tiles++;
         }
         if (n_bulk_out) *n_bulk_out = 0;
+        if (chk) { chk->uniform_per = per; chk->uniform_thread = thread_ok ? n / 32u : 0u; }
         return (int64_t)n_tiles;
     }
     uint32_t run_first = 0, run_n = 0, run_blocks = 0;

@@ -71,9 +71,63 @@ SS_DEV void ss_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dep
 SS_DEV void ss_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 #endif
 
+// Loads for the persistent kernel (VOL = true).  A resident grid re-reads the same host addresses batch after
+// batch (the caller's arena ring, the control blocks) and the same stream states that other SMs have advanced in
+// between; plain loads may be served from a stale L1/L2 line, which never happens to a kernel that is launched
+// per batch.  ld.volatile fetches from the point of coherence every time.  Generic addressing: the payload
+// pointer may also be the staged copy in shared memory.
+#ifdef SS_HOST_EMU
+template <bool VOL> static inline uint4 ss_ld16(const void *p) { return *reinterpret_cast<const uint4 *>(p); }
+template <bool VOL> static inline uint32_t ss_ld4(const void *p) { return *reinterpret_cast<const uint32_t *>(p); }
+template <bool VOL> static inline uint32_t ss_ld1(const void *p) { return *reinterpret_cast<const uint8_t *>(p); }
+static inline void ss_dep_wait(const uint32_t *, uint32_t) {}
+static inline uint32_t ss_ld_acquire_u32(const uint32_t *p) { return *p; }
+static inline void ss_st_release_u32(uint32_t *p, uint32_t v) { *p = v; }
+static inline void ss_nanosleep(uint32_t) {}
+#else
+SS_DEV uint32_t ss_ld_acquire_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+SS_DEV void ss_st_release_u32(uint32_t *p, uint32_t v) { asm volatile("st.release.gpu.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+SS_DEV void ss_nanosleep(uint32_t ns) { __nanosleep(ns); }
+template <bool VOL> SS_DEV uint4 ss_ld16(const void *p) {
+    if (!VOL) return *reinterpret_cast<const uint4 *>(p);
+    uint4 v;
+    asm volatile("ld.volatile.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+template <bool VOL> SS_DEV uint32_t ss_ld4(const void *p) {
+    if (!VOL) return *reinterpret_cast<const uint32_t *>(p);
+    uint32_t v;
+    asm volatile("ld.volatile.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+template <bool VOL> SS_DEV uint32_t ss_ld1(const void *p) {
+    if (!VOL) return *reinterpret_cast<const uint8_t *>(p);
+    uint32_t v;
+    asm volatile("ld.volatile.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Persistent kernel: batch b may touch the stream states only after batch b-1 has left them (the MAC chain).
+// *seq counts completed batches (device memory, released by the last warp of a batch).
+SS_DEV void ss_dep_wait(const uint32_t *seq, uint32_t need) {
+    if (!seq) return;
+    uint32_t v;
+    for (;;) {
+        asm volatile("ld.acquire.gpu.u32 %0, [%1];" : "=r"(v) : "l"(seq) : "memory");
+        if ((int32_t)(v - need) >= 0) break;
+        __nanosleep(40);
+    }
+}
+#endif
+
 #define SS_ARG_INPUT_INDEPENDENT 1u  // SsArgs.flags: desc/tiles/in were not written by the preceding kernel
 #define SS_ARG_STAGE_INPUT 2u        // SsArgs.flags: pull each packed tile's input through shared memory
 #define SS_ARG_STAGE_OUTPUT 4u       // SsArgs.flags: assemble each packed tile's output in shared memory, store whole lines
+#define SS_ARG_CHAIN 8u              // SsArgs.flags: resident kernel -- hand the stream states over through their stamps
+#define SS_ARG_CHAIN_UNIFORM 16u     // ... and every frame expects the stamp ver_all (no per-descriptor array)
 
 #define SS_F_OPEN 0x04000000u
 #define SS_F_EXTRACT 0x08000000u
@@ -108,15 +162,34 @@ struct SsArgs {
     const uint32_t *wb_status_src = nullptr;
     uint32_t *wb_status_dst = nullptr;
     uint32_t wb_n_status = 0;
+    unsigned long long *dbg_max = nullptr;  // SYMRELAY_TS=1, resident kernel: per batch, max over tiles of the four stamps
     unsigned long long *dbg_ts = nullptr;   // SYMRELAY_TS=1 (diagnostics): {kernel start, past the dependency wait, end} of warp 0
+    // Persistent kernel only: wait until *dep_seq >= dep_need before touching the stream states.
+    const uint32_t *dep_seq = nullptr;
+    uint32_t dep_need = 0;
+    // Resident kernel only: per-stream hand-over of the MAC chain between batches.  The upper 24 bits of a state's
+    // meta word carry the stamp of the last resident-kernel batch that went through that (slot, direction);
+    // ver[i] is the stamp descriptor i has to find there before it may read the state (0: no predecessor in
+    // flight), new_ver the stamp this batch leaves.  Release/acquire on that one word orders the nonce and key
+    // words written before it -- a frame waits for exactly its predecessor, not for a whole batch.
+    const uint32_t *ver = nullptr;
+    uint32_t new_ver = 0;
+    SsDesc *desc_fill = nullptr;   // resident kernel: also leave a copy of the tile's descriptors here (device memory), for the
+                                   // next batch that repeats them -- it then reads them from HBM instead of over PCIe
+    uint32_t ver_all = 0;     // SS_ARG_CHAIN_UNIFORM: every descriptor expects this stamp (the batch repeats its predecessor's streams)
 };
 
 SS_DEV void ss_dbg_stamp(const SsArgs &a, uint32_t tile_idx, uint32_t lane, uint32_t which) {
 #ifndef SS_HOST_EMU
-    if (a.dbg_ts && tile_idx == 0 && lane == 0) {
+    if (a.dbg_ts && tile_idx == 0 && lane == 0 && which < 4u) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         a.dbg_ts[which] = t;
+    }
+    if (a.dbg_max && lane == 0) {   // resident kernel: the latest tile of the batch to reach each point
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMax(a.dbg_max + which, t);
     }
 #endif
 }
@@ -324,13 +397,13 @@ void ss_rekey(uint32_t k[8], uint32_t nn[3]) {
 
 // ------------------------------------------------------- payload load/store --
 // Loads up to 64 bytes (16-byte pieces that start below nbytes) from a 16-aligned address.
-template <bool FULL_FAST = false>
+template <bool FULL_FAST = false, bool VOL = false>
 SS_DEV void ss_load64(const uint8_t *p, int nbytes, uint32_t m[16]) {
     const uint4 *q = reinterpret_cast<const uint4 *>(p);
     if (FULL_FAST && nbytes == 64) {    // full block: four unconditional vector loads
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const uint4 v = q[i];
+            const uint4 v = ss_ld16<VOL>(q + i);
             m[4 * i] = v.x; m[4 * i + 1] = v.y; m[4 * i + 2] = v.z; m[4 * i + 3] = v.w;
         }
         return;
@@ -339,7 +412,7 @@ SS_DEV void ss_load64(const uint8_t *p, int nbytes, uint32_t m[16]) {
     for (int i = 0; i < 4; i++) {
         uint4 v;
         v.x = v.y = v.z = v.w = 0;
-        if (16 * i < nbytes) v = q[i];
+        if (16 * i < nbytes) v = ss_ld16<VOL>(q + i);
         m[4 * i] = v.x; m[4 * i + 1] = v.y; m[4 * i + 2] = v.z; m[4 * i + 3] = v.w;
     }
 }
@@ -392,14 +465,15 @@ SS_DEV void ss_store_mac(uint8_t *p, const uint32_t mac[4]) {
 }
 
 // The 16 tag bytes of a wire frame (any alignment) as four little-endian words.
+template <bool VOL = false>
 SS_DEV void ss_load_mac(const uint8_t *p, uint32_t w[4]) {
     if ((reinterpret_cast<uintptr_t>(p) & 3u) == 0) {
         const uint32_t *q = reinterpret_cast<const uint32_t *>(p);
-        w[0] = q[0]; w[1] = q[1]; w[2] = q[2]; w[3] = q[3];
+        w[0] = ss_ld4<VOL>(q); w[1] = ss_ld4<VOL>(q + 1); w[2] = ss_ld4<VOL>(q + 2); w[3] = ss_ld4<VOL>(q + 3);
     } else {
         w[0] = w[1] = w[2] = w[3] = 0;
 #pragma unroll
-        for (int j = 0; j < 16; j++) w[j >> 2] |= (uint32_t)p[j] << (8 * (j & 3));
+        for (int j = 0; j < 16; j++) w[j >> 2] |= ss_ld1<VOL>(p + j) << (8 * (j & 3));
     }
 }
 
@@ -408,7 +482,7 @@ SS_DEV void ss_load_mac(const uint8_t *p, uint32_t w[4]) {
 // the warp, one pass.  BULK == true: one frame of any size, lanes stride by 32.
 // `given`: the tile itself when the launch carried the tile list in its parameters (small host batches:
 // one dependent read over PCIe fewer), else it is read from a.tiles.
-template <bool BULK>
+template <bool BULK, bool VOL = false>
 SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_dbg_stamp(a, tile_idx, lane, 0);
@@ -418,11 +492,13 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     const uint32_t nfr = BULK ? 1u : (tile.n_kind & 0xffffu);
 
     // ---- lane -> (frame f, first lane st of that frame) ---------------------
-    uint32_t d_slot = 0, d_in = 0, d_out = 0, d_lf = 0, my_nc = 0, d_skip = 0;
+    uint32_t d_slot = 0, d_in = 0, d_out = 0, d_lf = 0, my_nc = 0, d_skip = 0, d_ver = 0;
     if (lane < nfr) {
-        const SsDesc d = a.desc[tile.first + lane];
-        d_slot = d.slot; d_in = d.in_off; d_out = d.out_off; d_lf = d.len_flags;
+        const uint4 d = ss_ld16<VOL>(a.desc + tile.first + lane);
+        d_slot = d.x; d_in = d.y; d_out = d.z; d_lf = d.w;
         my_nc = 2u + (((d_lf & 0xffffffu) + 63u) >> 6);
+        if (a.desc_fill) *reinterpret_cast<uint4 *>(a.desc_fill + tile.first + lane) = d;
+        if (a.flags & SS_ARG_CHAIN) d_ver = (a.flags & SS_ARG_CHAIN_UNIFORM) ? a.ver_all : a.ver[tile.first + lane];
     }
     uint32_t f = 0, st = 0, my_start = 0;
     bool valid = true;
@@ -445,6 +521,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     const uint32_t in_off = ss_shfl(d_in, f);
     const uint32_t out_off = ss_shfl(d_out, f);
     const uint32_t lf = ss_shfl(d_lf, f);
+    const uint32_t exp_ver = (a.flags & SS_ARG_CHAIN) ? ss_shfl(d_ver, f) : 0u;
 
     const uint32_t mlen = lf & 0xffffffu;
     const bool is_open = (lf & SS_F_OPEN) != 0;
@@ -483,7 +560,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
 #pragma unroll
             for (uint32_t i = 0; i < SS_STAGE_BYTES / 512u; i++) {
                 const uint32_t p = lane + 32u * i;
-                if (p < pieces) stage[p] = g[p];
+                if (p < pieces) stage[p] = ss_ld16<VOL>(g + p);
             }
             ss_syncwarp();
             in_base = reinterpret_cast<const uint8_t *>(stage) - w_lo;
@@ -491,12 +568,23 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
         }
     }
     if (early) {
-        ss_load64(src + 64u * (size_t)(pre_payload ? b_first - 2u : 0u), pre_cbytes, m);
-        if (valid && is_open && b_first == 1u) hw = *reinterpret_cast<const uint32_t *>(in_base + in_off);
-        if (valid && is_open && b_first == 0u) ss_load_mac(src + mlen, wmac);
+        ss_load64<false, VOL>(src + 64u * (size_t)(pre_payload ? b_first - 2u : 0u), pre_cbytes, m);
+        if (valid && is_open && b_first == 1u) hw = ss_ld4<VOL>(in_base + in_off);
+        if (valid && is_open && b_first == 0u) ss_load_mac<VOL>(src + mlen, wmac);
     }
     ss_dbg_stamp(a, tile_idx, lane, 1);
     ss_pdl_wait();   // from here on we touch what the previous kernel may have written
+    ss_dep_wait(a.dep_seq, a.dep_need);   // (batch-level dependency; unused when a.ver is set)
+    if (a.flags & SS_ARG_CHAIN) {
+        // resident kernel: every lane waits until its frame's predecessor has left the state (warp-uniform loop)
+        const uint32_t *vp = reinterpret_cast<const uint32_t *>(sp + 2) + 3;
+        bool ready = !valid || exp_ver == 0u;
+        for (;;) {
+            if (!ready) ready = (ss_ld_acquire_u32(vp) >> 8) == exp_ver;
+            if (!ss_any(!ready)) break;
+            ss_nanosleep(40);
+        }
+    }
     ss_dbg_stamp(a, tile_idx, lane, 2);
     if (!BULK) ss_write_back(a, tile_idx, a.n_tiles, lane);
 
@@ -517,7 +605,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     {
         uint4 s0, s1, s2;
         s0.x = s0.y = s0.z = s0.w = 0; s1 = s0; s2 = s0;
-        if (valid) { s0 = sp[0]; s1 = sp[1]; s2 = sp[2]; }
+        if (valid) { s0 = ss_ld16<VOL>(sp); s1 = ss_ld16<VOL>(sp + 1); s2 = ss_ld16<VOL>(sp + 2); }
         k[0] = s0.x; k[1] = s0.y; k[2] = s0.z; k[3] = s0.w;
         k[4] = s1.x; k[5] = s1.y; k[6] = s1.z; k[7] = s1.w;
         nn[0] = s2.x; nn[1] = s2.y; nn[2] = s2.z; meta = s2.w;
@@ -532,10 +620,10 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
 
     if (!early) {
         if (!BULK) {
-            ss_load64(src + 64u * (size_t)(pre_payload ? b_first - 2u : 0u), pre_cbytes, m);
-            if (valid && is_open && b_first == 1u) hw = *reinterpret_cast<const uint32_t *>(in_base + in_off);
+            ss_load64<false, VOL>(src + 64u * (size_t)(pre_payload ? b_first - 2u : 0u), pre_cbytes, m);
+            if (valid && is_open && b_first == 1u) hw = ss_ld4<VOL>(in_base + in_off);
         }
-        if (!BULK && valid && is_open && lane == st) ss_load_mac(src + mlen, wmac);   // the wire tag, long before it is compared
+        if (!BULK && valid && is_open && lane == st) ss_load_mac<VOL>(src + mlen, wmac);   // the wire tag, long before it is compared
     }
 
     // Output side of the same idea: over PCIe, 16-byte stores at a 64-byte stride (plus 4-byte headers,
@@ -829,8 +917,11 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
             sp[2] = s2;
             stword = SS_ST_OK | (tag << 8);
         }
+        // resident kernel: hand the state on -- also when the frame failed, its successor is waiting for the stamp
+        if (a.flags & SS_ARG_CHAIN) ss_st_release_u32(reinterpret_cast<uint32_t *>(sp + 2) + 3, (meta & 0xffu) | (a.new_ver << 8));
         if (BULK) a.status[tile.first + f] = stword;
     }
+    ss_dbg_stamp(a, tile_idx, lane, 5);
     if (!BULK) {
         // lane i collects the status of frame i from that frame's leader: one coalesced store per tile
         const uint32_t v = ss_shfl(stword, lane < nfr ? my_start : 0u);
@@ -867,6 +958,7 @@ SS_DEV void ss_thread_window(uint32_t acc[5], uint32_t w[16], uint32_t q, uint32
     ss_phorner(acc, w, (uint32_t)nbytes, r);
 }
 
+template <bool VOL = false>
 SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_pdl_launch_dependents();
@@ -876,9 +968,25 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
     bool valid = lane < nfr;
     SsDesc d;
     d.slot = d.in_off = d.out_off = d.len_flags = 0;
-    if (valid) d = a.desc[tile.first + lane];
+    if (valid) {
+        const uint4 dv = ss_ld16<VOL>(a.desc + tile.first + lane);
+        d.slot = dv.x; d.in_off = dv.y; d.out_off = dv.z; d.len_flags = dv.w;
+        if (a.desc_fill) *reinterpret_cast<uint4 *>(a.desc_fill + tile.first + lane) = dv;
+    }
     ss_pdl_wait();
+    ss_dep_wait(a.dep_seq, a.dep_need);
     ss_write_back(a, tile_idx, a.n_tiles, lane);
+    const bool chain = (a.flags & SS_ARG_CHAIN) != 0;
+    if (chain) {   // resident kernel: wait for this frame's predecessor (see ss_process_tile)
+        const uint32_t exp_ver = !valid ? 0u : ((a.flags & SS_ARG_CHAIN_UNIFORM) ? a.ver_all : a.ver[tile.first + lane]);
+        const uint32_t *vp = reinterpret_cast<const uint32_t *>(a.states + ((size_t)d.slot * 2u + ((d.len_flags & SS_F_OPEN) ? 1u : 0u)) * 3u + 2u) + 3;
+        bool ready = !valid || exp_ver == 0u;
+        for (;;) {
+            if (!ready) ready = (ss_ld_acquire_u32(vp) >> 8) == exp_ver;
+            if (!ss_any(!ready)) break;
+            ss_nanosleep(40);
+        }
+    }
     const uint32_t lf = d.len_flags;
     if (valid && (lf & SS_F_EXTRACT) && !(lf & SS_F_OPEN) && a.status[tile.first + lane] != SS_ST_OK) valid = false;
     if (valid && (lf & (SS_F_RUN | SS_F_OPEN)) == (SS_F_RUN | SS_F_OPEN) &&
@@ -896,7 +1004,7 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
     const uint8_t *src = a.in + d.in_off + (is_open ? 4u : 0u);
     uint8_t *dst = a.out + d.out_off + (is_open ? 0u : 4u);
     uint4 *sp = a.states + ((size_t)d.slot * 2u + (is_open ? 1u : 0u)) * 3u;
-    const uint4 s0 = sp[0], s1 = sp[1], s2 = sp[2];
+    const uint4 s0 = ss_ld16<VOL>(sp), s1 = ss_ld16<VOL>(sp + 1), s2 = ss_ld16<VOL>(sp + 2);
     uint32_t k[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
     uint32_t nn[3] = {s2.x, s2.y, s2.z};
     const bool in_run = (lf & SS_F_RUN) != 0 && is_open;
@@ -915,7 +1023,7 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
         x[0] ^= tag;
         *reinterpret_cast<uint32_t *>(a.out + d.out_off) = (mlen + 17u) | ((x[0] & 0xffu) << 24);
     } else {
-        const uint32_t c0 = *reinterpret_cast<const uint32_t *>(a.in + d.in_off) >> 24;
+        const uint32_t c0 = ss_ld4<VOL>(a.in + d.in_off) >> 24;
         tag = (x[0] ^ c0) & 0xffu;
         x[0] = (x[0] & 0xffffff00u) | c0;
     }
@@ -925,7 +1033,7 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
     for (uint32_t j = 0; j < npay; j++) {
         const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
         uint32_t m[16];
-        ss_load64(src + 64u * (size_t)j, cbytes, m);
+        ss_load64<false, VOL>(src + 64u * (size_t)j, cbytes, m);
         if (!is_open) {
             ss_chacha_block(k, 2u + j, nn[0], nn[1], nn[2], x);
 #pragma unroll
@@ -946,14 +1054,14 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
     if (!is_open) ss_store_mac(dst + mlen, mac);
     else {
         uint32_t wmac[4];
-        ss_load_mac(src + mlen, wmac);
+        ss_load_mac<VOL>(src + mlen, wmac);
         ok = ((wmac[0] ^ mac[0]) | (wmac[1] ^ mac[1]) | (wmac[2] ^ mac[2]) | (wmac[3] ^ mac[3])) == 0;
         if (ok) {
 #pragma unroll 1
             for (uint32_t j = 0; j < npay; j++) {              // verified: decrypt (ciphertext is still in L1/L2)
                 const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
                 uint32_t m[16];
-                ss_load64(src + 64u * (size_t)j, cbytes, m);
+                ss_load64<false, VOL>(src + 64u * (size_t)j, cbytes, m);
                 ss_chacha_block(k, 2u + j, nn[0], nn[1], nn[2], x);
 #pragma unroll
                 for (int i = 0; i < 16; i++) m[i] ^= x[i];
@@ -962,7 +1070,9 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
         }
     }
     const uint32_t frame_idx = tile.first + lane;
-    if (!ok) { a.status[frame_idx] = SS_ST_BAD_MAC; return; }
+    uint32_t *verp = reinterpret_cast<uint32_t *>(sp + 2) + 3;
+    const uint32_t ver_word = (s2.w & 0xffu) | (a.new_ver << 8);
+    if (!ok) { a.status[frame_idx] = SS_ST_BAD_MAC; if (chain) ss_st_release_u32(verp, ver_word); return; }
     if (in_run) { a.status[frame_idx] = SS_ST_OK | (tag << 8); return; }
     nn[1] ^= mac[0];
     nn[2] ^= mac[1];
@@ -977,5 +1087,6 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
     uint4 t2;
     t2.x = nn[0]; t2.y = nn[1]; t2.z = nn[2]; t2.w = s2.w;
     sp[2] = t2;
+    if (chain) ss_st_release_u32(verp, ver_word);
     a.status[frame_idx] = SS_ST_OK | (tag << 8);
 }

@@ -8,6 +8,7 @@
 // There is deliberately no CPU path in this file: every entry point that
 // computes needs a CUDA device.
 #include <cuda_runtime.h>
+#include <emmintrin.h>
 
 #include <atomic>
 #include <algorithm>
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const Ss
     uint8_t *mine = sx_stage + (size_t)threadIdx.x * SS_EXTRACT_STRIDE;
     const bool staged = mine_to_do && mlen <= SS_EXTRACT_STAGE;
     uint32_t kind = 0;
-    if (mine_to_do) kind = states[((size_t)d.slot * 2u) * 3u + 2u].w;   // provider kind lives in the tx state's meta word
+    if (mine_to_do) kind = states[((size_t)d.slot * 2u) * 3u + 2u].w & 0xffu;   // provider kind: low byte of the tx state's meta word
     if (staged) {
         const uint4 *src = reinterpret_cast<const uint4 *>(text);
         uint32_t *dst = reinterpret_cast<uint32_t *>(mine);
@@ -156,6 +157,305 @@ __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const Ss
     status[i] = r.status;
     delta[i].off = d.in_off;
     delta[i].len = r.len;
+}
+
+
+// ------------------------------------------------------ persistent relay kernel --
+// Small host batches (the token-streaming shape, BASELINE config 2) used to cost one kernel launch each:
+// 2.5 us of driver call, and 5.7 us between the end of kernel j and kernel j+1 being allowed past its
+// dependency wait, because a grid only counts as complete once its host-visible stores have been flushed
+// over PCIe.  This kernel stays resident instead.  The host writes a batch header into a
+// ring in mapped pinned memory and bumps a doorbell; one poller warp copies new headers into device memory.
+// The SMs are split into two roles:
+//   * COMPUTE warps draw tile tickets from a device counter, fetch their tile's descriptors and payload from
+//     the host arenas (prefetching batches ahead), wait until each frame's PREDECESSOR on its stream has left
+//     the stream state (the MAC chain, handed over per stream through a stamp in the state itself -- neither a
+//     grid boundary nor a barrier between batches), seal/open, and leave wire bytes and status words in
+//     DEVICE staging;
+//   * DRAIN warps, on other SMs, copy a finished batch's staging to the caller's host memory in 512-byte rows,
+//     fence to system scope and raise that batch's completion flag in host memory.
+// The split is what keeps the chain short: an SM that streams stores over PCIe acknowledges its other stores
+// late (measured: the device-scope fence of a computing warp took up to 7.7 us while results were draining from
+// the same SMs, 0.4 us otherwise), and that fence sits between every two batches of a stream.
+// The kernel exits when it has been idle for `idle_ns` (or the host asks), so cudaDeviceSynchronize()/cudaFree()
+// by other code in the process still return; the host relaunches it with the next batch.  Replaces the same
+// per-frame libsodium calls as every other batch path (/root/reference/src/provider.ts:248, :174).
+#define PK_RING 32u        // batches posted and not yet reaped, at most (>= the host pipeline depth)
+#define PK_RUNNING 1u
+#define PK_EXITING 2u
+#define PK_EXITED 3u
+#define PK_CHUNK 8192u     // bytes of results one drain ticket moves to the host
+
+struct PkSlot {            // 128 bytes; written by the host, read by the poller warp
+    const SsDesc *desc;
+    const SsTile *tiles;
+    const uint8_t *in;         // caller's arena (pinned host memory)
+    uint8_t *out;              // device staging for the results
+    uint32_t *status;          // device staging for the status words
+    uint32_t n_desc, n_tiles;
+    uint32_t flags, uni_per, uni_thread, out_n16;   // out_n16: 16-byte units of the out arena
+    uint8_t *host_out;         // where the drain warps put them
+    uint32_t *host_status;
+    const uint32_t *ver;       // per descriptor: the stamp its stream state must carry before the frame may use it
+    uint32_t new_ver, ver_all; // the stamp this batch leaves in every state it goes through; SS_ARG_CHAIN_UNIFORM: the one every frame expects
+    SsDesc *desc_fill;         // non-NULL: tiles also copy their descriptors here (device memory) for the next batch that repeats them
+    uint64_t pad[3];
+};
+static_assert(sizeof(PkSlot) == 128, "slot layout");
+
+struct PkHost {            // mapped pinned host memory
+    volatile unsigned long long doorbell;   // batches posted so far (host writes)
+    volatile uint32_t quit;                 // host: exit as soon as everything posted is done
+    uint32_t pad0[13];
+    volatile uint32_t state;                // PK_* (the GPU writes; the host writes PK_RUNNING before a launch)
+    uint32_t pad1[15];
+    volatile unsigned long long exit_installed;   // batches the exiting kernel had taken (= all completed)
+    uint64_t pad2[7];
+    struct { volatile unsigned long long v; uint64_t pad[7]; } done[PK_RING];   // [seq % PK_RING] = seq + 1: results of batch seq are in host memory
+    PkSlot slot[PK_RING];
+};
+
+struct PkEntry {           // device memory, one per ring slot
+    unsigned long long range;    // first tile ticket << 24 | tiles, published last (one 8-byte store)
+    unsigned long long drange;   // first drain ticket << 24 | chunks
+    unsigned long long seq;
+    uint32_t done, sysdone;
+    PkSlot s;
+    uint64_t pad[12];
+};
+static_assert(sizeof(PkEntry) == 256, "entry layout");
+#define PK_MAX_CTAS 1024u
+struct PkDev {
+    unsigned long long ticket;        uint64_t pad0[15];
+    unsigned long long drain_ticket;  uint64_t pad1[15];
+    unsigned long long sys_completed; uint64_t pad2[15];
+    // One copy per CTA of the words every idle or dependent warp polls, 128 bytes apart: with a single copy
+    // hundreds of polling warps hammer one L2 slice and the store they are waiting for queues behind their loads.
+    struct { unsigned long long tiles, chunks; uint64_t pad[14]; } posted[PK_MAX_CTAS];   // posted so far; bit 63 of tiles: the grid exits
+    PkEntry e[PK_RING];
+};
+#define PK_TS_WORDS 16u     // SYMRELAY_TS=1, per batch: [0] doorbell seen, [1..4] tile 0 {start, loads issued, dependency met, done}, [5] tile 0
+                            // signalled, [7] batch in host memory, [8..13] max over the batch's tiles of stamps 0..5
+
+__device__ __forceinline__ unsigned long long pk_ld_u64(const volatile unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long pk_ld_acquire_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long pk_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// release/acquire fences (not the sequentially consistent ones __threadfence*() compile to)
+__device__ __forceinline__ void pk_fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ void pk_fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+
+// Warp 0 of block 0: doorbell -> device-side batch table; decides when the grid exits.  Warp-uniform: every
+// lane issues the same loads (one transaction, broadcast), lane 0 writes the entry, all lanes write the copies.
+__device__ void pk_poller(PkHost *host, PkDev *dev, unsigned long long first_seq, unsigned long long idle_ns,
+                          unsigned long long *ts) {
+    const uint32_t lane = threadIdx.x & 31u;
+    unsigned long long installed = first_seq, cum = 0, dcum = 0;
+    unsigned long long t_last = pk_now();
+    for (;;) {
+        const uint4 db4 = ss_ld16<true>(const_cast<const unsigned long long *>(&host->doorbell));   // doorbell ‖ quit in one read
+        const unsigned long long db = (unsigned long long)db4.x | ((unsigned long long)db4.y << 32);
+        const uint32_t quit = db4.z;
+        if (db > installed) {
+            pk_fence_sys();   // acquire: what the host wrote before the doorbell (headers, control blocks, payload)
+            const unsigned long long t_seen = pk_now();
+            while (installed < db) {
+                const PkSlot *hs = &host->slot[installed % PK_RING];
+                PkEntry *e = &dev->e[installed % PK_RING];
+                // plain loads (ordered by the acquire fence above): volatile ones would go out one after the other
+                const uint4 *hq = reinterpret_cast<const uint4 *>(hs);
+                const uint4 a = hq[0], b = hq[1], c = hq[2], d = hq[3], f = hq[4], g = hq[5], h = hq[6];
+                const unsigned long long n_tiles = c.w;   // PkSlot::n_tiles
+                const unsigned long long n_chunks = ((unsigned long long)d.w * 16ull + PK_CHUNK - 1u) / PK_CHUNK +
+                                                    ((unsigned long long)c.z * 4ull + PK_CHUNK - 1u) / PK_CHUNK;   // out arena + status words
+                if (lane == 0) {
+                    uint4 *es = reinterpret_cast<uint4 *>(&e->s);
+                    es[0] = a; es[1] = b; es[2] = c; es[3] = d; es[4] = f; es[5] = g; es[6] = h;
+                    e->seq = installed;
+                    e->done = 0; e->sysdone = 0;
+                    if (ts) {
+                        unsigned long long *w = ts + (installed % 4096ull) * PK_TS_WORDS;
+                        w[0] = t_seen; w[8] = w[9] = w[10] = w[11] = w[12] = w[13] = 0;
+                    }
+                    pk_fence_gpu();
+                    *reinterpret_cast<volatile unsigned long long *>(&e->drange) = (dcum << 24) | n_chunks;
+                    *reinterpret_cast<volatile unsigned long long *>(&e->range) = (cum << 24) | n_tiles;
+                }
+                cum += n_tiles;
+                dcum += n_chunks;
+                installed++;
+            }
+            __syncwarp();
+            pk_fence_gpu();   // release: one fence, then relaxed stores of the copies (a st.release each would fence each time)
+            for (uint32_t c = lane; c < gridDim.x; c += 32u) {
+                asm volatile("st.relaxed.gpu.u64 [%0], %1;" ::"l"(&dev->posted[c].chunks), "l"(dcum) : "memory");
+                asm volatile("st.relaxed.gpu.u64 [%0], %1;" ::"l"(&dev->posted[c].tiles), "l"(cum) : "memory");
+            }
+            t_last = pk_now();
+            continue;
+        }
+        const unsigned long long sc = pk_ld_u64(&dev->sys_completed);
+        const unsigned long long now = pk_now();
+        if (sc != installed - first_seq) { t_last = now; continue; }   // batches in flight: not idle
+        if (quit || now - t_last > idle_ns) {
+            // Exit hand-shake (the host does: doorbell store, full fence, state load).  The state store is a posted
+            // PCIe write and the doorbell re-read a PCIe read, which cannot pass it: either the host sees EXITING
+            // and waits for the verdict, or this re-read sees its new batch.
+            if (lane == 0) host->state = PK_EXITING;
+            __threadfence_system();
+            const unsigned long long db2 = pk_ld_u64(&host->doorbell);
+            if (db2 != installed) {
+                if (lane == 0) host->state = PK_RUNNING;
+                __threadfence_system();
+                t_last = pk_now();
+                continue;
+            }
+            if (lane == 0) host->exit_installed = installed;
+            __threadfence_system();
+            if (lane == 0) host->state = PK_EXITED;
+            __threadfence_system();
+            for (uint32_t c = lane; c < gridDim.x; c += 32u)
+                asm volatile("st.release.gpu.u64 [%0], %1;" ::"l"(&dev->posted[c].tiles), "l"(cum | (1ull << 63)) : "memory");
+            return;
+        }
+    }
+}
+
+// ticket -> ring entry: lane j looks at entry j; `which`: 0 tile range, 1 drain range.  Returns the entry index and
+// the ticket's offset inside it.
+__device__ __forceinline__ uint32_t pk_find(PkDev *dev, unsigned long long t, uint32_t lane, int which, uint32_t *k) {
+    const unsigned long long r = pk_ld_u64(which ? &dev->e[lane].drange : &dev->e[lane].range);
+    const unsigned long long start = r >> 24, cnt = r & 0xffffffull;
+    const uint32_t hits = __ballot_sync(0xffffffffu, t >= start && t < start + cnt);
+    const uint32_t j = (uint32_t)__ffs((int)hits) - 1u;   // exactly one entry holds a posted ticket
+    *k = (uint32_t)(t - __shfl_sync(0xffffffffu, start, (int)j));
+    return j;
+}
+
+// DRAIN role: staging -> the caller's host memory, PK_CHUNK bytes per ticket.
+__device__ void pk_drain(PkHost *host, PkDev *dev, unsigned long long first_seq, unsigned long long *ts) {
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        unsigned long long t = 0;
+        if (lane == 0) t = atomicAdd(&dev->drain_ticket, 1ull);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        for (;;) {
+            if (pk_ld_acquire_u64(&dev->posted[blockIdx.x].chunks) > t) break;
+            if (pk_ld_acquire_u64(&dev->posted[blockIdx.x].tiles) >> 63) return;
+            __nanosleep(200);
+        }
+        uint32_t k;
+        PkEntry *e = &dev->e[pk_find(dev, t, lane, 1, &k)];
+        pk_fence_gpu();
+        const PkSlot s = e->s;
+        const unsigned long long seq = e->seq;
+        while (ss_ld_acquire_u32(&e->done) != s.n_tiles) __nanosleep(100);   // every tile of the batch has stored its results
+        const uint32_t out_chunks = (uint32_t)(((unsigned long long)s.out_n16 * 16ull + PK_CHUNK - 1u) / PK_CHUNK);
+        const uint4 *src;
+        uint4 *dst;
+        uint32_t n16;
+        if (k < out_chunks) {
+            src = reinterpret_cast<const uint4 *>(s.out) + (size_t)k * (PK_CHUNK / 16u);
+            dst = reinterpret_cast<uint4 *>(s.host_out) + (size_t)k * (PK_CHUNK / 16u);
+            n16 = s.out_n16 - k * (PK_CHUNK / 16u);
+        } else {
+            const uint32_t kk = k - out_chunks, n16s = (s.n_desc + 3u) >> 2;   // status words, 16 bytes at a time (both buffers are padded)
+            src = reinterpret_cast<const uint4 *>(s.status) + (size_t)kk * (PK_CHUNK / 16u);
+            dst = reinterpret_cast<uint4 *>(s.host_status) + (size_t)kk * (PK_CHUNK / 16u);
+            n16 = n16s - kk * (PK_CHUNK / 16u);
+        }
+        if (n16 > PK_CHUNK / 16u) n16 = PK_CHUNK / 16u;
+        uint4 v[PK_CHUNK / 512u];
+#pragma unroll
+        for (uint32_t i = 0; i < PK_CHUNK / 512u; i++)
+            if (lane + 32u * i < n16) v[i] = src[lane + 32u * i];
+#pragma unroll
+        for (uint32_t i = 0; i < PK_CHUNK / 512u; i++)
+            if (lane + 32u * i < n16) dst[lane + 32u * i] = v[i];
+        pk_fence_sys();
+        __syncwarp();
+        if (lane == 0 && atomicAdd(&e->sysdone, 1u) + 1u == (uint32_t)(pk_ld_u64(&e->drange) & 0xffffffull)) {
+            pk_fence_sys();
+            host->done[seq % PK_RING].v = seq + 1ull;
+            if (ts) ts[(seq % 4096ull) * PK_TS_WORDS + 7] = pk_now();
+            atomicAdd(&dev->sys_completed, 1ull);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128, 3) ss_persistent_kernel(PkHost *host, PkDev *dev, uint4 *states,
+                                                                 unsigned long long first_seq, unsigned long long idle_ns,
+                                                                 unsigned long long *ts, uint32_t drain_every) {
+    const uint32_t lane = threadIdx.x & 31u;
+    if (blockIdx.x == 0 && (threadIdx.x >> 5) == 0) { pk_poller(host, dev, first_seq, idle_ns, ts); return; }
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    if (smid % drain_every == drain_every - 1u) { pk_drain(host, dev, first_seq, ts); return; }   // role by SM, not by block
+    const unsigned long long *my_posted = &dev->posted[blockIdx.x].tiles;
+    for (;;) {
+        unsigned long long t = 0;
+        if (lane == 0) t = atomicAdd(&dev->ticket, 1ull);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        for (;;) {   // wait until the ticket names a posted tile
+            const unsigned long long p = pk_ld_acquire_u64(my_posted);
+            if ((p & ~(1ull << 63)) > t) break;
+            if (p >> 63) return;
+            __nanosleep(200);
+        }
+        uint32_t k;
+        PkEntry *e = &dev->e[pk_find(dev, t, lane, 0, &k)];
+        pk_fence_gpu();   // the entry's fields were written before its range word
+        const PkSlot s = e->s;
+        const unsigned long long seq = e->seq;
+        SsArgs a;
+        a.desc = s.desc;
+        a.tiles = s.tiles;
+        a.in = s.in;
+        a.out = s.out;
+        a.status = s.status;
+        a.n_tiles = s.n_tiles;
+        a.states = states;
+        a.flags = s.flags | SS_ARG_INPUT_INDEPENDENT | SS_ARG_CHAIN;
+        a.run_nonce = nullptr;
+        a.ver = s.ver;           // the MAC chain is handed over per stream (ss_core.cuh), not per batch
+        a.new_ver = s.new_ver;
+        a.ver_all = s.ver_all;
+        a.desc_fill = s.desc_fill;
+        unsigned long long *my_ts = (ts && k == 0) ? ts + (seq % 4096ull) * PK_TS_WORDS : nullptr;
+        a.dbg_ts = my_ts ? my_ts + 1 : nullptr;     // ss_process_tile stamps [1..4] for tile index 0
+        a.dbg_max = ts ? ts + (seq % 4096ull) * PK_TS_WORDS + 8 : nullptr;   // [8..]: the batch's LAST tile to get there
+        SsTile tile;
+        if (s.uni_per) {   // every frame has one block count: the tile follows from its index
+            if (k < s.uni_thread) { tile.first = 32u * k; tile.n_kind = 32u | (1u << 17); }
+            else {
+                tile.first = 32u * s.uni_thread + (k - s.uni_thread) * s.uni_per;
+                tile.n_kind = s.n_desc - tile.first < s.uni_per ? s.n_desc - tile.first : s.uni_per;
+            }
+        } else {
+            tile = s.tiles[k];
+        }
+        // Plain loads throughout: the acquire loads above (and in the dependency wait) order them after the host's
+        // and the previous batch's stores, and pinned host memory is not kept in the GPU's caches (tools/probes).
+        if (tile.n_kind & (1u << 17)) ss_process_thread_tile<false>(a, k, &tile);
+        else ss_process_tile<false, false>(a, k, &tile);
+        // this tile's results are in device staging: count it; the batch's last tile releases the drain
+        pk_fence_gpu();
+        __syncwarp();
+        if (lane == 0) atomicAdd(&e->done, 1u);
+        ss_dbg_stamp(a, k, lane, 4);
+        if (my_ts && lane == 0) my_ts[5] = pk_now();
+    }
 }
 
 // Stream set-up (libsodium init_push/init_pull): one thread per
@@ -273,6 +573,7 @@ static __device__ __align__(256) uint4 g_run_nonce_static[SYMRELAY_STATIC_RUN_MA
 static_assert(sizeof(uint4) * SYMRELAY_STATIC_RUN_MAX == (1u << 20), "the header promises 1 MiB per GPU");
 
 // --------------------------------------------------------------- host side --
+#define SLOT_CLOSED 0xffffffffu   /* slot_stamp entry of a slot that is not open */
 namespace {
 
 struct Stage {
@@ -301,6 +602,9 @@ struct Stage {
     // perm[k] = the caller's index of sorted descriptor k, applied to statuses and deltas on completion.
     std::vector<uint32_t> perm;
     bool permuted = false;
+    int64_t pk_seq = -1;          // >= 0: this batch went to the persistent kernel as its batch number pk_seq
+    uint64_t tmpl_gen = 0;        // h_ctrl holds tiles ‖ descriptors of this template generation (0: something else)
+    uint64_t dev_tmpl_gen = 0;    // d_ctrl holds the descriptors of this template generation (left there by the tiles of an earlier batch)
 };
 
 struct Shard {
@@ -308,6 +612,28 @@ struct Shard {
     uint4 *d_states = nullptr;
     uint4 *d_sx_fast = nullptr;            // extractor tables (SX_TABLES_BYTES), allocated last in shard_init
     uint4 *d_run_static = nullptr;         // device address of g_run_nonce_static on this GPU (symrelay_batch_device_runs_static)
+    // persistent kernel (small zero-copy host batches)
+    PkHost *pk_host = nullptr;             // mapped pinned: doorbell, state, completion flags, batch headers
+    PkDev *pk_dev = nullptr;
+    uint64_t pk_posted = 0;                // batches posted so far
+    unsigned long long *d_pk_ts = nullptr; // SYMRELAY_TS=1: PK_TS_WORDS stamps per batch, 4096 batches round-robin
+    bool pk_quit_req = false;              // the kernel was asked to exit because ordinary launches follow on s_k
+    uint32_t pk_floor = 0;                 // batch stamps up to here are settled (an ordinary launch on s_k followed them)
+    bool stamp_dirty = false;              // the last batch stamped the slot table but never ran (refused / failed)
+    // Template: the descriptors of the last batch that took the general path to the resident kernel, with what
+    // planning and checking them produced.  A batch whose descriptors (and arena sizes) are byte-identical, and
+    // which directly follows a batch of that template, needs none of that again: same tiles, same streams, every
+    // frame's predecessor is the previous batch.  Token streaming produces exactly this (BASELINE config 2).
+    std::vector<symrelay_desc> tmpl_desc;
+    uint64_t tmpl_in_bytes = 0, tmpl_out_bytes = 0, tmpl_sum = 0, last_sum = 0;
+    uint32_t tmpl_n = 0, tmpl_n_tiles = 0, tmpl_uni_per = 0, tmpl_uni_thread = 0, tmpl_flags = 0;
+    size_t tmpl_tiles_bytes = 0;
+    uint64_t tmpl_gen = 0;                 // identity of the template (0: none); Stage::tmpl_gen says whose control block a stage holds
+    uint64_t slot_gen = 0, tmpl_slot_gen = 0;   // bumped by every stream open/close on this GPU
+    bool tmpl_streak = false;              // the previous batch on this GPU was this template, through the resident kernel
+    bool tmpl_lazy = false;                // slot_stamp entries of the template's streams are behind by (stamp - tmpl_stamped) batches
+    std::vector<uint8_t> tmpl_tiles;       // the template's tile list (non-uniform batches)
+    cudaStream_t s_init = nullptr;         // stream set-up / export: must not queue behind the resident kernel on s_k
     std::vector<uint32_t> slot_stamp;      // [slot*2+dir] -> stamp of the last host batch that named it (duplicate check)
     uint32_t stamp = 0;
     std::vector<uint8_t> h_sx_fast;
@@ -344,6 +670,11 @@ struct symrelay_ctx {
     bool pdl = true;   // SYMRELAY_PDL=0 turns programmatic dependent launch off
     bool inline_tiles = true;   // SYMRELAY_INLINE_TILES=0: small host batches read their tile list from memory like all others
     bool bucket = true;     // SYMRELAY_BUCKET=0: large staged batches are planned in the caller's descriptor order
+    bool persist = true;    // SYMRELAY_PERSIST=0: small host batches are launched one kernel per batch (the round-1 path)
+    uint64_t pk_idle_ns = 200000;   // SYMRELAY_PERSIST_IDLE_US: the resident kernel exits after this long without work
+    uint64_t pk_batches = 0, pk_launches = 0, tmpl_hits = 0;
+    uint32_t pk_ctas_per_sm = 1;    // SYMRELAY_PERSIST_CTAS_PER_SM
+    uint32_t pk_drain_every = 4;    // SYMRELAY_PERSIST_DRAIN_EVERY: every n-th SM copies results to the host, the others compute
     bool defer_wb = true;   // SYMRELAY_DEFER=0: pipelined zero-copy batches write their results to the host themselves
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
     uint64_t inject_refusal = 0;   // SYMRELAY_INJECT_REFUSAL=k: the front end's k-th batch is refused (tests of the error path)
@@ -549,7 +880,7 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
             return fail(ctx, SYMRELAY_ECUDA, "cudaGetSymbolAddress(run scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
         sh.d_run_static = reinterpret_cast<uint4 *>(p);
     }
-    sh.slot_stamp.assign((size_t)ctx->opts.max_streams * 2u, 0u);
+    sh.slot_stamp.assign((size_t)ctx->opts.max_streams * 2u, SLOT_CLOSED);
     const size_t table_bytes = (size_t)ctx->opts.max_streams * 2u * 48u;
     CU(ctx, cudaMalloc(&sh.d_states, table_bytes));
     CU(ctx, cudaMemset(sh.d_states, 0, table_bytes));
@@ -557,6 +888,11 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_k, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_out, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_aux, cudaStreamNonBlocking));
+    CU(ctx, cudaStreamCreateWithFlags(&sh.s_init, cudaStreamNonBlocking));
+    CU(ctx, cudaHostAlloc(&sh.pk_host, sizeof(PkHost), cudaHostAllocMapped | cudaHostAllocPortable));
+    memset(sh.pk_host, 0, sizeof(PkHost));
+    sh.pk_host->state = PK_EXITED;
+    CU(ctx, cudaMalloc(&sh.pk_dev, sizeof(PkDev)));
     CU(ctx, cudaEventCreateWithFlags(&sh.ev_fork, cudaEventDisableTiming));
     CU(ctx, cudaEventCreateWithFlags(&sh.ev_join, cudaEventDisableTiming));
     {
@@ -575,21 +911,24 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     CU(ctx, cudaHostAlloc(&sh.h_init, sizeof(SsInitRec) * sh.init_cap, cudaHostAllocDefault));
     CU(ctx, cudaMalloc(&sh.d_init, sizeof(SsInitRec) * sh.init_cap));
     sh.stages.resize(ctx->opts.pipeline_depth);
-    const size_t ctrl_bytes = (size_t)ctx->opts.max_batch_frames * (sizeof(symrelay_desc) + sizeof(symrelay_tile));
+    const size_t ctrl_bytes = (size_t)ctx->opts.max_batch_frames * (sizeof(symrelay_desc) + sizeof(symrelay_tile) + 4u) + 64u;
     for (Stage &st : sh.stages) {
         CU(ctx, cudaMalloc(&st.d_ctrl, ctrl_bytes));
         CU(ctx, cudaHostAlloc(&st.h_ctrl, ctrl_bytes, cudaHostAllocMapped));
         CU(ctx, cudaMalloc(&st.d_in, ctx->opts.stage_bytes));
         CU(ctx, cudaMalloc(&st.d_out, ctx->opts.stage_bytes));
-        CU(ctx, cudaMalloc(&st.d_status, (size_t)ctx->opts.max_batch_frames * 4u));
-        CU(ctx, cudaHostAlloc(&st.h_status, (size_t)ctx->opts.max_batch_frames * 4u, cudaHostAllocMapped));
+        CU(ctx, cudaMalloc(&st.d_status, (size_t)ctx->opts.max_batch_frames * 4u + 16u));   // +16: the drain moves status words 16 bytes at a time
+        CU(ctx, cudaHostAlloc(&st.h_status, (size_t)ctx->opts.max_batch_frames * 4u + 16u, cudaHostAllocMapped));
         CU(ctx, cudaMalloc(&st.d_delta, (size_t)ctx->opts.max_batch_frames * sizeof(symrelay_delta)));
         CU(ctx, cudaHostAlloc(&st.h_delta, (size_t)ctx->opts.max_batch_frames * sizeof(symrelay_delta), cudaHostAllocMapped));
         CU(ctx, cudaEventCreateWithFlags(&st.ev_in, cudaEventDisableTiming));
         CU(ctx, cudaEventCreateWithFlags(&st.ev_k, cudaEventDisableTiming));
         CU(ctx, cudaEventCreateWithFlags(&st.ev_out, cudaEventDisableTiming));
     }
-    if (getenv("SYMRELAY_TS")) { CU(ctx, cudaMalloc(&sh.d_ts, 4096u * 4u * 8u)); CU(ctx, cudaMemset(sh.d_ts, 0, 4096u * 4u * 8u)); }
+    if (getenv("SYMRELAY_TS")) {
+        CU(ctx, cudaMalloc(&sh.d_ts, 4096u * 4u * 8u)); CU(ctx, cudaMemset(sh.d_ts, 0, 4096u * 4u * 8u));
+        CU(ctx, cudaMalloc(&sh.d_pk_ts, 4096u * PK_TS_WORDS * 8u)); CU(ctx, cudaMemset(sh.d_pk_ts, 0, 4096u * PK_TS_WORDS * 8u));
+    }
     CU(ctx, cudaMalloc(&sh.d_sx_fast, SX_TABLES_BYTES));
     CU(ctx, cudaMemcpy(sh.d_sx_fast, sh.h_sx_fast.data(), SX_TABLES_BYTES, cudaMemcpyHostToDevice));
     return 0;
@@ -598,7 +937,9 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
 static void shard_free(Shard &sh) {
     if (sh.dev < 0) return;
     set_device(sh.dev);
+    if (sh.pk_host) sh.pk_host->quit = 1;   // the resident kernel leaves as soon as it is drained
     if (sh.s_k) cudaStreamSynchronize(sh.s_k);
+    if (sh.s_init) cudaStreamSynchronize(sh.s_init);
     if (sh.d_ts && sh.ts_n > 64) {   // diagnostics: how consecutive host batches overlap on the GPU
         std::vector<unsigned long long> ts(4096u * 4u);
         cudaMemcpy(ts.data(), sh.d_ts, ts.size() * 8u, cudaMemcpyDeviceToHost);
@@ -618,6 +959,51 @@ static void shard_free(Shard &sh) {
                     (unsigned long long)cnt, pre / cnt * 1e-3, wait / cnt * 1e-3, post / cnt * 1e-3, period / cnt * 1e-3, lead / cnt * 1e-3);
     }
     cudaFree(sh.d_ts);
+    if (sh.d_pk_ts && sh.pk_posted > 64) {   // diagnostics: where a batch spends its time inside the resident kernel
+        std::vector<unsigned long long> ts(4096u * PK_TS_WORDS);
+        cudaMemcpy(ts.data(), sh.d_pk_ts, ts.size() * 8u, cudaMemcpyDeviceToHost);
+        const uint64_t last = sh.pk_posted - 1, first = last >= 2048 ? last - 2047 : 1;
+        double d[8] = {0, 0, 0, 0, 0, 0, 0, 0}, m[6] = {0, 0, 0, 0, 0, 0}, mm[4] = {0, 0, 0, 0};
+        uint64_t cnt = 0;
+        for (uint64_t k = first + 1; k <= last; k++) {
+            const unsigned long long *c = &ts[PK_TS_WORDS * (k % 4096u)], *p = &ts[PK_TS_WORDS * ((k - 1) % 4096u)];
+            if (!c[0] || !c[1] || !c[7] || !p[7] || c[7] < c[0]) continue;
+            d[0] += (double)(c[1] - c[0]);   // doorbell seen -> tile 0 starts
+            d[1] += (double)(c[2] - c[1]);   // descriptors and loads issued
+            d[2] += (double)(c[3] - c[2]);   // waiting for the previous batch
+            d[3] += (double)(c[4] - c[3]);   // ChaCha20/Poly1305 + stores
+            d[4] += (double)(c[5] - c[4]);   // device-scope fence + count
+            d[5] += (double)(c[7] - c[5]);   // tile 0 signalled -> the whole batch drained to the host
+            d[6] += (double)(c[7] - c[0]);   // doorbell seen -> batch's results in host memory
+            d[7] += (double)(c[7] - p[7]);   // period
+            m[0] += (double)((long long)(c[8] - c[0]));     // doorbell seen -> the batch's last tile starts
+            m[1] += (double)((long long)(c[9] - c[8]));     // ... has its loads issued
+            m[2] += (double)((long long)(c[10] - p[11]));   // previous batch's last tile done -> this batch's last tile past the dependency
+            m[3] += (double)((long long)(c[11] - c[10]));   // ... -> last tile done
+            m[4] += (double)((long long)(c[12] - p[12]));   // chain link: last signal to last signal
+            m[3] = m[3];
+            mm[0] += (double)((long long)(c[10] - p[12]));  // previous batch's last signal -> this batch's last tile past the dependency
+            mm[1] += (double)((long long)(c[13] - c[10]));  // -> last tile computed (states written)
+            mm[2] += (double)((long long)(c[12] - c[13]));  // -> last tile signalled
+            mm[3] += (double)((long long)(c[7] - c[12]));   // -> the batch's results are in host memory (drain warps)
+            m[5] += (double)((long long)(c[3] - p[11]));    // previous batch's last tile done -> tile 0 past the dependency
+            cnt++;
+        }
+        if (cnt)
+            fprintf(stderr, "symrelay resident-kernel timeline over %llu batches (us, tile 0): doorbell->start %.2f, loads issued %.2f, "
+                    "waiting for the previous batch %.2f, compute+stores %.2f, signal %.2f, then until the batch is drained %.2f; doorbell->results "
+                    "in host memory %.2f; period %.2f\n", (unsigned long long)cnt, d[0] / cnt * 1e-3, d[1] / cnt * 1e-3, d[2] / cnt * 1e-3,
+                    d[3] / cnt * 1e-3, d[4] / cnt * 1e-3, d[5] / cnt * 1e-3, d[6] / cnt * 1e-3, d[7] / cnt * 1e-3);
+        if (cnt)
+            fprintf(stderr, "  latest tile of a batch: starts %.2f after the doorbell was seen, loads issued %.2f later; previous batch's last "
+                    "tile done -> tile 0 past the dependency %.2f, -> last tile past it %.2f, -> last tile done +%.2f; chain link %.2f\n",
+                    m[0] / cnt * 1e-3, m[1] / cnt * 1e-3, m[5] / cnt * 1e-3, m[2] / cnt * 1e-3, m[3] / cnt * 1e-3, m[4] / cnt * 1e-3);
+        if (cnt)
+            fprintf(stderr, "  chain (max over the tiles of a batch): previous batch's last signal -> last tile past the dependency %.2f -> states "
+                    "written +%.2f -> signalled +%.2f -> drained to host memory +%.2f\n", mm[0] / cnt * 1e-3, mm[1] / cnt * 1e-3,
+                    mm[2] / cnt * 1e-3, mm[3] / cnt * 1e-3);
+    }
+    cudaFree(sh.d_pk_ts);
     if (sh.s_out) cudaStreamSynchronize(sh.s_out);
     for (Stage &st : sh.stages) {
         cudaFree(st.d_ctrl); cudaFreeHost(st.h_ctrl); cudaFree(st.d_in); cudaFree(st.d_out);
@@ -628,6 +1014,8 @@ static void shard_free(Shard &sh) {
         if (st.ev_out) cudaEventDestroy(st.ev_out);
     }
     cudaFree(sh.d_states); cudaFreeHost(sh.h_init); cudaFree(sh.d_init); cudaFree(sh.d_sx_fast);
+    cudaFree(sh.pk_dev); cudaFreeHost(sh.pk_host);
+    if (sh.s_init) cudaStreamDestroy(sh.s_init);
     if (sh.s_in) cudaStreamDestroy(sh.s_in);
     if (sh.s_k) cudaStreamDestroy(sh.s_k);
     if (sh.s_out) cudaStreamDestroy(sh.s_out);
@@ -659,6 +1047,10 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (ctx->opts.flags & SYMRELAY_OPT_NO_ZERO_COPY) ctx->zero_copy_max = 0;
     { const char *e = getenv("SYMRELAY_PROF"); ctx->prof = e && e[0] == '1'; }
     { const char *e = getenv("SYMRELAY_DEFER"); if (e && e[0] == '0') ctx->defer_wb = false; }
+    { const char *e = getenv("SYMRELAY_PERSIST"); if (e && e[0] == '0') ctx->persist = false; }
+    if (const char *m = getenv("SYMRELAY_PERSIST_CTAS_PER_SM")) ctx->pk_ctas_per_sm = (uint32_t)atoi(m);
+    if (const char *m = getenv("SYMRELAY_PERSIST_DRAIN_EVERY")) { const int v = atoi(m); if (v >= 2) ctx->pk_drain_every = (uint32_t)v; }
+    if (const char *m = getenv("SYMRELAY_PERSIST_IDLE_US")) ctx->pk_idle_ns = strtoull(m, nullptr, 10) * 1000ull;
     { const char *e = getenv("SYMRELAY_BUCKET"); if (e && e[0] == '0') ctx->bucket = false; }
     { const char *e = getenv("SYMRELAY_INLINE_TILES"); if (e && e[0] == '0') ctx->inline_tiles = false; }
     if (const char *m = getenv("SYMRELAY_INJECT_REFUSAL")) ctx->inject_refusal = strtoull(m, nullptr, 10);
@@ -698,15 +1090,27 @@ void symrelay_destroy(symrelay_ctx *ctx) {
 }
 
 // ---- streams ------------------------------------------------------------------
+static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st);
 static int sched_slot_busy(symrelay_ctx *ctx, uint32_t slot);     // scheduler_impl.inc
 static void sched_slot_reset(symrelay_ctx *ctx, uint32_t slot);
+// A slot changes hands: its states are rewritten by the init kernel (stamp 0), so nobody may wait for an old stamp.
+static void tmpl_flush_stamps(Shard &sh);
+static void stamp_reset(symrelay_ctx *ctx, uint32_t slot, bool open) {
+    Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
+    tmpl_flush_stamps(sh);   // first: a late flush must not write over what is set here
+    sh.tmpl_streak = false;
+    sh.slot_gen++;           // a cached template's "all slots open" verdict no longer holds
+    sh.slot_stamp[(size_t)slot * 2u] = sh.slot_stamp[(size_t)slot * 2u + 1u] = open ? 0u : SLOT_CLOSED;
+}
 static int push_init_recs(symrelay_ctx *ctx, Shard &sh, uint32_t n) {
     CU(ctx, set_device(sh.dev));
-    CU(ctx, cudaMemcpyAsync(sh.d_init, sh.h_init, sizeof(SsInitRec) * n, cudaMemcpyHostToDevice, sh.s_k));
-    ss_init_kernel<<<(n + 127) / 128, 128, 0, sh.s_k>>>(sh.d_init, n, sh.d_states);
+    // On its own stream: s_k may be occupied by the resident kernel for as long as batches keep coming, and a new
+    // or closing connection touches no slot that a batch in flight names.
+    CU(ctx, cudaMemcpyAsync(sh.d_init, sh.h_init, sizeof(SsInitRec) * n, cudaMemcpyHostToDevice, sh.s_init));
+    ss_init_kernel<<<(n + 127) / 128, 128, 0, sh.s_init>>>(sh.d_init, n, sh.d_states);
     ctx->launches++;
     CU(ctx, cudaGetLastError());
-    CU(ctx, cudaStreamSynchronize(sh.s_k));  // h_init is reused by the next call
+    CU(ctx, cudaStreamSynchronize(sh.s_init));  // h_init is reused by the next call; the states are visible to later batches
     return 0;
 }
 
@@ -740,6 +1144,7 @@ int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_
         ctx->free_slots[g].pop_back();
         ctx->slot_state[slots_out[i]] = 1;
         sched_slot_reset(ctx, slots_out[i]);
+        stamp_reset(ctx, slots_out[i], true);
         g = (g + 1) % ctx->n_gpus;
     }
     for (int gi = 0; gi < ctx->n_gpus; gi++) {
@@ -782,6 +1187,7 @@ int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, const uint8_t
     ctx->free_slots[g].pop_back();
     ctx->slot_state[slot] = 1;
     sched_slot_reset(ctx, slot);
+    stamp_reset(ctx, slot, true);
     Shard &sh = ctx->shard[g];
     fill_rec(&sh.h_init[0], slot, 0, tx_key, tx_init, tx_init_len, (uint32_t)provider_kind);
     fill_rec(&sh.h_init[1], slot, 1, rx_key, rx_init, rx_init_len, (uint32_t)provider_kind);
@@ -803,6 +1209,7 @@ int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot) {
     int rc = push_init_recs(ctx, sh, 2);  // wipes the key material on the device
     if (rc) return rc;
     sched_slot_reset(ctx, slot);   // a half-received frame of the old connection must not eat the next one's bytes
+    stamp_reset(ctx, slot, false);
     ctx->slot_state[slot] = 0;
     ctx->free_slots[slot % (uint32_t)ctx->n_gpus].push_back(slot);
     return 0;
@@ -815,9 +1222,13 @@ int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_t tx_state[SY
     if (slot >= ctx->opts.max_streams || !ctx->slot_state[slot]) return fail(ctx, SYMRELAY_ENOENT, "slot %u not open", slot);
     Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
     CU(ctx, set_device(sh.dev));
+    for (Stage &st : sh.stages) {   // "live" means after every host batch submitted so far
+        const int rc = finish_stage(ctx, sh, st);
+        if (rc) return rc;
+    }
     uint8_t buf[96];
-    CU(ctx, cudaMemcpyAsync(buf, sh.d_states + (size_t)slot * 6u, 96, cudaMemcpyDeviceToHost, sh.s_k));
-    CU(ctx, cudaStreamSynchronize(sh.s_k));
+    CU(ctx, cudaMemcpyAsync(buf, sh.d_states + (size_t)slot * 6u, 96, cudaMemcpyDeviceToHost, sh.s_init));
+    CU(ctx, cudaStreamSynchronize(sh.s_init));
     if (tx_state) { memcpy(tx_state, buf, 44); memset(tx_state + 44, 0, 8); }
     if (rx_state) { memcpy(rx_state, buf + 48, 44); memset(rx_state + 44, 0, 8); }
     return 0;
@@ -891,9 +1302,156 @@ int symrelay_batch_device_runs_static(symrelay_ctx *ctx, int gpu_index, const sy
                         nullptr, (cudaStream_t)cuda_stream, 0u, scratch);
 }
 
+// ---- persistent kernel: host side ------------------------------------------------------------
+// Ordinary launches are about to go to s_k: the resident kernel must leave first (stream order then keeps every
+// batch in submission order).  No waiting here -- the launches simply queue behind it.
+// Copy into a pinned block the GPU is about to read, with streaming stores: the lines were last touched by the
+// device's PCIe reads, ordinary stores would first have to pull them back into this core's cache.  dst 16-byte
+// aligned.  Ordered before the doorbell / the launch by the _mm_sfence() there.
+static inline void nt_copy(void *dst, const void *src, size_t bytes) {
+    __m128i *d = reinterpret_cast<__m128i *>(dst);
+    const __m128i *q = reinterpret_cast<const __m128i *>(src);
+    size_t i = 0;
+    for (; i + 16 <= bytes; i += 16) _mm_stream_si128(d++, _mm_loadu_si128(q++));
+    if (i < bytes) memcpy(d, q, bytes - i);
+}
+
+static inline uint32_t pk_version(uint32_t stamp) { return (stamp & 0x7fffffu) | 0x800000u; }   // 24 bits, never 0, repeats every 8 M batches
+
+// Waits until every batch handed to the resident kernel has finished (rare paths only).
+static int pk_drain_host(symrelay_ctx *ctx, Shard &sh) {
+    for (Stage &st : sh.stages)
+        if (st.busy && st.pk_seq >= 0) {
+            const int rc = finish_stage(ctx, sh, st);
+            if (rc) return rc;
+        }
+    return 0;
+}
+
+// The fast path does not touch the stamp table; before anyone reads it again, give the template's streams the
+// stamp of the last batch that went through them.
+static void tmpl_flush_stamps(Shard &sh) {
+    if (!sh.tmpl_lazy) return;
+    uint32_t *stamp = sh.slot_stamp.data();
+    const uint32_t now = sh.stamp;
+    for (const symrelay_desc &d : sh.tmpl_desc) {
+        uint32_t &e = stamp[(size_t)d.slot * 2u + ((d.len_flags >> 26) & 1u)];
+        if (e != SLOT_CLOSED) e = now;
+    }
+    sh.tmpl_lazy = false;
+}
+
+static void pk_quiesce(Shard &sh) {
+    if (!sh.pk_host || sh.pk_quit_req) return;
+    if (sh.pk_host->state == PK_EXITED && sh.pk_posted == sh.pk_host->exit_installed) return;   // not running, nothing pending
+    sh.pk_host->quit = 1;
+    sh.pk_quit_req = true;
+}
+
+static int pk_launch(symrelay_ctx *ctx, Shard &sh, uint64_t first_seq) {
+    sh.pk_host->state = PK_RUNNING;
+    std::atomic_thread_fence(std::memory_order_seq_cst);
+    CU(ctx, cudaMemsetAsync(sh.pk_dev, 0, sizeof(PkDev), sh.s_k));
+    // Resident CTAs per SM: a warp is held from its tile's first PCIe read until its results have been fenced to the
+    // host (~15 us), of which ~4 us compute; with one CTA per SM the batches behind the one that computes cannot all
+    // prefetch.  Never more CTAs than fit at once: every warp of the grid must be able to run (they wait on each other).
+    int sms = 148, per_sm = 1;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, sh.dev);
+    CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ss_persistent_kernel, 128, 0));
+    if (per_sm > (int)ctx->pk_ctas_per_sm) per_sm = (int)ctx->pk_ctas_per_sm;
+    if (per_sm < 1) per_sm = 1;
+    sms *= per_sm;
+    if (sms > (int)PK_MAX_CTAS) sms = (int)PK_MAX_CTAS;
+    ss_persistent_kernel<<<(unsigned)sms, 128, 0, sh.s_k>>>(sh.pk_host, sh.pk_dev, sh.d_states, (unsigned long long)first_seq,
+                                                            (unsigned long long)ctx->pk_idle_ns, sh.d_pk_ts, ctx->pk_drain_every);
+    ctx->launches++;
+    ctx->pk_launches++;
+    CU(ctx, cudaGetLastError());
+    return 0;
+}
+
+// Spin until pred() holds; every few microseconds make sure the kernel has not died under us.
+extern "C++" {
+template <typename P>
+static int pk_spin(symrelay_ctx *ctx, Shard &sh, P pred, const char *what) {
+    for (uint32_t spins = 1;; spins++) {
+        if (pred()) return 0;
+        __builtin_ia32_pause();
+        if ((spins & 0x3fffu) == 0) {
+            const cudaError_t e = cudaStreamQuery(sh.s_k);
+            if (e != cudaSuccess && e != cudaErrorNotReady)
+                return fail(ctx, SYMRELAY_ECUDA, "resident relay kernel failed while %s: %s", what, cudaGetErrorString(e));
+            if (e == cudaSuccess && !pred()) {
+                // nothing is running on s_k although work is pending: the kernel left (idle exit raced this batch
+                // in a way the hand-shake did not cover, or it was never started) -- start it on what is pending
+                std::atomic_thread_fence(std::memory_order_seq_cst);
+                if (pred()) return 0;
+                if (sh.pk_host->state == PK_EXITED && sh.pk_host->exit_installed < sh.pk_posted) {
+                    const int rc = pk_launch(ctx, sh, sh.pk_host->exit_installed);
+                    if (rc) return rc;
+                }
+            }
+        }
+    }
+}
+}  // extern "C++"
+
+// Hands one planned batch to the resident kernel.  st.h_ctrl holds tiles ‖ descs already.
+static int pk_post(symrelay_ctx *ctx, Shard &sh, Stage &st, const uint8_t *ctrl, size_t tiles_bytes, uint32_t n, uint32_t n_tiles,
+                   const uint8_t *in, uint8_t *out, uint64_t out_bytes, uint32_t flags, uint32_t uni_per, uint32_t uni_thread,
+                   const uint32_t *ver, uint32_t new_ver, uint32_t ver_all = 0, const SsDesc *desc_dev = nullptr, SsDesc *desc_fill = nullptr) {
+    PkHost *H = sh.pk_host;
+    if (sh.pk_quit_req) {
+        // Launches were queued behind the kernel since; a batch posted now would overtake them.  Wait for the kernel
+        // to be gone (it leaves as soon as it is drained), then the relaunch below queues behind those launches.
+        const int rc = pk_spin(ctx, sh, [&] { return H->state == PK_EXITED; }, "waiting for it to exit");
+        if (rc) return rc;
+        sh.pk_quit_req = false;
+        H->quit = 0;
+    }
+    const uint64_t seq = sh.pk_posted;
+    PkSlot &ps = H->slot[seq % PK_RING];
+    ps.desc = desc_dev ? desc_dev : reinterpret_cast<const SsDesc *>(ctrl + tiles_bytes);
+    ps.desc_fill = desc_fill;
+    ps.tiles = reinterpret_cast<const SsTile *>(ctrl);
+    ps.in = in; ps.out = st.d_out; ps.status = st.d_status;   // results: device staging first, the drain warps move them
+    ps.n_desc = n; ps.n_tiles = n_tiles;
+    ps.flags = flags; ps.uni_per = uni_per; ps.uni_thread = uni_thread; ps.out_n16 = (uint32_t)(out_bytes >> 4);
+    ps.host_out = out; ps.host_status = st.h_status;
+    ps.ver = ver; ps.new_ver = new_ver; ps.ver_all = ver_all;
+    _mm_sfence();   // header, control block (streaming stores) and the caller's payload before the doorbell
+    std::atomic_thread_fence(std::memory_order_release);
+    H->doorbell = seq + 1;
+    sh.pk_posted = seq + 1;
+    st.pk_seq = (int64_t)seq;
+    ctx->pk_batches++;
+    std::atomic_thread_fence(std::memory_order_seq_cst);   // doorbell store before the state load (see pk_poller)
+    uint32_t state = H->state;
+    if (state == PK_EXITING) {
+        const int rc = pk_spin(ctx, sh, [&] { return H->state != PK_EXITING; }, "settling its exit");
+        if (rc) return rc;
+        state = H->state;
+    }
+    if (state == PK_EXITED) return pk_launch(ctx, sh, H->exit_installed);
+    return 0;
+}
+
+static inline bool pk_batch_done(const Shard &sh, int64_t seq) {
+    return sh.pk_host->done[(uint64_t)seq % PK_RING].v >= (unsigned long long)seq + 1ull;
+}
+
+// Has the batch in this stage finished (results in host memory)?  Never blocks.
+static bool stage_ready(const Shard &sh, const Stage &st) {
+    if (!st.busy) return true;
+    if (st.pk_seq >= 0) return pk_batch_done(sh, st.pk_seq);
+    if (st.deferred && st.wb_by < 0) return false;   // its results still sit in device staging
+    return cudaEventQuery(st.deferred ? sh.stages[(size_t)st.wb_by].ev_out : st.ev_out) == cudaSuccess;
+}
+
 // The results of stage `idx` still sit in device staging and nothing that follows will carry them.
 static int flush_write_back(symrelay_ctx *ctx, Shard &sh, int idx) {
     Stage &p = sh.stages[(size_t)idx];
+    pk_quiesce(sh);
     SsArgs a;
     memset(&a, 0, sizeof a);
     a.wb_src = reinterpret_cast<const uint4 *>(p.d_out);
@@ -915,6 +1473,13 @@ static int flush_write_back(symrelay_ctx *ctx, Shard &sh, int idx) {
 static int finish_stage(symrelay_ctx *ctx, Shard &sh, Stage &st) {
     if (!st.busy) return 0;
     CU(ctx, set_device(sh.dev));
+    if (st.pk_seq >= 0) {
+        const int64_t seq = st.pk_seq;
+        const int rc = pk_spin(ctx, sh, [&] { return pk_batch_done(sh, seq); }, "waiting for a batch");
+        if (rc) return rc;
+        std::atomic_thread_fence(std::memory_order_acquire);
+        st.pk_seq = -1;
+    } else
     if (st.deferred) {
         const int idx = (int)(&st - sh.stages.data());
         if (sh.pending_wb == idx) {
@@ -957,11 +1522,51 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (rc) return rc;
     PROF_MARK(ctx, 0);
 
+    // Fast path: the batch repeats the template (see Shard) and directly follows a batch of it.
+    if (sh.tmpl_streak && n == sh.tmpl_n && in_bytes == sh.tmpl_in_bytes && out_bytes == sh.tmpl_out_bytes &&
+        sh.slot_gen == sh.tmpl_slot_gen && !sh.stamp_dirty && sh.stamp < 0xfffffd00u &&
+        memcmp(desc, sh.tmpl_desc.data(), (size_t)n * sizeof(symrelay_desc)) == 0 &&
+        is_library_pinned(ctx, in, in_bytes) && is_library_pinned(ctx, out, out_bytes)) {
+        PROF_MARK(ctx, 1);
+        if (st.tmpl_gen != sh.tmpl_gen) {   // this stage's control block holds something else: (re)write tiles ‖ descriptors once
+            if (!sh.tmpl_uni_per) memcpy(st.h_ctrl, sh.tmpl_tiles.data(), (size_t)sh.tmpl_n_tiles * sizeof(symrelay_tile));
+            memcpy(st.h_ctrl + sh.tmpl_tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
+            st.tmpl_gen = sh.tmpl_gen;
+        }
+        PROF_MARK(ctx, 3);
+        const uint32_t prev = sh.stamp++;   // the stamp table itself is brought up to date when the streak ends (tmpl_flush_stamps)
+        sh.tmpl_lazy = true;
+        // Descriptors: the first batch of a template through this stage leaves a copy in the stage's device control
+        // block (every tile stores the 160 bytes it has just read); later ones read that copy instead of the host's.
+        SsDesc *dev_descs = reinterpret_cast<SsDesc *>(st.d_ctrl);
+        const bool cached = st.dev_tmpl_gen == sh.tmpl_gen;
+        st.dev_tmpl_gen = sh.tmpl_gen;
+        rc = pk_post(ctx, sh, st, st.h_ctrl, sh.tmpl_tiles_bytes, n, sh.tmpl_n_tiles, in, out, out_bytes,
+                     sh.tmpl_flags | SS_ARG_CHAIN_UNIFORM, sh.tmpl_uni_per, sh.tmpl_uni_thread, nullptr, pk_version(sh.stamp),
+                     pk_version(prev), cached ? dev_descs : nullptr, cached ? nullptr : dev_descs);
+        if (rc) { sh.stamp_dirty = true; sh.tmpl_streak = false; return rc; }
+        PROF_MARK(ctx, 5);
+        st.deferred = false; st.wb_by = -1; st.permuted = false;
+        ctx->prof_n++;
+        ctx->zero_copy_batches++;
+        ctx->tmpl_hits++;
+        st.busy = true;
+        st.n = n;
+        st.user_status = status;
+        st.user_delta = nullptr;
+        st.ticket = (seq << 3) | gpu_index;
+        return st.ticket;
+    }
+    tmpl_flush_stamps(sh);     // the general path reads and writes the stamp table: bring it up to date first
+    sh.tmpl_streak = false;
+    st.tmpl_gen = 0;
+
     // control block: tiles ‖ descs, planned straight into pinned memory
     symrelay_tile *h_tiles = reinterpret_cast<symrelay_tile *>(st.h_ctrl);
     uint32_t n_bulk = 0;
     symrelay_plan_check chk;
     chk.in_bytes = in_bytes; chk.out_bytes = out_bytes; chk.max_streams = ctx->opts.max_streams;
+    chk.uniform_per = chk.uniform_thread = 0;
     // Large batches bound for the DMA pipeline are planned bucketed (plan.h): descriptors sorted by block count
     // on their way into the control block.  The tile area is then sized for the worst case (one tile per frame).
     int64_t n_tiles = -2;
@@ -976,6 +1581,8 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (n_tiles == -2) n_tiles = symrelay_plan_inline(desc, n, h_tiles, ctx->opts.max_batch_frames, &n_bulk, &chk);
     if (n_tiles < 0) return fail(ctx, SYMRELAY_EINVAL, "bad descriptor (alignment or length) in batch");
     PROF_MARK(ctx, 1);
+    const size_t tiles_bytes = bucketed ? bucket_tiles_bytes : align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
+    const size_t ver_off = tiles_bytes + (size_t)n * sizeof(symrelay_desc);   // control block: tiles ‖ descriptors ‖ expected stamps
     // bounds / ownership checks (computed by the planner's first pass over the descriptors)
     uint32_t bad = chk.out_of_bounds;
     const uint32_t any_flags = chk.any_flags, out_overlap = chk.out_overlap;
@@ -987,22 +1594,44 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         // walk enforces the chain rule of the header: at most one frame per (slot, direction) in a batch --
         // a second one would race the first on the nonce chain in HBM and both would "succeed" -- except
         // inbound runs (consecutive F_OPEN|F_RUN descriptors of one slot), and those at most 64 long.
-        const uint8_t *open_slot = ctx->slot_state.data();
-        uint32_t *stamp = sh.slot_stamp.data();
-        if (++sh.stamp == 0u) { std::fill(sh.slot_stamp.begin(), sh.slot_stamp.end(), 0u); sh.stamp = 1u; }
-        const uint32_t now = sh.stamp, runf = SYMRELAY_F_OPEN | SYMRELAY_F_RUN;
+        uint32_t *stamp = sh.slot_stamp.data();   // [slot*2+dir]: stamp of the last batch that named it; SLOT_CLOSED for a slot that is not open
+        if (sh.stamp_dirty) {
+            // the previous batch left its stamp in the table but never ran: let everything in flight finish and
+            // declare all stamps so far settled, so that nobody waits for a stamp that is never written
+            rc = pk_drain_host(ctx, sh);
+            if (rc) return rc;
+            sh.pk_floor = sh.stamp;
+        }
+        sh.stamp_dirty = true;   // until this batch has been posted or launched
+        if (++sh.stamp >= 0xfffffe00u) {   // (once in ~4 billion batches) start the stamps over, with nothing in flight
+            rc = pk_drain_host(ctx, sh);
+            if (rc) return rc;
+            for (uint32_t &v : sh.slot_stamp) v = v == SLOT_CLOSED ? SLOT_CLOSED : 0u;
+            sh.stamp = 1u; sh.pk_floor = 0u;
+        }
+        const uint32_t now = sh.stamp, floor = sh.pk_floor, runf = SYMRELAY_F_OPEN | SYMRELAY_F_RUN;
+        // ver[i]: the stamp frame i's stream state has to carry before the resident kernel may use it = the last
+        // resident-kernel batch that went through that (slot, direction), 0 when that one is long done (stamps up
+        // to pk_floor were followed by an ordinary launch on the same stream).  Collected in cache, then streamed
+        // behind the descriptors in the control block.
+        static thread_local std::vector<uint32_t> verv;
+        if (verv.size() < n) verv.resize(n);
+        uint32_t *ver = verv.data();
         uint32_t closed = 0, dup = 0, run_len = 1, too_long = 0, prev_slot = 0xffffffffu, prev_lf = 0;
         for (uint32_t i = 0; i < n; i++) {
             const uint32_t slot = desc[i].slot, lf = desc[i].len_flags;
-            closed |= (uint32_t)(open_slot[slot] == 0);
             const uint32_t idx = slot * 2u + ((lf >> 26) & 1u);
             const bool cont = slot == prev_slot && (lf & runf) == runf && (prev_lf & runf) == runf;
-            dup |= (uint32_t)(stamp[idx] == now && !cont);
-            stamp[idx] = now;
+            const uint32_t before = stamp[idx];
+            closed |= (uint32_t)(before == SLOT_CLOSED);
+            dup |= (uint32_t)(before == now && !cont);
+            stamp[idx] = before == SLOT_CLOSED ? SLOT_CLOSED : now;
+            ver[i] = before > floor ? pk_version(before) : 0u;
             run_len = cont ? run_len + 1u : 1u;
             too_long |= (uint32_t)(run_len > SS_RUN_MAX);
             prev_slot = slot; prev_lf = lf;
         }
+        nt_copy(st.h_ctrl + ver_off, ver, (size_t)n * 4u);
         if (closed) return fail(ctx, SYMRELAY_ENOENT, "a descriptor names a slot that is not open");
         if (dup) return fail(ctx, SYMRELAY_EINVAL, "two frames of one (slot, direction) in a batch: a stream's frames are MAC-chained, put them in consecutive batches (or mark inbound ones SYMRELAY_F_RUN)");
         if (too_long) return fail(ctx, SYMRELAY_EINVAL, "a run of more than %u SYMRELAY_F_RUN frames of one slot", SS_RUN_MAX);
@@ -1024,9 +1653,9 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         return fail(ctx, SYMRELAY_EINVAL, "SYMRELAY_F_EXTRACT needs delta and delta_arena");
     if (extract && !st.d_delta_arena) CU(ctx, cudaMalloc(&st.d_delta_arena, ctx->opts.stage_bytes));
     if (runs && !st.d_run_nonce) CU(ctx, cudaMalloc(&st.d_run_nonce, (size_t)ctx->opts.max_batch_frames * sizeof(uint4)));
-    const size_t tiles_bytes = bucketed ? bucket_tiles_bytes : align_up((size_t)n_tiles * sizeof(symrelay_tile), 16);
     PROF_MARK(ctx, 2);
-    if (!bucketed) memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
+    if (!bucketed) nt_copy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
+    _mm_sfence();
     st.permuted = bucketed;
     const size_t ctrl_bytes = tiles_bytes + (size_t)n * sizeof(symrelay_desc);
     PROF_MARK(ctx, 3);
@@ -1038,6 +1667,55 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     const bool zero_copy = in_bytes + out_bytes <= ctx->zero_copy_max && is_library_pinned(ctx, in, in_bytes) &&
                            is_library_pinned(ctx, out, out_bytes) &&
                            (!extract || is_library_pinned(ctx, delta_arena, in_bytes < delta_arena_bytes ? in_bytes : delta_arena_bytes));
+    if (zero_copy && ctx->persist && n_bulk == 0 && !extract && !runs && n_tiles > 0 && sh.stages.size() <= PK_RING) {
+        // Packed-tile batches go to the resident kernel: no launch, no grid boundary between consecutive batches.
+        if (sh.pending_wb >= 0) { rc = flush_write_back(ctx, sh, sh.pending_wb); if (rc) return rc; }
+        const uint32_t flags = ctx->stage_input ? SS_ARG_STAGE_INPUT : 0u;   // outputs go to device staging: no PCIe-shaped stores needed
+        PROF_MARK(ctx, 4);
+        rc = pk_post(ctx, sh, st, st.h_ctrl, tiles_bytes, n, (uint32_t)n_tiles, in, out, out_bytes, flags,
+                     chk.uniform_per, chk.uniform_thread, reinterpret_cast<const uint32_t *>(st.h_ctrl + ver_off), pk_version(sh.stamp));
+        if (rc) return rc;
+        sh.stamp_dirty = false;
+        {   // Template bookkeeping.  A cheap checksum decides whether this batch looks like the previous one; only
+            // then are its descriptors kept (a copy per batch would tax traffic that never repeats).
+            const uint64_t *w = reinterpret_cast<const uint64_t *>(desc);
+            uint64_t s0 = n, s1 = 0, s2 = 0, s3 = 0;   // four independent sums: vectorises; memcmp has the last word anyway
+            for (uint32_t i = 0; i + 4u <= 2u * n; i += 4u) { s0 += w[i]; s1 += w[i + 1]; s2 += w[i + 2]; s3 += w[i + 3]; }
+            if (n & 1u) { s0 += w[2u * n - 2u]; s1 += w[2u * n - 1u]; }
+            const uint64_t sum = (s0 * 0x9e3779b97f4a7c15ull) ^ (s1 * 0xc2b2ae3d27d4eb4full) ^ (s2 + (s3 << 1)) ^ 1ull;
+            if (sh.tmpl_gen && sum == sh.tmpl_sum && n == sh.tmpl_n && in_bytes == sh.tmpl_in_bytes && out_bytes == sh.tmpl_out_bytes &&
+                memcmp(desc, sh.tmpl_desc.data(), (size_t)n * sizeof(symrelay_desc)) == 0) {
+                sh.tmpl_streak = true;    // same as the installed template: the next identical batch takes the fast path
+                sh.tmpl_slot_gen = sh.slot_gen;
+                st.tmpl_gen = (tiles_bytes == sh.tmpl_tiles_bytes) ? sh.tmpl_gen : 0;
+            } else if (sum == sh.last_sum) {
+                sh.tmpl_desc.assign(desc, desc + n);
+                sh.tmpl_n = n; sh.tmpl_in_bytes = in_bytes; sh.tmpl_out_bytes = out_bytes; sh.tmpl_sum = sum;
+                sh.tmpl_n_tiles = (uint32_t)n_tiles; sh.tmpl_uni_per = chk.uniform_per; sh.tmpl_uni_thread = chk.uniform_thread;
+                sh.tmpl_flags = flags; sh.tmpl_tiles_bytes = tiles_bytes;
+                sh.tmpl_tiles.assign(st.h_ctrl, st.h_ctrl + (chk.uniform_per ? 0 : (size_t)n_tiles * sizeof(symrelay_tile)));
+                sh.tmpl_gen++;
+                sh.tmpl_slot_gen = sh.slot_gen;
+                sh.tmpl_streak = true;
+                st.tmpl_gen = sh.tmpl_gen;
+            }
+            sh.last_sum = sum;
+        }
+        PROF_MARK(ctx, 5);
+        st.deferred = false;
+        st.wb_by = -1;
+        ctx->prof_n++;
+        ctx->zero_copy_batches++;
+        st.busy = true;
+        st.n = n;
+        st.user_status = status;
+        st.user_delta = nullptr;
+        st.ticket = (seq << 3) | gpu_index;
+        return st.ticket;
+    }
+    pk_quiesce(sh);   // ordinary launches on s_k from here on: whatever the resident kernel was given is settled by stream order
+    sh.pk_floor = sh.stamp;
+    sh.stamp_dirty = false;   // (a failure below leaves stamps behind, but at or below the floor)
     if (zero_copy) {
         // (Copying the control block or the input with cudaMemcpyAsync on the kernel's stream instead was
         // measured and is much worse: 26-36 us per batch against 16 us, small DMA copies have a high fixed cost.)
@@ -1084,6 +1762,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     }
     if (sh.pending_wb >= 0) { rc = flush_write_back(ctx, sh, sh.pending_wb); if (rc) return rc; }
     ctx->staged_batches++;
+    st.dev_tmpl_gen = 0;   // d_ctrl is overwritten
     CU(ctx, cudaMemcpyAsync(st.d_ctrl, st.h_ctrl, ctrl_bytes, cudaMemcpyHostToDevice, sh.s_in));
     if (in_bytes) CU(ctx, cudaMemcpyAsync(st.d_in, in, in_bytes, cudaMemcpyHostToDevice, sh.s_in));
     CU(ctx, cudaEventRecord(st.ev_in, sh.s_in));
@@ -1162,6 +1841,7 @@ int symrelay_probe_int_peak(symrelay_ctx *ctx, int gpu_index, double *arx_tops, 
     std::lock_guard<std::mutex> lk(ctx->mu);
     Shard &sh = ctx->shard[gpu_index];
     CU(ctx, set_device(sh.dev));
+    pk_quiesce(sh);
     uint32_t *d_out = reinterpret_cast<uint32_t *>(sh.d_init);  // never written in practice
     cudaEvent_t e0, e1;
     CU(ctx, cudaEventCreate(&e0));

@@ -81,16 +81,25 @@ def test_open_side_and_host_rejections(relay):
     for f in frames:
         msgs.append(mirror.open_frame(f)[0])
     tickets = []
+    import symmetry_b200 as sb
+
+    res = {}
     for f in frames:
         tickets.append(relay.submit_open(slot, f))
-        relay.flush()
+        while True:
+            try:
+                relay.flush()
+                break
+            except sb.RelayError as e:      # every pipeline stage holds an unfinished batch: drain one and retry
+                assert e.code == sb.relay.EAGAIN
+                for c in relay.poll(wait=True):
+                    res[c["ticket"]] = c
     tickets.append(relay.submit_open(slot, b"\x05\x00\x00abcde"))            # < 17 bytes after the prefix
     tickets.append(relay.submit_open(slot, b"\x30\x00\x00" + bytes(30)))      # prefix disagrees with the length
     forged = bytearray(peer.seal_frame(b"forged?"))
     forged[10] ^= 1
     tickets.append(relay.submit_open(slot, bytes(forged)))
     relay.flush()
-    res = {}
     while len(res) < len(tickets):
         for c in relay.poll(wait=True):
             res[c["ticket"]] = c
