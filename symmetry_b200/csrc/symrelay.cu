@@ -271,30 +271,48 @@ __device__ void pk_poller(PkHost *host, PkDev *dev, unsigned long long first_seq
             pk_fence_sys();   // acquire: what the host wrote before the doorbell (headers, control blocks, payload)
             const unsigned long long t_seen = pk_now();
             while (installed < db) {
-                const PkSlot *hs = &host->slot[installed % PK_RING];
-                PkEntry *e = &dev->e[installed % PK_RING];
-                // plain loads (ordered by the acquire fence above): volatile ones would go out one after the other
-                const uint4 *hq = reinterpret_cast<const uint4 *>(hs);
-                const uint4 a = hq[0], b = hq[1], c = hq[2], d = hq[3], f = hq[4], g = hq[5], h = hq[6];
-                const unsigned long long n_tiles = c.w;   // PkSlot::n_tiles
-                const unsigned long long n_chunks = ((unsigned long long)d.w * 16ull + PK_CHUNK - 1u) / PK_CHUNK +
-                                                    ((unsigned long long)c.z * 4ull + PK_CHUNK - 1u) / PK_CHUNK;   // out arena + status words
-                if (lane == 0) {
+                // Lane L installs batch installed + L: the headers of everything new are read at once (one PCIe round
+                // trip, not one per batch -- under load a round trip is 5-10 us and eight batches queued up cost 37 us).
+                const unsigned long long m = db - installed < 32ull ? db - installed : 32ull;
+                const bool mine = lane < m;
+                const unsigned long long my_seq = installed + lane;
+                uint4 q[7];
+#pragma unroll
+                for (int i = 0; i < 7; i++) q[i] = make_uint4(0, 0, 0, 0);
+                if (mine) {
+                    const uint4 *hq = reinterpret_cast<const uint4 *>(&host->slot[my_seq % PK_RING]);   // plain loads, ordered by the acquire fence above
+#pragma unroll
+                    for (int i = 0; i < 7; i++) q[i] = hq[i];
+                }
+                const unsigned long long n_tiles = mine ? q[2].w : 0u;   // PkSlot::n_tiles
+                const unsigned long long n_chunks = mine ? ((unsigned long long)q[3].w * 16ull + PK_CHUNK - 1u) / PK_CHUNK +
+                                                               ((unsigned long long)q[2].z * 4ull + PK_CHUNK - 1u) / PK_CHUNK : 0u;   // out arena + status words
+                unsigned long long it = n_tiles, ic = n_chunks;   // inclusive prefix sums over the lanes
+#pragma unroll
+                for (uint32_t o = 1; o < 32u; o <<= 1) {
+                    const unsigned long long a = __shfl_up_sync(0xffffffffu, it, o), c = __shfl_up_sync(0xffffffffu, ic, o);
+                    if (lane >= o) { it += a; ic += c; }
+                }
+                PkEntry *e = &dev->e[my_seq % PK_RING];
+                if (mine) {
                     uint4 *es = reinterpret_cast<uint4 *>(&e->s);
-                    es[0] = a; es[1] = b; es[2] = c; es[3] = d; es[4] = f; es[5] = g; es[6] = h;
-                    e->seq = installed;
+#pragma unroll
+                    for (int i = 0; i < 7; i++) es[i] = q[i];
+                    e->seq = my_seq;
                     e->done = 0; e->sysdone = 0;
                     if (ts) {
-                        unsigned long long *w = ts + (installed % 4096ull) * PK_TS_WORDS;
+                        unsigned long long *w = ts + (my_seq % 4096ull) * PK_TS_WORDS;
                         w[0] = t_seen; w[8] = w[9] = w[10] = w[11] = w[12] = w[13] = 0;
                     }
-                    pk_fence_gpu();
-                    *reinterpret_cast<volatile unsigned long long *>(&e->drange) = (dcum << 24) | n_chunks;
-                    *reinterpret_cast<volatile unsigned long long *>(&e->range) = (cum << 24) | n_tiles;
                 }
-                cum += n_tiles;
-                dcum += n_chunks;
-                installed++;
+                pk_fence_gpu();   // fields before the range words
+                if (mine) {
+                    *reinterpret_cast<volatile unsigned long long *>(&e->drange) = ((dcum + ic - n_chunks) << 24) | n_chunks;
+                    *reinterpret_cast<volatile unsigned long long *>(&e->range) = ((cum + it - n_tiles) << 24) | n_tiles;
+                }
+                cum += __shfl_sync(0xffffffffu, it, 31);
+                dcum += __shfl_sync(0xffffffffu, ic, 31);
+                installed += m;
             }
             __syncwarp();
             pk_fence_gpu();   // release: one fence, then relaxed stores of the copies (a st.release each would fence each time)
@@ -616,6 +634,7 @@ struct Shard {
     PkHost *pk_host = nullptr;             // mapped pinned: doorbell, state, completion flags, batch headers
     PkDev *pk_dev = nullptr;
     uint64_t pk_posted = 0;                // batches posted so far
+    int pk_grid = 0;                       // CTAs of the resident grid (all co-resident)
     unsigned long long *d_pk_ts = nullptr; // SYMRELAY_TS=1: PK_TS_WORDS stamps per batch, 4096 batches round-robin
     bool pk_quit_req = false;              // the kernel was asked to exit because ordinary launches follow on s_k
     uint32_t pk_floor = 0;                 // batch stamps up to here are settled (an ordinary launch on s_k followed them)
@@ -959,9 +978,17 @@ static void shard_free(Shard &sh) {
                     (unsigned long long)cnt, pre / cnt * 1e-3, wait / cnt * 1e-3, post / cnt * 1e-3, period / cnt * 1e-3, lead / cnt * 1e-3);
     }
     cudaFree(sh.d_ts);
-    if (sh.d_pk_ts && sh.pk_posted > 64) {   // diagnostics: where a batch spends its time inside the resident kernel
+    if (sh.d_pk_ts && sh.pk_posted > 8) {   // diagnostics: where a batch spends its time inside the resident kernel
         std::vector<unsigned long long> ts(4096u * PK_TS_WORDS);
         cudaMemcpy(ts.data(), sh.d_pk_ts, ts.size() * 8u, cudaMemcpyDeviceToHost);
+        if (const char *path = getenv("SYMRELAY_TS_DUMP")) {   // raw stamps of the last 4096 batches, for offline analysis
+            if (FILE *f = fopen(path, "wb")) {
+                const unsigned long long hdr[2] = {sh.pk_posted, PK_TS_WORDS};
+                fwrite(hdr, 8, 2, f);
+                fwrite(ts.data(), 8, ts.size(), f);
+                fclose(f);
+            }
+        }
         const uint64_t last = sh.pk_posted - 1, first = last >= 2048 ? last - 2047 : 1;
         double d[8] = {0, 0, 0, 0, 0, 0, 0, 0}, m[6] = {0, 0, 0, 0, 0, 0}, mm[4] = {0, 0, 0, 0};
         uint64_t cnt = 0;
@@ -1355,13 +1382,17 @@ static int pk_launch(symrelay_ctx *ctx, Shard &sh, uint64_t first_seq) {
     // Resident CTAs per SM: a warp is held from its tile's first PCIe read until its results have been fenced to the
     // host (~15 us), of which ~4 us compute; with one CTA per SM the batches behind the one that computes cannot all
     // prefetch.  Never more CTAs than fit at once: every warp of the grid must be able to run (they wait on each other).
-    int sms = 148, per_sm = 1;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, sh.dev);
-    CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ss_persistent_kernel, 128, 0));
-    if (per_sm > (int)ctx->pk_ctas_per_sm) per_sm = (int)ctx->pk_ctas_per_sm;
-    if (per_sm < 1) per_sm = 1;
-    sms *= per_sm;
-    if (sms > (int)PK_MAX_CTAS) sms = (int)PK_MAX_CTAS;
+    if (!sh.pk_grid) {
+        int sms = 148, per_sm = 1;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, sh.dev);
+        CU(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ss_persistent_kernel, 128, 0));
+        if (per_sm > (int)ctx->pk_ctas_per_sm) per_sm = (int)ctx->pk_ctas_per_sm;
+        if (per_sm < 1) per_sm = 1;
+        sms *= per_sm;
+        if (sms > (int)PK_MAX_CTAS) sms = (int)PK_MAX_CTAS;
+        sh.pk_grid = sms;
+    }
+    const int sms = sh.pk_grid;
     ss_persistent_kernel<<<(unsigned)sms, 128, 0, sh.s_k>>>(sh.pk_host, sh.pk_dev, sh.d_states, (unsigned long long)first_seq,
                                                             (unsigned long long)ctx->pk_idle_ns, sh.d_pk_ts, ctx->pk_drain_every);
     ctx->launches++;

@@ -1,7 +1,5 @@
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
-for d in 12; do
-echo "== depth $d"
-BENCH_E2E_DEPTH=$d BENCH_SYNC_LAT=0 SYMRELAY_TS=1 SYMRELAY_PROF=1 timeout 300 python bench.py --steps 3000 --warmup 20 --sub none --no-latency --no-cpu 2>gpurun_out/b19_$d.err >gpurun_out/b19_$d.json; grep -E "resident|profile|latest|chain" gpurun_out/b19_$d.err
-done
-echo "== sync"
-SYMRELAY_TS=1 SYMRELAY_PROF=1 timeout 300 python bench.py --steps 20 --warmup 5 --sub none --no-latency --no-cpu 2>gpurun_out/b19s.err >gpurun_out/b19s.json; grep -E "resident|profile|latest|chain" gpurun_out/b19s.err
+for c in "1 4" "2 4" "3 4" "2 6" "3 8"; do set -- $c
+for k in 20 3000; do
+echo "== ctas/sm $1 drain_every $2 steps $k"
+SYMRELAY_PERSIST_CTAS_PER_SM=$1 SYMRELAY_PERSIST_DRAIN_EVERY=$2 BENCH_SYNC_LAT=0 timeout 300 python bench.py --steps $k --warmup 5 --sub none --no-latency --no-cpu 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['e2e']['value']/1e6, d['e2e']['ms_per_step']*1e3)"
+done; done
