@@ -38,7 +38,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 L2_BYTES = 126 << 20
 METRIC = "sealed_frames_per_sec"
 DEFAULT_STEPS = {"c2": 20000, "c3": 200, "c4": 64, "c5": 360, "c1": 20, "c4sweep": 8}
-SUB_STEPS = {"c4": 24, "c3": 120}          # steps of the sub-lines riding on the default line
+SUB_STEPS = {"c4": 64, "c3": 200}          # steps of the sub-lines riding on the default line
 
 
 # ------------------------------------------------------------------ workload --
@@ -258,8 +258,9 @@ def run_reference(args):
     steps = min(args.steps, max_steps)
     # The pool warms up on the same threads before the timed steps; a short timed region (the driver's
     # --steps 20 is about a millisecond of CPU work) needs more warm-up than --warmup to reach the steady
-    # state the long cpu_baseline sample of the other arm measures, so warm for at least ~50 ms.
-    warm = max(args.warmup, min(max_steps, int(0.05 / max(probe / 2, 1e-9))))
+    # state the long cpu_baseline sample of the other arm measures (idle cores take tens of milliseconds to reach
+    # their working clocks), so warm for at least ~0.3 s.
+    warm = max(args.warmup, min(max_steps, int(0.3 / max(probe / 2, 1e-9))))
     sec, kind = cpu_run(lens, steps, warm, threads)
     frames = len(lens) * steps
     val = frames / sec
