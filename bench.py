@@ -904,6 +904,8 @@ def main():
     ap.add_argument("--py-e2e", action="store_true", help="drive the e2e loop from Python instead of tools/e2e_driver.c")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (huge workloads)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step directly (no CUDA graph)")
+    ap.add_argument("--single-process", action="store_true",
+                    help="with --gpus N (no torchrun): one process, one thread, one context over N GPUs; end-to-end leg only")
     args = ap.parse_args()
     if args.steps is None:   # a step of c3/c4/c5 is 10-400x a step of c2
         args.steps = DEFAULT_STEPS.get(args.workload, 20000)
@@ -913,6 +915,10 @@ def main():
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.single_process:
+        import bench_extra
+
+        bench_extra.run_single_process(args)
     elif args.workload == "c5":
         run_c5(args)
     elif args.workload == "c1":

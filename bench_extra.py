@@ -179,3 +179,112 @@ def run_c4_sweep(args):
     }
     print(json.dumps(line), flush=True)
     job.close()
+
+
+def run_single_process(args):
+    """--single-process --gpus N: ONE process, ONE thread, one context over N GPUs -- the reference's own shape (one
+    Node process, src/provider.ts:37-58).  Streams are sharded slot % N inside the context; the
+    thread visits the GPUs round-robin through symrelay_batch_submit/_wait (tools/e2e_driver.c).  Prints the e2e
+    figure as `value` too: there is no device-resident leg in this mode."""
+    import torch
+
+    import symmetry_b200 as sb
+    from oracle import libsodium as ls
+    from symmetry_b200 import build as sbuild
+    from symmetry_b200 import synth
+
+    N = args.gpus
+    assert torch.cuda.device_count() >= N, f"needs {N} GPUs"
+    name = args.workload if args.workload in ("c2", "c3", "c4") else "c2"
+    K, W = args.steps, max(args.warmup, 3)
+    D = int(os.environ.get("BENCH_E2E_DEPTH", "12"))
+    per = []
+    total = 0
+    for g in range(N):
+        lens, desc_txt, scaling, first = B.workload(name, N, g)
+        per.append({"lens": lens, "lay": B.Layout(lens), "first": first})
+        total += len(lens)
+    stage_bytes = max(64 << 20, max((p["lay"].in_bytes + 4095) // 4096 * 4096 for p in per))
+    relay = sb.SymRelay(gpu_ids=tuple(range(N)), max_streams=max(4 * total, 4096), pipeline_depth=D, stage_bytes=stage_bytes,
+                        max_batch_frames=max(2 * max(len(p["lens"]) for p in per), 4096))
+    # open all streams, then give GPU g the slots that landed on it (slot % N == g)
+    keys, hdrs = synth.stream_keys(total)
+    slots = relay.open_streams(keys, hdrs, keys, hdrs)
+    by_gpu = [[i for i in range(total) if int(slots[i]) % N == g] for g in range(N)]
+    R2 = max(2 * D + 2, 8)
+    descs, rings, stats, samples = [], [], [], []
+    for g in range(N):
+        idx = by_gpu[g][: len(per[g]["lens"])]
+        assert len(idx) == len(per[g]["lens"]), "slots did not spread evenly over the GPUs"
+        lay = per[g]["lay"]
+        descs.append(np.ascontiguousarray(lay.descs(slots[idx], True)))
+        ring = relay.alloc_pinned(R2 * lay.slot_bytes)
+        ring[:] = np.random.default_rng(500 + g).integers(0, 256, ring.size, dtype=np.uint8)
+        rings.append(ring)
+        stats.append(np.full(R2 * 2 * len(idx), 0xFF, dtype=np.uint32))
+        samples.append([(0, idx[0]), (len(idx) - 1, idx[-1])])
+        per[g]["idx"] = idx
+        per[g]["plain"] = {j: [bytes(ring[r * lay.slot_bytes + int(lay.p_offs[j]): r * lay.slot_bytes + int(lay.p_offs[j]) + int(lay.lens[j])])
+                               for r in range(R2)] for j, _ in samples[g]}
+    drv = C.CDLL(sbuild.build_driver())
+    drv.e2e_ring_run_multi.restype = C.c_double
+    PP, U32, U64 = C.c_void_p * N, C.c_uint32 * N, C.c_uint64 * N
+    drv.e2e_ring_run_multi.argtypes = [C.c_void_p, C.c_int, PP, U32, PP, U64, U64, U64, U64, C.c_uint32, C.c_uint32, C.c_uint64,
+                                       C.c_uint32, PP]
+
+    def go(first_step, steps):
+        return drv.e2e_ring_run_multi(
+            relay.ctx, N, PP(*[d.ctypes.data for d in descs]), U32(*[len(d) for d in descs]), PP(*[r.ctypes.data for r in rings]),
+            U64(*[p["lay"].slot_bytes for p in per]), U64(*[p["lay"].in_bytes for p in per]), U64(*[p["lay"].P for p in per]),
+            U64(*[p["lay"].out_bytes for p in per]), R2, D, first_step, steps, PP(*[s.ctypes.data for s in stats]))
+
+    # priming: the first D steps seal only (no inbound frames exist yet), as in bench.py
+    seal_descs = [np.ascontiguousarray(p["lay"].descs(slots[p["idx"]], False)) for p in per]
+    full = descs
+    descs = seal_descs
+    for s in stats:
+        s[:] = 0xFF
+    step = 0
+    assert go(step, D) > 0
+    step += D
+    descs = full
+    assert go(step, W) > 0
+    step += W
+    clocks = B.ClockSampler(0)
+    tw0 = time.perf_counter()
+    secs = go(step, K)
+    tw1 = time.perf_counter()
+    assert secs > 0, f"driver failed: {secs} {relay.lib.symrelay_last_error(relay.ctx)}"
+    step += K
+    clk = clocks.stop([(tw0, tw1)])
+    for g in range(N):
+        n_g = len(per[g]["idx"])
+        st = stats[g].reshape(R2, 2 * n_g)
+        for i in range(step - K, step):
+            assert (st[i % R2] == 0).all(), f"non-OK status on GPU {g}"
+        lay = per[g]["lay"]
+        for j, gi in samples[g]:
+            ref = ls.State(bytes(keys[gi]), bytes(hdrs[gi]))
+            for i in range(step):
+                w = ref.seal_frame(per[g]["plain"][j][i % R2])
+            assert relay.export(int(slots[gi]))[0] == ref.raw, f"tx chain of a stream on GPU {g} differs from libsodium"
+            o = ((step - 1 + D) % R2) * lay.slot_bytes + lay.P + int(lay.w_offs[j])
+            assert bytes(rings[g][o:o + len(w)]) == w
+    frames = sum(len(p["lens"]) for p in per)
+    val = frames * K / secs
+    lay0 = per[0]["lay"]
+    line = {
+        "metric": B.METRIC, "value": val, "unit": "frames/s", "n_gpus": N, "steps": K, "warmup": W, "ms_per_step": secs / K * 1e3,
+        "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": dict(B.make_config(name, N, K, True, B.plan_mode_for(name)),
+                       mode="single process, single thread, one context over all GPUs (tools/e2e_driver.c e2e_ring_run_multi)"),
+        "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": int(sum(p["lay"].in_bytes + 2 * len(p["lens"]) * 16 for p in per)),
+                "d2h_bytes_per_step": int(sum(p["lay"].out_bytes + 2 * len(p["lens"]) * 4 for p in per)), "steps": K,
+                "ms_per_step": secs / K * 1e3,
+                "path": f"symrelay_batch_submit/wait on pinned host arenas, {N} GPUs visited round-robin by one thread, depth {D}"},
+        "note": "value repeats e2e: this mode has no device-resident leg (run without --single-process for it)",
+        "gpu_launches": relay.launches, "clocks": clk,
+        "parity": "statuses all OK; sampled tx chains and last wire frames == libsodium on every GPU",
+    }
+    print(json.dumps(line), flush=True)
+    relay.close()

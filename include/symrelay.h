@@ -302,6 +302,14 @@ SYMRELAY_API int symrelay_flush(symrelay_ctx *ctx);
 SYMRELAY_API int symrelay_poll(symrelay_ctx *ctx, symrelay_completion *out, int max);
 SYMRELAY_API int symrelay_poll_wait(symrelay_ctx *ctx, symrelay_completion *out, int max);
 SYMRELAY_API int symrelay_release(symrelay_ctx *ctx, int64_t ticket);
+/* Completion wake-up for an event loop.  The reference is woken by libuv when its sockets have something for it
+ * (`peer.on('data')`, 'drain': src/provider.ts:174, :250-252) and never polls; SURVEY.md 8(b) asks the same of this
+ * boundary.  Returns an eventfd (owned by the context, closed by symrelay_destroy) that becomes readable whenever a
+ * batch of the per-frame front end has finished: read the 8-byte counter, then call symrelay_poll, which delivers
+ * the completions without waiting.  The first call starts one watcher thread for the context; that thread also
+ * performs the deadline flushes (opts.sched_flush_us), so an idle loop need not call symrelay_poll for them.
+ * The N-API shim hands the descriptor to uv_poll_init. */
+SYMRELAY_API int symrelay_event_fd(symrelay_ctx *ctx);
 /* frames/batches handled by the front end and the p50/p99/p99.9 of their added latency */
 SYMRELAY_API int symrelay_sched_stats(symrelay_ctx *ctx, symrelay_sched_stats_t *out);
 SYMRELAY_API int symrelay_sched_reset_stats(symrelay_ctx *ctx);

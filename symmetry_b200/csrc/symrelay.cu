@@ -11,6 +11,10 @@
 #include <emmintrin.h>
 
 #include <atomic>
+#include <condition_variable>
+#include <thread>
+#include <sys/eventfd.h>
+#include <unistd.h>
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
@@ -626,6 +630,7 @@ struct Stage {
 };
 
 struct Shard {
+    std::mutex mu;                         // everything below and this GPU's Sched: one lock per GPU, none shared between GPUs
     int dev = -1;
     uint4 *d_states = nullptr;
     uint4 *d_sx_fast = nullptr;            // extractor tables (SX_TABLES_BYTES), allocated last in shard_init
@@ -679,11 +684,23 @@ struct symrelay_ctx {
     symrelay_opts opts{};
     std::vector<uint8_t> slot_state;      // 0 free, 1 open
     std::vector<uint32_t> free_slots[8];  // per GPU (slot % n_gpus == gpu)
-    std::mutex mu;
+    std::mutex mu;        // the slot table (slot_state, free_slots) only; taken before a shard's lock, never after
+    std::mutex err_mu;    // err
+    std::mutex pin_mu;    // writers of pins[] (leaf lock)
+    // Completion wake-up (symrelay_event_fd): one watcher thread per context, started on first use
+    int evfd = -1;
+    std::thread watcher;
+    std::atomic<bool> watcher_stop{false};
+    std::atomic<uint32_t> watcher_work{0};   // bumped by the front end whenever a frame is accepted or a batch goes out
+    std::mutex watch_mu;
+    std::condition_variable watch_cv;
     std::string err;
     std::atomic<uint64_t> launches{0};
     int64_t ticket_counter = 0;
-    std::vector<std::pair<uintptr_t, uint64_t>> pinned;   // arenas handed out by symrelay_alloc_pinned
+    // arenas handed out by symrelay_alloc_pinned (and the front end's own): read without a lock on every batch
+    struct Pin { std::atomic<uintptr_t> base{0}; std::atomic<uint64_t> bytes{0}; };
+    Pin pins[2048];
+    std::atomic<uint32_t> n_pins{0};
     uint64_t zero_copy_max = 1ull << 20;                   // in+out bytes up to which a batch runs zero-copy
     uint64_t zero_copy_batches = 0, staged_batches = 0;
     bool pdl = true;   // SYMRELAY_PDL=0 turns programmatic dependent launch off
@@ -720,9 +737,33 @@ static inline double prof_now() {
 
 static bool is_library_pinned(const symrelay_ctx *ctx, const void *p, uint64_t bytes) {
     const uintptr_t a = reinterpret_cast<uintptr_t>(p);
-    for (const auto &r : ctx->pinned)
-        if (a >= r.first && a + bytes <= r.first + r.second) return true;
+    const uint32_t n = ctx->n_pins.load(std::memory_order_acquire);
+    for (uint32_t i = 0; i < n; i++) {
+        const uintptr_t base = ctx->pins[i].base.load(std::memory_order_relaxed);
+        if (base && a >= base && a + bytes <= base + ctx->pins[i].bytes.load(std::memory_order_relaxed)) return true;
+    }
     return false;
+}
+static bool pin_add(symrelay_ctx *ctx, void *p, uint64_t bytes) {
+    std::lock_guard<std::mutex> lk(ctx->pin_mu);
+    const uint32_t n = ctx->n_pins.load(std::memory_order_relaxed);
+    uint32_t at = n;
+    for (uint32_t i = 0; i < n; i++)
+        if (!ctx->pins[i].base.load(std::memory_order_relaxed)) { at = i; break; }
+    if (at >= 2048u) return false;
+    ctx->pins[at].bytes.store(bytes, std::memory_order_relaxed);
+    ctx->pins[at].base.store(reinterpret_cast<uintptr_t>(p), std::memory_order_release);
+    if (at == n) ctx->n_pins.store(n + 1u, std::memory_order_release);
+    return true;
+}
+static void pin_remove(symrelay_ctx *ctx, void *p) {
+    std::lock_guard<std::mutex> lk(ctx->pin_mu);
+    const uint32_t n = ctx->n_pins.load(std::memory_order_relaxed);
+    for (uint32_t i = 0; i < n; i++)
+        if (ctx->pins[i].base.load(std::memory_order_relaxed) == reinterpret_cast<uintptr_t>(p)) {
+            ctx->pins[i].base.store(0, std::memory_order_release);
+            break;
+        }
 }
 
 static thread_local char g_err[256];
@@ -733,7 +774,7 @@ static int fail(symrelay_ctx *ctx, int code, const char *fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(buf, sizeof buf, fmt, ap);
     va_end(ap);
-    if (ctx) ctx->err = buf;
+    if (ctx) { std::lock_guard<std::mutex> lk(ctx->err_mu); ctx->err = buf; }
     snprintf(g_err, sizeof g_err, "%s", buf);
     return code;
 }
@@ -885,7 +926,13 @@ const char *symrelay_strerror(int code) {
     }
 }
 
-const char *symrelay_last_error(symrelay_ctx *ctx) { return ctx ? ctx->err.c_str() : g_err; }
+const char *symrelay_last_error(symrelay_ctx *ctx) {
+    if (ctx) {   // a copy for this thread: another thread's failure may replace the context's string at any time
+        std::lock_guard<std::mutex> lk(ctx->err_mu);
+        snprintf(g_err, sizeof g_err, "%s", ctx->err.c_str());
+    }
+    return g_err;
+}
 
 uint64_t symrelay_launch_count(symrelay_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
 
@@ -1092,7 +1139,6 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
             return nullptr;
         }
         if (shard_init(ctx, ctx->shard[g], gpu_ids[g]) != 0) {
-            snprintf(g_err, sizeof g_err, "%s", ctx->err.c_str());
             symrelay_destroy(ctx);
             return nullptr;
         }
@@ -1106,6 +1152,12 @@ static void sched_free(symrelay_ctx *ctx, int g);
 
 void symrelay_destroy(symrelay_ctx *ctx) {
     if (!ctx) return;
+    if (ctx->watcher.joinable()) {
+        ctx->watcher_stop = true;
+        { std::lock_guard<std::mutex> lk(ctx->watch_mu); ctx->watch_cv.notify_all(); }
+        ctx->watcher.join();
+    }
+    if (ctx->evfd >= 0) close(ctx->evfd);
     if (ctx->prof && ctx->prof_n) {
         const char *names[8] = {"recycle", "plan", "checks", "ctrl copy", "launch", "event record", "wait", ""};
         fprintf(stderr, "symrelay host batch profile over %llu batches (us per batch):", (unsigned long long)ctx->prof_n);
@@ -1170,15 +1222,16 @@ int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_
         slots_out[i] = ctx->free_slots[g].back();
         ctx->free_slots[g].pop_back();
         ctx->slot_state[slots_out[i]] = 1;
-        sched_slot_reset(ctx, slots_out[i]);
-        stamp_reset(ctx, slots_out[i], true);
         g = (g + 1) % ctx->n_gpus;
     }
     for (int gi = 0; gi < ctx->n_gpus; gi++) {
         Shard &sh = ctx->shard[gi];
+        std::lock_guard<std::mutex> slk(sh.mu);
         uint32_t fill = 0;
         for (uint32_t i = 0; i < n; i++) {
             if ((int)(slots_out[i] % (uint32_t)ctx->n_gpus) != gi) continue;
+            sched_slot_reset(ctx, slots_out[i]);
+            stamp_reset(ctx, slots_out[i], true);
             fill_rec(&sh.h_init[fill++], slots_out[i], 0, tx_keys ? tx_keys + 32ull * i : nullptr,
                      tx_inits ? tx_inits + (size_t)init_len * i : nullptr, init_len, (uint32_t)provider_kind);
             fill_rec(&sh.h_init[fill++], slots_out[i], 1, rx_keys ? rx_keys + 32ull * i : nullptr,
@@ -1213,9 +1266,10 @@ int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, const uint8_t
     const uint32_t slot = ctx->free_slots[g].back();
     ctx->free_slots[g].pop_back();
     ctx->slot_state[slot] = 1;
+    Shard &sh = ctx->shard[g];
+    std::lock_guard<std::mutex> slk(sh.mu);
     sched_slot_reset(ctx, slot);
     stamp_reset(ctx, slot, true);
-    Shard &sh = ctx->shard[g];
     fill_rec(&sh.h_init[0], slot, 0, tx_key, tx_init, tx_init_len, (uint32_t)provider_kind);
     fill_rec(&sh.h_init[1], slot, 1, rx_key, rx_init, rx_init_len, (uint32_t)provider_kind);
     int rc = push_init_recs(ctx, sh, 2);
@@ -1228,9 +1282,10 @@ int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot) {
     if (!ctx) return SYMRELAY_EINVAL;
     std::lock_guard<std::mutex> lk(ctx->mu);
     if (slot >= ctx->opts.max_streams || !ctx->slot_state[slot]) return fail(ctx, SYMRELAY_ENOENT, "slot %u not open", slot);
+    Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
+    std::lock_guard<std::mutex> slk(sh.mu);
     if (sched_slot_busy(ctx, slot))
         return fail(ctx, SYMRELAY_EAGAIN, "slot %u still has frames in a batch that is filling or in flight: flush, poll, then close", slot);
-    Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
     fill_rec(&sh.h_init[0], slot, 0, nullptr, nullptr, 0, 0);
     fill_rec(&sh.h_init[1], slot, 1, nullptr, nullptr, 0, 0);
     int rc = push_init_recs(ctx, sh, 2);  // wipes the key material on the device
@@ -1245,9 +1300,9 @@ int symrelay_stream_close(symrelay_ctx *ctx, uint32_t slot) {
 int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_t tx_state[SYMRELAY_STATEBYTES],
                            uint8_t rx_state[SYMRELAY_STATEBYTES]) {
     if (!ctx) return SYMRELAY_EINVAL;
-    std::lock_guard<std::mutex> lk(ctx->mu);
     if (slot >= ctx->opts.max_streams || !ctx->slot_state[slot]) return fail(ctx, SYMRELAY_ENOENT, "slot %u not open", slot);
     Shard &sh = ctx->shard[slot % (uint32_t)ctx->n_gpus];
+    std::lock_guard<std::mutex> lk(sh.mu);
     CU(ctx, set_device(sh.dev));
     for (Stage &st : sh.stages) {   // "live" means after every host batch submitted so far
         const int rc = finish_stage(ctx, sh, st);
@@ -1826,18 +1881,18 @@ int64_t symrelay_batch_submit(symrelay_ctx *ctx, const symrelay_desc *desc, uint
                               uint64_t in_bytes, uint8_t *out, uint64_t out_bytes, uint32_t *status,
                               symrelay_delta *delta, uint8_t *delta_arena, uint64_t delta_arena_bytes) {
     if (!ctx || !desc || n == 0 || !in || !out) return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_submit: null/empty argument");
-    std::lock_guard<std::mutex> lk(ctx->mu);
     const int gpu_index = (int)(desc[0].slot % (uint32_t)ctx->n_gpus);
+    std::lock_guard<std::mutex> lk(ctx->shard[gpu_index].mu);
     return submit_locked(ctx, gpu_index, desc, n, in, in_bytes, out, out_bytes, status, delta, delta_arena,
                          delta_arena_bytes, /*may_defer=*/true);
 }
 
 int symrelay_batch_wait(symrelay_ctx *ctx, int64_t ticket) {
     if (!ctx || ticket < 0) return SYMRELAY_EINVAL;
-    std::lock_guard<std::mutex> lk(ctx->mu);
     const int gpu_index = (int)(ticket & 7);
     if (gpu_index >= ctx->n_gpus) return fail(ctx, SYMRELAY_ENOENT, "bad ticket");
     Shard &sh = ctx->shard[gpu_index];
+    std::lock_guard<std::mutex> lk(sh.mu);
     const int64_t seq = ticket >> 3;
     if (seq >= sh.next_ticket_seq) return fail(ctx, SYMRELAY_ENOENT, "ticket not issued");
     Stage &st = sh.stages[(size_t)(seq % (int64_t)sh.stages.size())];
@@ -1857,7 +1912,7 @@ int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n
     if (!ctx || !desc || !in || !out) return fail(ctx, SYMRELAY_EINVAL, "symrelay_batch_host: null argument");
     int64_t t;
     {   // a synchronous caller waits for this very batch: let the kernel write to the host itself
-        std::lock_guard<std::mutex> lk(ctx->mu);
+        std::lock_guard<std::mutex> lk(ctx->shard[desc[0].slot % (uint32_t)ctx->n_gpus].mu);
         t = submit_locked(ctx, (int)(desc[0].slot % (uint32_t)ctx->n_gpus), desc, n, in, in_bytes, out, out_bytes, status,
                           delta, delta_arena, delta_arena_bytes, /*may_defer=*/false);
     }
@@ -1869,8 +1924,8 @@ int symrelay_batch_host(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n
 
 int symrelay_probe_int_peak(symrelay_ctx *ctx, int gpu_index, double *arx_tops, double *imad_tops) {
     if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
-    std::lock_guard<std::mutex> lk(ctx->mu);
     Shard &sh = ctx->shard[gpu_index];
+    std::lock_guard<std::mutex> lk(sh.mu);
     CU(ctx, set_device(sh.dev));
     pk_quiesce(sh);
     uint32_t *d_out = reinterpret_cast<uint32_t *>(sh.d_init);  // never written in practice
@@ -1912,18 +1967,17 @@ void *symrelay_alloc_pinned(symrelay_ctx *ctx, uint64_t bytes) {
         fail(ctx, SYMRELAY_ENOMEM, "cudaHostAlloc(%llu) failed", (unsigned long long)bytes);
         return nullptr;
     }
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    ctx->pinned.emplace_back(reinterpret_cast<uintptr_t>(p), bytes);
+    if (!pin_add(ctx, p, bytes)) {
+        cudaFreeHost(p);
+        fail(ctx, SYMRELAY_ENOMEM, "too many pinned arenas (2048)");
+        return nullptr;
+    }
     return p;
 }
 
 void symrelay_free_pinned(symrelay_ctx *ctx, void *p) {
     if (!p) return;
-    if (ctx) {
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        for (size_t i = 0; i < ctx->pinned.size(); i++)
-            if (ctx->pinned[i].first == reinterpret_cast<uintptr_t>(p)) { ctx->pinned.erase(ctx->pinned.begin() + (long)i); break; }
-    }
+    if (ctx) pin_remove(ctx, p);
     cudaFreeHost(p);
 }
 

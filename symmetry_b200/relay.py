@@ -207,6 +207,11 @@ class SymRelay:
             self._check(n)
         return [tick[i] for i in range(max(n, 0))], used.value
 
+    def event_fd(self) -> int:
+        """eventfd that becomes readable when a batch of the per-frame front end has finished (what the N-API shim
+        gives to uv_poll); starts the context's watcher thread on first use."""
+        return self._check(self.lib.symrelay_event_fd(self.ctx))
+
     def flush(self) -> None:
         self._check(self.lib.symrelay_flush(self.ctx))
 

@@ -209,6 +209,41 @@ def test_deadline_flush_and_latency_stats():
         assert st["frames"] == 1000 and 0 < st["p50_us"] < 50000 and st["p99_us"] >= st["p50_us"]
 
 
+def test_event_fd_wakes_the_loop_and_flushes_on_deadline():
+    """the event loop must never block on the GPU nor poll for it.  The context's eventfd becomes readable
+    when a batch has finished, and the watcher thread performs the deadline flush, so a loop that only select()s on
+    the descriptor gets its completions: no symrelay_flush, no symrelay_poll before the wake-up."""
+    import os
+    import select
+
+    import symmetry_b200 as sb
+
+    rng = random.Random(8)
+    with sb.SymRelay(gpu_ids=(0,), max_streams=256, flush_us=300) as r:
+        fd = r.event_fd()
+        assert fd >= 0 and r.event_fd() == fd
+        keys = [rng.randbytes(32) for _ in range(20)]
+        hdrs = [rng.randbytes(24) for _ in range(20)]
+        slots = [r.open_stream(k, h, None, None) for k, h in zip(keys, hdrs)]
+        refs = [ls.State(k, h) for k, h in zip(keys, hdrs)]
+        for rnd in range(3):
+            msgs = [rng.randbytes(rng.choice([0, 64, 300])) for _ in slots]
+            want = {r.submit_seal(s, m): (i, m) for i, (s, m) in enumerate(zip(slots, msgs))}
+            got = {}
+            for _ in range(50):
+                ready, _, _ = select.select([fd], [], [], 1.0)
+                assert ready, "the event descriptor never became readable: no deadline flush or no wake-up"
+                assert int.from_bytes(os.read(fd, 8), "little") >= 1
+                for c in r.poll():
+                    got[c["ticket"]] = c
+                if len(got) == len(want):
+                    break
+            assert len(got) == len(want)
+            for t, (i, m) in want.items():
+                assert got[t]["status"] == 0 and got[t]["data"] == refs[i].seal_frame(m)
+        assert not select.select([fd], [], [], 0.05)[0], "readable with nothing finished"
+
+
 def test_receive_side_reassembly_and_runs(relay):
     """secret-stream `_onrawdata` semantics: frames arrive as a byte stream cut at arbitrary points
     (inside the uint24 length too); all frames completed by a segment are opened in one batch as a run."""

@@ -109,3 +109,39 @@ double c1_run(symrelay_ctx *ctx, uint32_t slot, const uint8_t *blob, const uint3
     if (delta_bytes) *delta_bytes = db;
     return t1 - t0;
 }
+
+/* The reference is ONE Node process (src/provider.ts:37-58: one SymmetryProvider, one event loop): this is
+ * e2e_ring_run for a context that spans several GPUs, driven by one thread.  Per step it visits every GPU once:
+ * wait for that GPU's batch of `depth` steps ago, submit its next one.  Arrays are indexed by GPU; every GPU has its
+ * own descriptor array (its streams), ring and status block.  Returns seconds, or a negative SYMRELAY_E* code. */
+double e2e_ring_run_multi(symrelay_ctx *ctx, int n_gpus, const symrelay_desc **desc, const uint32_t *n, uint8_t **ring_base,
+                          const uint64_t *slot_bytes, const uint64_t *in_bytes, const uint64_t *out_off, const uint64_t *out_bytes,
+                          uint32_t ring, uint32_t depth, uint64_t first_step, uint32_t steps, uint32_t **status) {
+    int64_t *tickets = (int64_t *)malloc(sizeof(int64_t) * depth * (size_t)n_gpus);
+    for (size_t d = 0; d < (size_t)depth * (size_t)n_gpus; d++) tickets[d] = -1;
+    const double t0 = now();
+    for (uint64_t i = first_step; i < first_step + steps; i++)
+        for (int g = 0; g < n_gpus; g++) {
+            int64_t *slot = &tickets[(size_t)g * depth + i % depth];
+            if (*slot >= 0) {
+                int rc = symrelay_batch_wait(ctx, *slot);
+                if (rc) { free(tickets); return (double)rc; }
+            }
+            *slot = symrelay_batch_submit(ctx, desc[g], n[g], ring_base[g] + (i % ring) * slot_bytes[g], in_bytes[g],
+                                          ring_base[g] + ((i + depth) % ring) * slot_bytes[g] + out_off[g], out_bytes[g],
+                                          status[g] + (size_t)(i % ring) * n[g], NULL, NULL, 0);
+            if (*slot < 0) { double e = (double)*slot; free(tickets); return e; }
+        }
+    for (uint32_t d = 0; d < depth; d++)
+        for (int g = 0; g < n_gpus; g++) {
+            const uint64_t i = first_step + steps + d;   /* drain in submission order */
+            int64_t t = tickets[(size_t)g * depth + i % depth];
+            if (t >= 0) {
+                int rc = symrelay_batch_wait(ctx, t);
+                if (rc) { free(tickets); return (double)rc; }
+            }
+        }
+    const double t1 = now();
+    free(tickets);
+    return t1 - t0;
+}
