@@ -27,7 +27,21 @@ static inline int symrelay_desc_check_inline(const symrelay_desc *d) {
 #ifndef SYMRELAY_THREAD_TILE_MIN_FRAMES
 #define SYMRELAY_THREAD_TILE_MIN_FRAMES 8192u /* batches smaller than this are latency-bound: packed tiles only */
 #endif
+#ifndef SYMRELAY_THREAD_TILE_MAX_BLOCKS
 #define SYMRELAY_THREAD_TILE_MAX_BLOCKS 6u   /* frames of up to 4 payload blocks (256 B) */
+#endif
+
+// Strided tiles (bit 16 of n_kind, bits 24..29 = lanes per frame): frames of 7..32 blocks (385 B .. 1,920 B) whose bucket
+// is too small for thread tiles to be throughput-bound.  k lanes walk a frame's blocks with stride k, 32/k frames of
+// one block count side by side; k is the smallest power of two that leaves a lane at most five blocks, so a tile
+// takes about as long as five blocks whatever the frame size.  They run in the bulk kernel with the big frames
+// (one frame per warp is the k = 32 case).
+static inline uint32_t symrelay_seg_lanes(uint32_t nc) {
+    uint32_t k = 2u;
+    while ((nc + k) / k > 5u) k <<= 1;   // ceil((nc + 1) / k) virtual blocks per lane
+    return k > 32u ? 32u : k;
+}
+#define SYMRELAY_THREAD_TILE_BIG_BUCKET 8192u   /* a size class with this many frames fills the GPU with thread tiles whatever the frame size */
 
 // Small tiles first (packed, or thread-per-frame tiles: bit 17 of n_kind, 32 consecutive frames with
 // the same block count, one per lane), bulk tiles after them.  Runs on the host's per-batch critical
@@ -114,7 +128,19 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
     if (n && nc_min == nc_max && nc_max <= 32u) {
         // every frame has the same block count (token streaming, BASELINE config 2): the tiles follow in
         // closed form -- no per-descriptor walk
-        const bool thread_ok = n >= SYMRELAY_THREAD_TILE_MIN_FRAMES && nc_max <= SYMRELAY_THREAD_TILE_MAX_BLOCKS;
+        const bool thread_ok = (n >= SYMRELAY_THREAD_TILE_MIN_FRAMES && nc_max <= SYMRELAY_THREAD_TILE_MAX_BLOCKS) ||
+                               n >= SYMRELAY_THREAD_TILE_BIG_BUCKET;
+        if (!thread_ok && nc_max > SYMRELAY_THREAD_TILE_MAX_BLOCKS) {
+            // mid-size frames, not enough of them for thread tiles: strided tiles, all in the bulk class
+            const uint32_t k = symrelay_seg_lanes(nc_max), per_s = 32u / k;
+            for (uint32_t i = 0; i < n; i += per_s) {
+                const uint32_t cnt = n - i < per_s ? n - i : per_s;
+                if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = cnt | (1u << 16) | (k << 24); }
+                n_tiles++;
+            }
+            if (n_bulk_out) *n_bulk_out = (uint32_t)n_tiles;
+            return (int64_t)n_tiles;
+        }
         uint32_t per = 32u / nc_max;
         if (per > 16u) per = 16u;
         uint32_t i = 0;
@@ -201,26 +227,35 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
     if (chk) { chk->out_of_bounds = scan[1]; chk->any_flags = scan[2]; chk->out_overlap = scan[5]; }
     if (scan[0]) return SYMRELAY_EINVAL;
     if (scan[2] & SYMRELAY_F_RUN) return -2;
-    // bucket 0..30: 2..32 blocks; bucket 31: bulk
-    uint32_t count[32] = {0};
+    // bucket 0..30: 2..32 blocks; bucket 31: bulk.  Inside the bulk bucket the frames are ordered by size class
+    // (power-of-two ranges of the block count), LARGEST FIRST: a 16 KiB frame keeps its warp nine times as long as a
+    // 2 KiB one, so the long ones must start first or they finish last.
+    uint32_t count[32] = {0}, bulk_class[20] = {0};
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t c = nc[i];
         count[(c > 32u ? 33u : c) - 2u]++;
+        if (c > 32u) bulk_class[31 - __builtin_clz(c)]++;   // c in [33, 2^18 + 2]: classes 5..18
     }
     const bool thread_ok = n >= SYMRELAY_THREAD_TILE_MIN_FRAMES;
     uint32_t base[32], at = 0;
     uint64_t n_tiles = 0;
+    uint32_t n_strided = 0;
+    uint32_t sbase[32], scount[32];   // per bucket: the part that becomes strided tiles (second pass, bulk class)
     for (uint32_t b = 0; b < 32u; b++) {
         base[b] = at;
         uint32_t m = count[b], s = at;
         at += m;
+        sbase[b] = 0; scount[b] = 0;
         if (b == 31u) break;   // bulk tiles are appended after every packed tile
         const uint32_t c = b + 2u;
-        if (thread_ok && c <= SYMRELAY_THREAD_TILE_MAX_BLOCKS)
+        const bool threads = thread_ok && (c <= SYMRELAY_THREAD_TILE_MAX_BLOCKS || m >= SYMRELAY_THREAD_TILE_BIG_BUCKET);
+        if (!threads && c > SYMRELAY_THREAD_TILE_MAX_BLOCKS) { sbase[b] = s; scount[b] = m; continue; }
+        if (threads)
             for (; m >= 32u; m -= 32u, s += 32u) {
                 if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = s; tiles[n_tiles].n_kind = 32u | (1u << 17); }
                 n_tiles++;
             }
+        if (c > SYMRELAY_THREAD_TILE_MAX_BLOCKS) { sbase[b] = s; scount[b] = m; continue; }   // the tail of a big bucket (< 32 frames)
         uint32_t per = 32u / c;
         if (per > 16u) per = 16u;
         for (; m; ) {
@@ -230,17 +265,27 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
             m -= k; s += k;
         }
     }
+    for (uint32_t b = 0; b < 31u; b++) {
+        const uint32_t c = b + 2u, k = symrelay_seg_lanes(c), per_s = 32u / k;
+        for (uint32_t m = scount[b], s = sbase[b]; m; ) {
+            const uint32_t cnt = m < per_s ? m : per_s;
+            if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = s; tiles[n_tiles].n_kind = cnt | (1u << 16) | (k << 24); }
+            n_tiles++; n_strided++;
+            m -= cnt; s += cnt;
+        }
+    }
     for (uint32_t k = 0; k < count[31]; k++) {
         if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = base[31] + k; tiles[n_tiles].n_kind = 1u | (1u << 16); }
         n_tiles++;
     }
-    if (n_bulk_out) *n_bulk_out = count[31];
+    if (n_bulk_out) *n_bulk_out = count[31] + n_strided;
     if (tiles && sorted && perm) {
-        uint32_t next[32];
+        uint32_t next[32], bnext[20];
         for (uint32_t b = 0; b < 32u; b++) next[b] = base[b];
+        for (uint32_t k = 20u, at2 = base[31]; k-- > 0u;) { bnext[k] = at2; at2 += bulk_class[k]; }   // largest class first
         for (uint32_t i = 0; i < n; i++) {
             const uint32_t c = nc[i];
-            const uint32_t pos = next[(c > 32u ? 33u : c) - 2u]++;
+            const uint32_t pos = c > 32u ? bnext[31 - __builtin_clz(c)]++ : next[c - 2u]++;
             sorted[pos] = desc[i];
             perm[pos] = i;
         }

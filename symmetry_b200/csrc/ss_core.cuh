@@ -39,9 +39,11 @@ SS_DEV uint32_t ss_reduce_max(uint32_t v) { return __reduce_max_sync(0xffffffffu
 SS_DEV uint32_t ss_reduce_min(uint32_t v) { return __reduce_min_sync(0xffffffffu, v); }
 SS_DEV bool ss_any(bool p) { return __any_sync(0xffffffffu, p) != 0; }
 SS_DEV void ss_syncwarp() { __syncwarp(); }
-// bulk tiles: r, r^2, r^3, r^4, r^128 of the warp's frame, each as 5 limbs followed by 4 limbs-times-5 (45 words)
+// strided tiles: r, r^2, r^3, r^4, r^(4*segw) of each of the warp's frames (up to 16 with 2 lanes per frame), each
+// as 5 limbs followed by 4 limbs-times-5 (45 of 48 words)
+#define SS_MAX_SEG_FRAMES 16u
 SS_DEV uint32_t *ss_powers_buffer() {
-    __shared__ uint32_t pw[4][48];
+    __shared__ uint32_t pw[4][SS_MAX_SEG_FRAMES * 48u];
     return pw[(threadIdx.x >> 5) & 3u];
 }
 #define SS_STAGE_BYTES 2048u
@@ -478,18 +480,23 @@ SS_DEV void ss_load_mac(const uint8_t *p, uint32_t w[4]) {
 }
 
 // --------------------------------------------------------------- the tile ---
-// One warp processes one tile.  BULK == false: up to 16 small frames packed in
-// the warp, one pass.  BULK == true: one frame of any size, lanes stride by 32.
+// One warp processes one tile.  BULK == false: up to 16 small frames packed in the warp, one lane per 64-byte
+// block, one pass.  BULK == true ("strided"): every frame of the tile gets segw lanes (2, 4, 8, 16 or all 32: bits
+// 24..29 of n_kind, 0 = 32) which walk its blocks with stride segw -- one big frame per warp, or 32/segw mid-size
+// frames of one block count side by side.
 // `given`: the tile itself when the launch carried the tile list in its parameters (small host batches:
 // one dependent read over PCIe fewer), else it is read from a.tiles.
-template <bool BULK, bool VOL = false>
+// SEG (with BULK): the tile may hold several frames with fewer than 32 lanes each; SEG == false keeps the one-frame-per-
+// warp case free of the bookkeeping (its register budget is tight: 72, seven blocks of 128 threads per SM).
+template <bool BULK, bool VOL = false, bool SEG = false>
 SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_dbg_stamp(a, tile_idx, lane, 0);
     ss_pdl_launch_dependents();   // the next batch's kernel may start its own prologue now
     if (!(a.flags & SS_ARG_INPUT_INDEPENDENT)) ss_pdl_wait();   // descriptors may come from the previous kernel
     const SsTile tile = given ? *given : a.tiles[tile_idx];
-    const uint32_t nfr = BULK ? 1u : (tile.n_kind & 0xffffu);
+    const uint32_t nfr = (BULK && !SEG) ? 1u : (tile.n_kind & 0xffffu);
+    const uint32_t segw = (BULK && SEG) ? (((tile.n_kind >> 24) & 63u) ? ((tile.n_kind >> 24) & 63u) : 32u) : 32u;   // lanes per frame (strided tiles)
 
     // ---- lane -> (frame f, first lane st of that frame) ---------------------
     uint32_t d_slot = 0, d_in = 0, d_out = 0, d_lf = 0, my_nc = 0, d_skip = 0, d_ver = 0;
@@ -497,11 +504,17 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
         const uint4 d = ss_ld16<VOL>(a.desc + tile.first + lane);
         d_slot = d.x; d_in = d.y; d_out = d.z; d_lf = d.w;
         my_nc = 2u + (((d_lf & 0xffffffu) + 63u) >> 6);
-        if (a.desc_fill) *reinterpret_cast<uint4 *>(a.desc_fill + tile.first + lane) = d;
-        if (a.flags & SS_ARG_CHAIN) d_ver = (a.flags & SS_ARG_CHAIN_UNIFORM) ? a.ver_all : a.ver[tile.first + lane];
+        if (!BULK && a.desc_fill) *reinterpret_cast<uint4 *>(a.desc_fill + tile.first + lane) = d;
+        if (!BULK && (a.flags & SS_ARG_CHAIN)) d_ver = (a.flags & SS_ARG_CHAIN_UNIFORM) ? a.ver_all : a.ver[tile.first + lane];
     }
     uint32_t f = 0, st = 0, my_start = 0;
     bool valid = true;
+    if (BULK && SEG) {
+        f = lane / segw;           // segw is a power of two
+        st = f * segw;
+        valid = f < nfr;
+        if (!valid) f = 0;
+    }
     if (!BULK) {
         uint32_t incl = my_nc;
 #pragma unroll
@@ -521,7 +534,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     const uint32_t in_off = ss_shfl(d_in, f);
     const uint32_t out_off = ss_shfl(d_out, f);
     const uint32_t lf = ss_shfl(d_lf, f);
-    const uint32_t exp_ver = (a.flags & SS_ARG_CHAIN) ? ss_shfl(d_ver, f) : 0u;
+    const uint32_t exp_ver = (!BULK && (a.flags & SS_ARG_CHAIN)) ? ss_shfl(d_ver, f) : 0u;   // (the resident kernel runs packed and thread tiles only)
 
     const uint32_t mlen = lf & 0xffffffu;
     const bool is_open = (lf & SS_F_OPEN) != 0;
@@ -574,8 +587,8 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     }
     ss_dbg_stamp(a, tile_idx, lane, 1);
     ss_pdl_wait();   // from here on we touch what the previous kernel may have written
-    ss_dep_wait(a.dep_seq, a.dep_need);   // (batch-level dependency; unused when a.ver is set)
-    if (a.flags & SS_ARG_CHAIN) {
+    if (!BULK) ss_dep_wait(a.dep_seq, a.dep_need);   // (batch-level dependency; unused when a.ver is set)
+    if (!BULK && (a.flags & SS_ARG_CHAIN)) {
         // resident kernel: every lane waits until its frame's predecessor has left the state (warp-uniform loop)
         const uint32_t *vp = reinterpret_cast<const uint32_t *>(sp + 2) + 3;
         bool ready = !valid || exp_ver == 0u;
@@ -664,11 +677,14 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     uint32_t tagval = 0;               // lane b==1: seal -> wire tag byte, open -> decrypted tag
     uint32_t keep[16];                 // packed open: plaintext held back until the MAC verdict
     bool have_A = false;
-    const uint32_t niter = BULK ? ((nc + 1u + 31u) >> 5) : 1u;  // bulk walks virtual blocks 0..nc
+    // strided tiles walk virtual blocks 0..nc of every frame; the loop is warp-uniform (it holds shuffles), so it runs
+    // for the longest frame of the tile (the planner groups frames of one block count)
+    const uint32_t niter = !BULK ? 1u : (SEG ? ss_reduce_max(valid ? (nc + segw) / segw : 0u) : ((nc + 1u + 31u) >> 5));
+    const uint32_t stride = BULK ? segw : 32u;
 
 #pragma unroll 1
     for (uint32_t it = 0; it < niter; ++it) {
-        const uint32_t b = (lane - st) + 32u * it;
+        const uint32_t b = (lane - st) + stride * it;
         const bool has_block = valid && b < nc;
         const bool need_ks = has_block;
         // (Bulk tiles load after the rounds: they have enough warps in flight, and holding the
@@ -692,21 +708,21 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
             sw[0] = x[4]; sw[1] = x[5]; sw[2] = x[6]; sw[3] = x[7];
             if (BULK) {
                 uint32_t t[5], t3[5];
-                uint32_t *pw = ss_powers_buffer();
+                uint32_t *pw = ss_powers_buffer() + 48u * f;
                 ss_pmul(t, r, r);        // r^2
                 ss_pmul(t3, t, r);       // r^3
                 ss_pmul(r128, t, t);     // r^4
                 ss_syncwarp();           // (the previous tile of this warp is done with the buffer)
-                if (lane == 0) {         // every lane holds the same values: one writer is enough
+                if (valid && lane == st) {   // every lane of a frame holds the same values: one writer is enough
                     ss_store_power(pw, r); ss_store_power(pw + 9, t); ss_store_power(pw + 18, t3); ss_store_power(pw + 27, r128);
                 }
 #pragma unroll 1
-                for (int i = 0; i < 5; i++) {  // r^8 .. r^128
+                for (uint32_t w = 1; w < segw; w <<= 1) {  // r^8 .. r^(4*segw): the step between a lane's consecutive windows
                     ss_pmul(t, r128, r128);
 #pragma unroll
                     for (int j = 0; j < 5; j++) r128[j] = t[j];
                 }
-                if (lane == 0) ss_store_power(pw + 36, r128);
+                if (valid && lane == st) ss_store_power(pw + 36, r128);
                 ss_syncwarp();
             }
         }
@@ -773,7 +789,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
                 // Full window of a bulk frame: A <- A*r^128 + b0*r^4 + b1*r^3 + b2*r^2 + b3*r as FIVE products
                 // accumulated in 64-bit and ONE carry pass (instead of five multiply-reduce rounds); the
                 // powers come from shared memory so they cost no registers.
-                const uint32_t *pw = ss_powers_buffer();
+                const uint32_t *pw = ss_powers_buffer() + 48u * f;
                 uint64_t d[5] = {0, 0, 0, 0, 0};
                 uint32_t l[5];
                 if (have_A) ss_pmac(d, A, pw + 36);
@@ -844,7 +860,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     }
 
     // ---- segmented sum of the limb vectors onto the leader lane -------------
-    const uint32_t endl = BULK ? 31u : st + nc - 1u;
+    const uint32_t endl = BULK ? st + segw - 1u : st + nc - 1u;
 #pragma unroll
     for (uint32_t o = 1; o < 32; o <<= 1) {
 #pragma unroll
@@ -880,13 +896,13 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
         }
     }
     if (BULK) {
-        if (is_open && !ok) {   // forged bulk frame: wipe what was decrypted speculatively (warp-uniform branch)
+        if (valid && is_open && !ok) {   // forged frame: wipe what was decrypted speculatively
             uint32_t z[16];
 #pragma unroll
             for (int i = 0; i < 16; i++) z[i] = 0;
 #pragma unroll 1
             for (uint32_t it = 0; it < niter; ++it) {
-                const uint32_t b = lane + 32u * it;
+                const uint32_t b = (lane - st) + stride * it;
                 if (b >= 2u && b < nc) {
                     const uint32_t j = b - 2u;
                     const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
@@ -918,7 +934,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
             stword = SS_ST_OK | (tag << 8);
         }
         // resident kernel: hand the state on -- also when the frame failed, its successor is waiting for the stamp
-        if (a.flags & SS_ARG_CHAIN) ss_st_release_u32(reinterpret_cast<uint32_t *>(sp + 2) + 3, (meta & 0xffu) | (a.new_ver << 8));
+        if (!BULK && (a.flags & SS_ARG_CHAIN)) ss_st_release_u32(reinterpret_cast<uint32_t *>(sp + 2) + 3, (meta & 0xffu) | (a.new_ver << 8));
         if (BULK) a.status[tile.first + f] = stword;
     }
     ss_dbg_stamp(a, tile_idx, lane, 5);

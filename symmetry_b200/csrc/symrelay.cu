@@ -47,6 +47,27 @@ __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_kernel(Ss
     else ss_process_tile<false>(a, warp);
 }
 
+// Large batches split the two small-tile kinds over two kernels (each launched over the whole small-tile range and taking
+// only its own kind): the thread-per-frame path needs far fewer registers than the packed one, and BASELINE config 3 is
+// 3,750 thread tiles that want to be resident all at once.
+#ifndef SS_THREAD_MIN_BLOCKS
+#define SS_THREAD_MIN_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, SS_THREAD_MIN_BLOCKS) ss_thread_kernel(SsArgs a) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= a.n_tiles) return;
+    const SsTile tile = a.tiles[warp];
+    if (!(tile.n_kind & (1u << 17))) return;
+    ss_process_thread_tile(a, warp, &tile);
+}
+__global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_only_kernel(SsArgs a) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= a.n_tiles) return;
+    const SsTile tile = a.tiles[warp];
+    if (tile.n_kind & (1u << 17)) return;
+    ss_process_tile<false>(a, warp, &tile);
+}
+
 // The same kernel for small host batches: the tile list rides in the launch parameters (constant bank), so a
 // warp does not start with a read of host memory that only tells it where its descriptors are.  Zero-copy
 // batches begin with three dependent reads over PCIe (tile -> descriptors -> payload); this removes the first.
@@ -70,7 +91,20 @@ __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_inline_ke
 __global__ void __launch_bounds__(128, SS_BULK_MIN_BLOCKS) ss_bulk_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
-    ss_process_tile<true>(a, warp);
+    const SsTile tile = a.tiles[warp];
+    if ((tile.n_kind >> 24) & 63u) return;   // a strided tile: ss_strided_kernel's
+    ss_process_tile<true>(a, warp, &tile);
+}
+
+// Strided tiles (plan.h): 32/k mid-size frames of one block count per warp, k lanes each.  Launched over the same
+// bulk-class tile range as ss_bulk_kernel; each of the two kernels takes its own kind and leaves the other's alone
+// (the entry points get one count for the class, and the tile list may live in device memory).
+__global__ void __launch_bounds__(128, 4) ss_strided_kernel(SsArgs a) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= a.n_tiles) return;
+    const SsTile tile = a.tiles[warp];
+    if (!((tile.n_kind >> 24) & 63u)) return;
+    ss_process_tile<true, false, true>(a, warp, &tile);
 }
 
 // Posts a deferred batch's results to the caller's host memory when no later batch carries them.
@@ -665,8 +699,8 @@ struct Shard {
     int pending_wb = -1;                           // stage whose results still sit in device staging
     unsigned long long *d_ts = nullptr;            // SYMRELAY_TS=1: 4 time stamps per batch, 4096 batches round-robin
     uint64_t ts_n = 0;
-    cudaStream_t s_aux = nullptr;                  // bulk tiles run here, next to the packed tiles of the same batch
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t s_aux = nullptr, s_aux2 = nullptr, s_aux3 = nullptr;   // side streams: the tile kinds of one batch run next to each other
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr, ev_join3 = nullptr;
     std::vector<Stage> stages;
     SsInitRec *h_init = nullptr, *d_init = nullptr;  // staging for stream_open
     uint32_t init_cap = 0;
@@ -848,25 +882,61 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     // PDL only where it was measured to help: the host zero-copy path (16.2 -> 10.9 us per C2 batch).
     // Device-resident launches replayed from a CUDA graph got slower with it (6.3 -> 10.3 us).
     const bool pdl = ctx->pdl && (arg_flags & SS_ARG_INPUT_INDEPENDENT);
-    // Small and bulk tiles of one batch touch disjoint frames: when both exist the bulk kernel runs on a
-    // side stream next to the packed kernel (fork/join with events; measured on BASELINE config 3 they
-    // took 57 us + 35 us back to back).
-    const bool side = fork && n_packed && n_bulk;
-    cudaStream_t bulk_stream = stream;
-    if (side) {
-        CU(ctx, cudaEventRecord(fork->ev_fork, stream));
-        CU(ctx, cudaStreamWaitEvent(fork->s_aux, fork->ev_fork, 0));
-        bulk_stream = fork->s_aux;
+    // The tile kinds of one batch touch disjoint frames, so each kind gets its own kernel and, when several are
+    // present, its own side stream next to the caller's (fork/join with events; BASELINE config 3: thread tiles
+    // 24 us, packed 16, strided 15, big frames 36 when run one after the other):
+    //   thread tiles (and the combined small-tile kernel of small batches)  -> the caller's stream
+    //   big frames, one per warp                                           -> side stream 1
+    //   strided tiles (mid-size frames)                                    -> side stream 2
+    //   packed tiles of a large batch                                      -> side stream 3
+    const bool big = n_packed > 148u * 8u && !write_back;   // large batch: split the small tiles by kind (see ss_thread_kernel)
+    bool has_thread = n_packed != 0, has_packed = big, has_strided = n_bulk != 0, has_bulk = n_bulk != 0;
+    if (host_tiles) {   // the tile list is in host memory: launch only what is there
+        has_strided = has_bulk = false;
+        for (uint32_t i = n_packed; i < n_tiles; i++) {
+            if ((host_tiles[i].n_kind >> 24) & 63u) has_strided = true; else has_bulk = true;
+        }
+        if (big) {
+            has_thread = has_packed = false;
+            for (uint32_t i = 0; i < n_packed && !(has_thread && has_packed); i++) {
+                if (host_tiles[i].n_kind & (1u << 17)) has_thread = true; else has_packed = true;
+            }
+        }
     }
+    const int kinds = (n_packed ? (big ? (int)has_thread + (int)has_packed : 1) : 0) + (int)has_strided + (int)has_bulk;
+    const bool side = fork && kinds > 1;
+    if (side) CU(ctx, cudaEventRecord(fork->ev_fork, stream));
+    cudaEvent_t joins[3];
+    int n_joins = 0;
+    // the stream for a kind that has a side stream: that stream (made to wait on the fork) when the batch forks at all
+    auto side_stream = [&](cudaStream_t s_side, cudaEvent_t ev) -> cudaStream_t {
+        if (!side) return stream;
+        cudaStreamWaitEvent(s_side, fork->ev_fork, 0);
+        joins[n_joins++] = ev;
+        return s_side;
+    };
+    // Launch order = the order in which the block scheduler hands out SM resources: the kinds with the longest warps
+    // first (a 16 KiB frame keeps its warp for nine rounds), the throughput kernels fill what is left.
     if (n_bulk) {
         SsArgs b = a;
         b.tiles = reinterpret_cast<const SsTile *>(d_tiles) + n_packed;
         b.n_tiles = n_bulk;
+        // (One warp per block, so that a warp that finds the other kind's tile gives its registers back at once, was
+        // measured and is worse: 71 -> 80 us on BASELINE config 3.)
         const uint32_t threads = n_bulk <= 148u * 8u ? 32u : 128u;
         const uint32_t wpb = threads / 32u;
-        CU(ctx, launch_pdl(ss_bulk_kernel, (n_bulk + wpb - 1) / wpb, threads, bulk_stream, pdl && !side, b));
-        ctx->launches++;
-        if (side) CU(ctx, cudaEventRecord(fork->ev_join, bulk_stream));
+        if (has_bulk) {
+            cudaStream_t s = side_stream(fork ? fork->s_aux : nullptr, fork ? fork->ev_join : nullptr);
+            CU(ctx, launch_pdl(ss_bulk_kernel, (n_bulk + wpb - 1) / wpb, threads, s, pdl && !side, b));
+            ctx->launches++;
+            if (s != stream) CU(ctx, cudaEventRecord(fork->ev_join, s));
+        }
+        if (has_strided) {
+            cudaStream_t s = side_stream(fork ? fork->s_aux2 : nullptr, fork ? fork->ev_join2 : nullptr);
+            CU(ctx, launch_pdl(ss_strided_kernel, (n_bulk + wpb - 1) / wpb, threads, s, false, b));
+            ctx->launches++;
+            if (s != stream) CU(ctx, cudaEventRecord(fork->ev_join2, s));
+        }
     }
     if (n_packed) {
         a.tiles = reinterpret_cast<const SsTile *>(d_tiles);
@@ -882,11 +952,23 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
         }
         const uint32_t threads = n_packed <= 148u * 8u ? 32u : 128u;  // few tiles: one warp per SM sub-partition
         const uint32_t wpb = threads / 32u;
-        if (host_tiles && n_packed <= SS_INLINE_TILES && ctx->inline_tiles) {
+        const uint32_t grid = (n_packed + wpb - 1) / wpb;
+        if (big) {
+            if (has_packed) {
+                cudaStream_t s = has_thread ? side_stream(fork ? fork->s_aux3 : nullptr, fork ? fork->ev_join3 : nullptr) : stream;
+                CU(ctx, launch_pdl(ss_packed_only_kernel, grid, threads, s, false, a));
+                ctx->launches++;
+                if (s != stream) CU(ctx, cudaEventRecord(fork->ev_join3, s));
+            }
+            if (has_thread) {   // the caller's stream
+                CU(ctx, launch_pdl(ss_thread_kernel, grid, threads, stream, false, a));
+                ctx->launches++;
+            }
+        } else if (host_tiles && n_packed <= SS_INLINE_TILES && ctx->inline_tiles) {
             static thread_local SsTileBlock tb;
             memcpy(tb.t, host_tiles, (size_t)n_packed * sizeof(SsTile));
             cudaLaunchConfig_t cfg = {};
-            cfg.gridDim = dim3((n_packed + wpb - 1) / wpb);
+            cfg.gridDim = dim3(grid);
             cfg.blockDim = dim3(threads);
             cfg.stream = stream;
             cudaLaunchAttribute attr[1];
@@ -895,12 +977,13 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
             cfg.attrs = attr;
             cfg.numAttrs = (pdl && !side) ? 1 : 0;
             CU(ctx, cudaLaunchKernelEx(&cfg, ss_packed_inline_kernel, a, tb));
+            ctx->launches++;
         } else {
-            CU(ctx, launch_pdl(ss_packed_kernel, (n_packed + wpb - 1) / wpb, threads, stream, pdl && !side, a));
+            CU(ctx, launch_pdl(ss_packed_kernel, grid, threads, stream, pdl && !side, a));
+            ctx->launches++;
         }
-        ctx->launches++;
     }
-    if (side) CU(ctx, cudaStreamWaitEvent(stream, fork->ev_join, 0));
+    for (int j = 0; j < n_joins; j++) CU(ctx, cudaStreamWaitEvent(stream, joins[j], 0));
     if (d_run_nonce) {
         ss_run_commit_kernel<<<(n + 127) / 128, 128, 0, stream>>>(reinterpret_cast<const SsDesc *>(d_desc), n, d_in,
                                                                   d_states, d_status);
@@ -953,7 +1036,13 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_in, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_k, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_out, cudaStreamNonBlocking));
-    CU(ctx, cudaStreamCreateWithFlags(&sh.s_aux, cudaStreamNonBlocking));
+    {   // the side streams of the long-running tile kinds get the highest priority: their blocks are placed first
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        CU(ctx, cudaStreamCreateWithPriority(&sh.s_aux, cudaStreamNonBlocking, hi));
+        CU(ctx, cudaStreamCreateWithPriority(&sh.s_aux2, cudaStreamNonBlocking, hi));
+    }
+    CU(ctx, cudaStreamCreateWithFlags(&sh.s_aux3, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_init, cudaStreamNonBlocking));
     CU(ctx, cudaHostAlloc(&sh.pk_host, sizeof(PkHost), cudaHostAllocMapped | cudaHostAllocPortable));
     memset(sh.pk_host, 0, sizeof(PkHost));
@@ -961,6 +1050,8 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     CU(ctx, cudaMalloc(&sh.pk_dev, sizeof(PkDev)));
     CU(ctx, cudaEventCreateWithFlags(&sh.ev_fork, cudaEventDisableTiming));
     CU(ctx, cudaEventCreateWithFlags(&sh.ev_join, cudaEventDisableTiming));
+    CU(ctx, cudaEventCreateWithFlags(&sh.ev_join2, cudaEventDisableTiming));
+    CU(ctx, cudaEventCreateWithFlags(&sh.ev_join3, cudaEventDisableTiming));
     {
         std::vector<uint16_t> table(SX_TABLE_ENTRIES);
         sx::build_table(table.data());
@@ -1094,6 +1185,10 @@ static void shard_free(Shard &sh) {
     if (sh.s_k) cudaStreamDestroy(sh.s_k);
     if (sh.s_out) cudaStreamDestroy(sh.s_out);
     if (sh.s_aux) cudaStreamDestroy(sh.s_aux);
+    if (sh.s_aux2) cudaStreamDestroy(sh.s_aux2);
+    if (sh.s_aux3) cudaStreamDestroy(sh.s_aux3);
+    if (sh.ev_join2) cudaEventDestroy(sh.ev_join2);
+    if (sh.ev_join3) cudaEventDestroy(sh.ev_join3);
     if (sh.ev_fork) cudaEventDestroy(sh.ev_fork);
     if (sh.ev_join) cudaEventDestroy(sh.ev_join);
 }

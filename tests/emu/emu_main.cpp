@@ -33,7 +33,10 @@ static void *lane_main(void *p) {
         if (j->args.tiles[t].n_kind & (1u << 17)) ss_process_thread_tile(j->args, t);
         else ss_process_tile<false>(j->args, t);
     }
-    for (uint32_t t = 0; t < j->n_bulk; t++) ss_process_tile<true>(j->args, j->n_packed + t);
+    for (uint32_t t = 0; t < j->n_bulk; t++) {
+        if ((j->args.tiles[j->n_packed + t].n_kind >> 24) & 63u) ss_process_tile<true, false, true>(j->args, j->n_packed + t);   // strided
+        else ss_process_tile<true>(j->args, j->n_packed + t);
+    }
     return nullptr;
 }
 

@@ -76,7 +76,7 @@ static inline void ss_syncwarp() { emu_sync(); }
 #define SS_STAGE_BYTES 2048u
 static uint4 emu_stage[SS_STAGE_BYTES / 16u];   // one warp runs at a time
 static inline uint4 *ss_stage_buffer() { return emu_stage; }
-static uint32_t emu_powers[48];
+static uint32_t emu_powers[16 * 48];   // SS_MAX_SEG_FRAMES frames per warp
 static inline uint32_t *ss_powers_buffer() { return emu_powers; }
 static inline uint32_t ss_popc(uint32_t v) { return (uint32_t)__builtin_popcount(v); }
 static inline uint32_t ss_clz(uint32_t v) { return v ? (uint32_t)__builtin_clz(v) : 32u; }

@@ -146,3 +146,17 @@ def test_thread_per_frame_tiles(be):
 def test_thread_tiles_in_runs(be):
     n, n_retry = pc.run_open_scenario(be, seed=9, n_streams=40)
     assert n > 64
+
+
+@pytest.mark.parametrize("length", [385, 449, 700, 1024, 1025, 1857, 1920])
+def test_strided_tiles_mid_size_frames(be, length):
+    """Uniform batches of 7..32-block frames are cut into strided tiles (k = 2, 4, 8 lanes per frame, 32/k frames per
+    warp, r^(4k) between a lane's windows): all lane counts, partial tail tiles, tags, forged frames."""
+    n = 19
+    lens = [length] * n
+    p, _ = bu.plain_layout(lens)
+    w, _ = bu.wire_layout(lens)
+    tiles, n_bulk = be.plan(bu.make_descs(np.arange(n), lens, p, w))
+    assert n_bulk == len(tiles) and all((int(t["n_kind"]) >> 24) & 63 in (2, 4, 8) for t in tiles)
+    pc.seal_open_roundtrip(be, lens, [i % 4 for i in range(n)], seed=500 + length, chain=2, corrupt=(0, 7, 18),
+                           speculative_min_len=385)

@@ -162,6 +162,17 @@ def test_thread_per_frame_tiles_on_a_large_uniform_batch(be):
     pc.seal_open_roundtrip(be, lens, tags, seed=31, chain=2, corrupt=(0, 31, 32, 6001, 11000, 11700, 11960))
 
 
+@pytest.mark.parametrize("length", [385, 448, 449, 512, 640, 700, 1000, 1024, 1025, 1280, 1500, 1856, 1857, 1919, 1920])
+def test_strided_tiles_mid_size_frames(dbe, length):
+    """Frames of 7..32 ChaCha20 blocks in a batch that is all one size class: 32/k frames per warp, k lanes each walking
+    the frame's blocks with stride k (2, 4 or 8 lanes here), partial MACs combined with r^(4k).  Every lane count, the
+    tail tile with fewer frames than fit, tags incl. REKEY, forged frames (decrypted speculatively, wiped on a bad
+    tag, state untouched, the true frame opens afterwards)."""
+    n = 37
+    tags = [0, 1, 2, 3] * 9 + [0]
+    pc.seal_open_roundtrip(dbe, [length] * n, tags, seed=1000 + length, chain=2, corrupt=(0, 5, 36), speculative_min_len=385)
+
+
 def test_counter_wrap_rekeys(be):
     key, hdr = bytes(range(32)), bytes(24)
     raw = bytearray(ls.State(key, hdr).raw)
