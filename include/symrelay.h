@@ -48,6 +48,7 @@ extern "C" {
 #define SYMRELAY_EAGAIN (-11) /* ring full: maps to `peer.write() === false`, provider.ts:248-252 */
 #define SYMRELAY_ENOMEM (-12)
 #define SYMRELAY_ENOENT (-2)
+#define SYMRELAY_EPROTO (-71) /* the peer broke the framing protocol (bad first message): secret-stream destroys the stream */
 #define SYMRELAY_ECUDA (-1000) /* CUDA failure: fatal for the batch, see symrelay_last_error() */
 
 /* per-frame status word written by the kernels: bits 0..7 code, bits 8..15 opened tag */
@@ -183,6 +184,21 @@ SYMRELAY_API int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, 
 SYMRELAY_API int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_keys, const uint8_t *tx_inits,
                                const uint8_t *rx_keys, const uint8_t *rx_inits, int init_len, int provider_kind,
                                uint32_t *slots_out);
+/* Connection set-up in batch: what secret-stream computes per connection before it sends its
+ * first message, for n new connections at once on GPU `gpu_index`.  Per connection i:
+ *     local id   = BLAKE2b-256(key = handshake_hashes[i] (64 B), message = the namespace of OUR role)
+ *     remote id  = the same with the peer's role's namespace: what symrelay_rx_expect_header should be given
+ *     header     = 24 fresh bytes: the secretstream header of the outbound direction (libsodium init_push draws them
+ *                  from its RNG; here ChaCha20 of a 32-byte seed -- seed32 NULL: read from the OS generator)
+ * i.e. libsodium crypto_generichash(out32, ns, 32, hash, 64) twice and randombytes_buf(24).  initiator[i] != 0 says which
+ * of the two 32-byte namespaces (hypercore-crypto `namespace('hyperswarm/secret-stream', 3)`, supplied by the caller)
+ * is ours.  Outputs (each may be NULL): local_ids n x 32, remote_ids n x 32, headers n x 24, first_messages n x 59
+ * (uint24-LE(56) ‖ local id ‖ header, ready for the socket).  Then symrelay_stream_open_batch(tx_inits = headers, 24).
+ * Hook: hyperswarm's 'connection' event, src/provider.ts:55-58. */
+SYMRELAY_API int symrelay_connect_batch(symrelay_ctx *ctx, int gpu_index, uint32_t n, const uint8_t *handshake_hashes,
+                                        const uint8_t *initiator, const uint8_t ns_initiator[32], const uint8_t ns_responder[32],
+                                        const uint8_t *seed32, uint8_t *local_ids, uint8_t *remote_ids, uint8_t *headers,
+                                        uint8_t *first_messages);
 /* Wipes the slot's keys on the device, forgets its half-received inbound frame (symrelay_rx_feed) and frees
  * the slot.  Close only after every frame submitted for the slot has completed: a frame still in flight would
  * be sealed with the wiped state.  The per-frame front end enforces that: while one of the slot's frames sits
@@ -298,6 +314,19 @@ SYMRELAY_API int64_t symrelay_submit_open(symrelay_ctx *ctx, uint32_t slot, cons
  *     behind a REKEY-tagged frame) must be resubmitted with symrelay_submit_open. */
 SYMRELAY_API int symrelay_rx_feed(symrelay_ctx *ctx, uint32_t slot, const uint8_t *seg, uint32_t n, uint32_t *consumed,
                                   int64_t *tickets, int max_tickets);
+/* symrelay_rx_expect_header  <-  secret-stream's handling of the connection's FIRST message: before any encrypted
+ *     frame each side sends uint24-LE(56) ‖ streamId[32] ‖ header[24] in the clear (`_onrawdata` with `_state` 0, the
+ *     fields typed at src/types.ts:156-159).  After this call the next frame symrelay_rx_feed completes on the slot is
+ *     taken as that message: its stream id is compared with expected_stream_id (NULL: not checked), its header and
+ *     rx_key initialise the slot's receive state on the GPU (HChaCha20 sub-key, libsodium init_pull), and the frames
+ *     after it are opened as usual.  A first message of another size or with another id makes symrelay_rx_feed return
+ *     SYMRELAY_EPROTO: the caller destroys the connection, as secret-stream does.  Open the slot with rx_key NULL.
+ * symrelay_stream_set_keepalive  <-  secret-stream `setKeepAlive` / the `_incoming` rule "an empty message on a
+ *     stream with keep-alive on is swallowed": zero-length inbound frames are opened (the chain advances) but never
+ *     delivered by symrelay_poll. */
+SYMRELAY_API int symrelay_rx_expect_header(symrelay_ctx *ctx, uint32_t slot, const uint8_t rx_key[SYMRELAY_KEYBYTES],
+                                           const uint8_t *expected_stream_id);
+SYMRELAY_API int symrelay_stream_set_keepalive(symrelay_ctx *ctx, uint32_t slot, int on);
 SYMRELAY_API int symrelay_flush(symrelay_ctx *ctx);
 SYMRELAY_API int symrelay_poll(symrelay_ctx *ctx, symrelay_completion *out, int max);
 SYMRELAY_API int symrelay_poll_wait(symrelay_ctx *ctx, symrelay_completion *out, int max);

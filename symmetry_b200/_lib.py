@@ -21,7 +21,8 @@ EXPORTS = (
     "symrelay_free_pinned", "symrelay_probe_int_peak", "symrelay_submit_seal", "symrelay_submit_open",
     "symrelay_flush", "symrelay_poll", "symrelay_poll_wait", "symrelay_release", "symrelay_sched_stats",
     "symrelay_sched_reset_stats", "symrelay_batch_device_runs", "symrelay_batch_device_runs_static",
-    "symrelay_rx_feed", "symrelay_event_fd",
+    "symrelay_rx_feed", "symrelay_event_fd", "symrelay_connect_batch", "symrelay_rx_expect_header",
+    "symrelay_stream_set_keepalive",
 )
 
 
@@ -106,6 +107,12 @@ def load() -> C.CDLL:
     L.symrelay_submit_open.argtypes = [vp, u32, vp, u32]
     L.symrelay_rx_feed.restype = ci
     L.symrelay_rx_feed.argtypes = [vp, u32, vp, u32, C.POINTER(u32), C.POINTER(i64), ci]
+    L.symrelay_connect_batch.restype = ci
+    L.symrelay_connect_batch.argtypes = [vp, ci, u32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.symrelay_rx_expect_header.restype = ci
+    L.symrelay_rx_expect_header.argtypes = [vp, u32, vp, vp]
+    L.symrelay_stream_set_keepalive.restype = ci
+    L.symrelay_stream_set_keepalive.argtypes = [vp, u32, ci]
     L.symrelay_event_fd.restype = ci
     L.symrelay_event_fd.argtypes = [vp]
     L.symrelay_flush.restype = ci

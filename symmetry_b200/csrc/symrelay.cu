@@ -32,6 +32,7 @@
 #include "ss_core.cuh"
 #include "ss_extract.cuh"
 #include "ss_runs.cuh"
+#include "ss_blake2b.cuh"
 
 static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) == sizeof(SsTile), "ABI layout");
 
@@ -512,6 +513,42 @@ __global__ void __launch_bounds__(128, 3) ss_persistent_kernel(PkHost *host, PkD
         ss_dbg_stamp(a, k, lane, 4);
         if (my_ts && lane == 0) my_ts[5] = pk_now();
     }
+}
+
+// Connection set-up in batch, one thread per new connection: the two stream ids of
+// secret-stream's first message and a fresh secretstream header for the outbound direction.
+//   id_local  = BLAKE2b-256(key = handshake hash, msg = namespace of OUR role)     (crypto_generichash)
+//   id_remote = ... of the peer's role: what the first inbound message must carry
+//   header    = 24 bytes of ChaCha20(seed, nonce = connection index) -- the seed is 32 fresh random bytes per call
+// rec: hash[64] ‖ initiator flag (u32) ‖ pad; out: id_local[32] ‖ id_remote[32] ‖ header[24] ‖ pad[8]
+struct SsConnRec { uint8_t hash[64]; uint32_t initiator; uint32_t pad[3]; };
+struct SsConnOut { uint8_t id_local[32], id_remote[32], header[24], pad[8]; };
+static_assert(sizeof(SsConnRec) == 80 && sizeof(SsConnOut) == 96, "connect record layout");
+__global__ void ss_connect_kernel(const SsConnRec *recs, uint32_t n, const uint4 *ns_pair /* initiator[32] ‖ responder[32] */,
+                                  const uint4 *seed /* 32 bytes */, uint32_t call_no, SsConnOut *out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t *kw = reinterpret_cast<const uint64_t *>(recs[i].hash);
+    uint64_t key[8], ns_i[4], ns_r[4], idl[4], idr[4];
+#pragma unroll
+    for (int j = 0; j < 8; j++) key[j] = kw[j];
+    const uint64_t *nw = reinterpret_cast<const uint64_t *>(ns_pair);
+#pragma unroll
+    for (int j = 0; j < 4; j++) { ns_i[j] = nw[j]; ns_r[j] = nw[4 + j]; }
+    const bool init = recs[i].initiator != 0;
+    sb_blake2b256_keyed(key, init ? ns_i : ns_r, idl);
+    sb_blake2b256_keyed(key, init ? ns_r : ns_i, idr);
+    uint64_t *o = reinterpret_cast<uint64_t *>(&out[i]);
+#pragma unroll
+    for (int j = 0; j < 4; j++) { o[j] = idl[j]; o[4 + j] = idr[j]; }
+    uint32_t k[8], x[16];
+    const uint32_t *sw = reinterpret_cast<const uint32_t *>(seed);
+#pragma unroll
+    for (int j = 0; j < 8; j++) k[j] = sw[j];
+    ss_chacha_block(k, 0, i, call_no, 0x73796d72u, x);
+    uint32_t *ho = reinterpret_cast<uint32_t *>(out[i].header);
+#pragma unroll
+    for (int j = 0; j < 6; j++) ho[j] = x[j];
 }
 
 // Stream set-up (libsodium init_push/init_pull): one thread per
@@ -1004,6 +1041,7 @@ const char *symrelay_strerror(int code) {
         case SYMRELAY_EAGAIN: return "ring full, try again";
         case SYMRELAY_ENOMEM: return "out of memory / slots";
         case SYMRELAY_ENOENT: return "no such slot or ticket";
+        case SYMRELAY_EPROTO: return "protocol violation by the peer";
         case SYMRELAY_ECUDA: return "CUDA failure";
         default: return "unknown error";
     }
@@ -1408,6 +1446,67 @@ int symrelay_stream_export(symrelay_ctx *ctx, uint32_t slot, uint8_t tx_state[SY
     CU(ctx, cudaStreamSynchronize(sh.s_init));
     if (tx_state) { memcpy(tx_state, buf, 44); memset(tx_state + 44, 0, 8); }
     if (rx_state) { memcpy(rx_state, buf + 48, 44); memset(rx_state + 44, 0, 8); }
+    return 0;
+}
+
+// ---- connection set-up in batch -------------------------------------------------------------------
+int symrelay_connect_batch(symrelay_ctx *ctx, int gpu_index, uint32_t n, const uint8_t *handshake_hashes, const uint8_t *initiator,
+                           const uint8_t ns_initiator[32], const uint8_t ns_responder[32], const uint8_t *seed32,
+                           uint8_t *local_ids, uint8_t *remote_ids, uint8_t *headers, uint8_t *first_messages) {
+    if (!ctx || gpu_index < 0 || gpu_index >= ctx->n_gpus) return SYMRELAY_EINVAL;
+    if (n == 0) return 0;
+    if (!handshake_hashes || !initiator || !ns_initiator || !ns_responder)
+        return fail(ctx, SYMRELAY_EINVAL, "symrelay_connect_batch: null argument");
+    Shard &sh = ctx->shard[gpu_index];
+    std::lock_guard<std::mutex> lk(sh.mu);
+    CU(ctx, set_device(sh.dev));
+    uint8_t seed[32];
+    if (seed32) memcpy(seed, seed32, 32);
+    else {   // 32 fresh random bytes from the kernel's generator
+        size_t got = 0;
+        if (FILE *f = fopen("/dev/urandom", "rb")) { got = fread(seed, 1, 32, f); fclose(f); }
+        if (got != 32) return fail(ctx, SYMRELAY_EINVAL, "symrelay_connect_batch: no entropy source for the headers");
+    }
+    const uint32_t chunk = 16384;
+    uint8_t *d_buf = nullptr;   // recs ‖ outs ‖ ns pair ‖ seed (set-up path: allocation here is fine)
+    const size_t recs_b = (size_t)chunk * sizeof(SsConnRec), outs_b = (size_t)chunk * sizeof(SsConnOut);
+    CU(ctx, cudaMalloc(&d_buf, recs_b + outs_b + 96));
+    std::vector<SsConnRec> recs(chunk);
+    std::vector<SsConnOut> outs(chunk);
+    uint8_t nsseed[96];
+    memcpy(nsseed, ns_initiator, 32); memcpy(nsseed + 32, ns_responder, 32); memcpy(nsseed + 64, seed, 32);
+    cudaError_t e = cudaMemcpyAsync(d_buf + recs_b + outs_b, nsseed, 96, cudaMemcpyHostToDevice, sh.s_init);
+    for (uint32_t at = 0; at < n && e == cudaSuccess; at += chunk) {
+        const uint32_t m = n - at < chunk ? n - at : chunk;
+        for (uint32_t i = 0; i < m; i++) {
+            memcpy(recs[i].hash, handshake_hashes + 64ull * (at + i), 64);
+            recs[i].initiator = initiator[at + i] ? 1u : 0u;
+        }
+        e = cudaMemcpyAsync(d_buf, recs.data(), (size_t)m * sizeof(SsConnRec), cudaMemcpyHostToDevice, sh.s_init);
+        if (e != cudaSuccess) break;
+        ss_connect_kernel<<<(m + 127) / 128, 128, 0, sh.s_init>>>(reinterpret_cast<const SsConnRec *>(d_buf), m,
+                                                                  reinterpret_cast<const uint4 *>(d_buf + recs_b + outs_b),
+                                                                  reinterpret_cast<const uint4 *>(d_buf + recs_b + outs_b + 64),
+                                                                  (uint32_t)(at / chunk), reinterpret_cast<SsConnOut *>(d_buf + recs_b));
+        ctx->launches++;
+        e = cudaMemcpyAsync(outs.data(), d_buf + recs_b, (size_t)m * sizeof(SsConnOut), cudaMemcpyDeviceToHost, sh.s_init);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(sh.s_init);
+        if (e != cudaSuccess) break;
+        for (uint32_t i = 0; i < m; i++) {
+            const size_t k = at + i;
+            if (local_ids) memcpy(local_ids + 32 * k, outs[i].id_local, 32);
+            if (remote_ids) memcpy(remote_ids + 32 * k, outs[i].id_remote, 32);
+            if (headers) memcpy(headers + 24 * k, outs[i].header, 24);
+            if (first_messages) {   // uint24-LE(56) ‖ streamId ‖ header: secret-stream's first frame, sent in the clear
+                uint8_t *fm = first_messages + 59 * k;
+                fm[0] = 56; fm[1] = 0; fm[2] = 0;
+                memcpy(fm + 3, outs[i].id_local, 32);
+                memcpy(fm + 35, outs[i].header, 24);
+            }
+        }
+    }
+    cudaFree(d_buf);
+    if (e != cudaSuccess) return fail(ctx, SYMRELAY_ECUDA, "symrelay_connect_batch: %s", cudaGetErrorString(e));
     return 0;
 }
 

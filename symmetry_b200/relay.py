@@ -26,6 +26,7 @@ F_RUN = 0x10000000
 LEN_MASK = 0x00FFFFFF
 ST_OK, ST_BAD_MAC, ST_TOO_SHORT, ST_EXTRACT_THROW, ST_EXTRACT_UNSUPPORTED, ST_RETRY, ST_FAILED = 0, 1, 2, 3, 4, 5, 6
 EAGAIN = -11
+EPROTO = -71
 PROVIDER_DEFAULT, PROVIDER_OLLAMA, PROVIDER_LLAMACPP = 0, 1, 2
 STATEBYTES, HEADERBYTES, KEYBYTES, WIRE_OVERHEAD = 52, 24, 32, 20
 
@@ -206,6 +207,27 @@ class SymRelay:
         if n < 0 and n != EAGAIN:
             self._check(n)
         return [tick[i] for i in range(max(n, 0))], used.value
+
+    def connect_batch(self, handshake_hashes: np.ndarray, initiator, ns_initiator: bytes, ns_responder: bytes,
+                      seed: bytes | None = None, gpu_index: int = 0):
+        """Connection set-up for n new connections at once: (local ids [n,32], remote ids [n,32], headers [n,24],
+        first messages [n,59]) -- the BLAKE2b stream ids and fresh secretstream headers secret-stream computes per
+        connection before its first message."""
+        hh = np.ascontiguousarray(handshake_hashes, dtype=np.uint8)
+        n = len(hh)
+        ini = np.ascontiguousarray(initiator, dtype=np.uint8)
+        lid, rid = np.zeros((n, 32), np.uint8), np.zeros((n, 32), np.uint8)
+        hdr, fm = np.zeros((n, 24), np.uint8), np.zeros((n, 59), np.uint8)
+        self._check(self.lib.symrelay_connect_batch(self.ctx, gpu_index, n, _ptr(hh), _ptr(ini), bytes(ns_initiator),
+                                                    bytes(ns_responder), _bytes_ptr(seed), _ptr(lid), _ptr(rid), _ptr(hdr), _ptr(fm)))
+        return lid, rid, hdr, fm
+
+    def rx_expect_header(self, slot: int, rx_key: bytes, expected_stream_id: bytes | None = None) -> None:
+        """The next frame fed on this slot is the peer's first message (uint24(56) ‖ streamId ‖ header)."""
+        self._check(self.lib.symrelay_rx_expect_header(self.ctx, int(slot), bytes(rx_key), _bytes_ptr(expected_stream_id)))
+
+    def set_keepalive(self, slot: int, on: bool = True) -> None:
+        self._check(self.lib.symrelay_stream_set_keepalive(self.ctx, int(slot), 1 if on else 0))
 
     def event_fd(self) -> int:
         """eventfd that becomes readable when a batch of the per-frame front end has finished (what the N-API shim

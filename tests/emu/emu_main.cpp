@@ -40,6 +40,15 @@ static void *lane_main(void *p) {
     return nullptr;
 }
 
+#include "../../symmetry_b200/csrc/ss_blake2b.cuh"
+// the product's BLAKE2b (stream ids) for a CPU check against libsodium's crypto_generichash
+extern "C" void emu_blake2b256_keyed(const uint8_t key[64], const uint8_t msg[32], uint8_t out[32]) {
+    uint64_t k[8], m[4], o[4];
+    memcpy(k, key, 64); memcpy(m, msg, 32);
+    sb_blake2b256_keyed(k, m, o);
+    memcpy(out, o, 32);
+}
+
 extern "C" int64_t emu_plan(const symrelay_desc *desc, uint32_t n, symrelay_tile *tiles, uint32_t max_tiles,
                             uint32_t *n_bulk) {
     return symrelay_plan_inline(desc, n, tiles, max_tiles, n_bulk);

@@ -160,3 +160,19 @@ def test_strided_tiles_mid_size_frames(be, length):
     assert n_bulk == len(tiles) and all((int(t["n_kind"]) >> 24) & 63 in (2, 4, 8) for t in tiles)
     pc.seal_open_roundtrip(be, lens, [i % 4 for i in range(n)], seed=500 + length, chain=2, corrupt=(0, 7, 18),
                            speculative_min_len=385)
+
+
+def test_stream_id_blake2b_matches_libsodium(emu_lib):
+    """secret-stream's stream id = crypto_generichash(out32, namespace, key = handshake hash): the product's BLAKE2b
+    (ss_blake2b.cuh, run here on the CPU) against libsodium's, random keys and messages."""
+    import random
+
+    import nacl.bindings as nb
+
+    rng = random.Random(77)
+    emu_lib.emu_blake2b256_keyed.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
+    for _ in range(200):
+        key, msg = rng.randbytes(64), rng.randbytes(32)
+        out = C.create_string_buffer(32)
+        emu_lib.emu_blake2b256_keyed(key, msg, out)
+        assert out.raw == nb.crypto_generichash_blake2b_salt_personal(msg, digest_size=32, key=key)
