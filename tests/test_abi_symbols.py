@@ -95,3 +95,17 @@ def test_bucketed_planner_covers_every_descriptor_once(tmp_path):
                     os.path.join(ROOT, "symmetry_b200", "csrc", "plan_scan_avx2.cpp")], check=True)
     res = subprocess.run([exe], capture_output=True, text=True)
     assert res.returncode == 0 and "valid=1" in res.stdout, res.stdout + res.stderr
+
+
+def test_napi_shim_is_valid_c_against_the_header():
+    """addon/symrelay_napi.c cannot be built here (no node_api.h, no Node), but it must at least be valid C that agrees
+    with include/symrelay.h: every ABI call it makes is type-checked against the header's prototypes."""
+    import subprocess
+
+    res = subprocess.run(["gcc", "-fsyntax-only", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
+                          os.path.join(ROOT, "addon", "symrelay_napi.c")], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    src = open(os.path.join(ROOT, "addon", "symrelay_napi.c")).read()
+    for fn in ("symrelay_submit_seal", "symrelay_rx_feed", "symrelay_poll", "symrelay_release", "symrelay_event_fd",
+               "symrelay_rx_expect_header", "symrelay_stream_set_keepalive", "symrelay_connect_batch"):
+        assert fn + "(" in src, f"the shim does not bind {fn}"
