@@ -342,6 +342,11 @@ SYMRELAY_API int symrelay_event_fd(symrelay_ctx *ctx);
 /* frames/batches handled by the front end and the p50/p99/p99.9 of their added latency */
 SYMRELAY_API int symrelay_sched_stats(symrelay_ctx *ctx, symrelay_sched_stats_t *out);
 SYMRELAY_API int symrelay_sched_reset_stats(symrelay_ctx *ctx);
+/* How the fused extractor fared on the front end's SYMRELAY_F_EXTRACT frames, per provider kind (enum symrelay_provider):
+ * counts[4 * kind + j], j = 0 delta extracted, 1 the reference would have thrown (SYMRELAY_ST_EXTRACT_THROW), 2 handed back
+ * to the host helper (SYMRELAY_ST_EXTRACT_UNSUPPORTED: each of those costs the stream a second batch), 3 anything else.
+ * Tells an operator how often real provider output leaves the GPU extractor's domain.  No counterpart in the reference. */
+SYMRELAY_API int symrelay_extract_stats(symrelay_ctx *ctx, uint64_t counts[12]);
 
 /* Measurement aid (bench.py): sustained integer throughput of this GPU in
  * Tera-ops/s for ChaCha20's ADD:XOR:ROTATE 1:1:1 mix and for 32x32->64

@@ -22,7 +22,7 @@ EXPORTS = (
     "symrelay_flush", "symrelay_poll", "symrelay_poll_wait", "symrelay_release", "symrelay_sched_stats",
     "symrelay_sched_reset_stats", "symrelay_batch_device_runs", "symrelay_batch_device_runs_static",
     "symrelay_rx_feed", "symrelay_event_fd", "symrelay_connect_batch", "symrelay_rx_expect_header",
-    "symrelay_stream_set_keepalive",
+    "symrelay_stream_set_keepalive", "symrelay_extract_stats",
 )
 
 
@@ -113,6 +113,8 @@ def load() -> C.CDLL:
     L.symrelay_rx_expect_header.argtypes = [vp, u32, vp, vp]
     L.symrelay_stream_set_keepalive.restype = ci
     L.symrelay_stream_set_keepalive.argtypes = [vp, u32, ci]
+    L.symrelay_extract_stats.restype = ci
+    L.symrelay_extract_stats.argtypes = [vp, C.POINTER(u64)]
     L.symrelay_event_fd.restype = ci
     L.symrelay_event_fd.argtypes = [vp]
     L.symrelay_flush.restype = ci

@@ -754,6 +754,7 @@ struct symrelay_ctx {
     Sched sched[8];
     symrelay_opts opts{};
     std::vector<uint8_t> slot_state;      // 0 free, 1 open
+    std::vector<uint8_t> slot_kind;       // provider kind given at open (extractor statistics)
     std::vector<uint32_t> free_slots[8];  // per GPU (slot % n_gpus == gpu)
     std::mutex mu;        // the slot table (slot_state, free_slots) only; taken before a shard's lock, never after
     std::mutex err_mu;    // err
@@ -1277,6 +1278,7 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
         }
     }
     ctx->slot_state.assign(ctx->opts.max_streams, 0);
+    ctx->slot_kind.assign(ctx->opts.max_streams, 0);
     for (uint32_t s = ctx->opts.max_streams; s-- > 0;) ctx->free_slots[s % (uint32_t)n_gpus].push_back(s);
     return ctx;
 }
@@ -1355,6 +1357,7 @@ int symrelay_stream_open_batch(symrelay_ctx *ctx, uint32_t n, const uint8_t *tx_
         slots_out[i] = ctx->free_slots[g].back();
         ctx->free_slots[g].pop_back();
         ctx->slot_state[slots_out[i]] = 1;
+        ctx->slot_kind[slots_out[i]] = (uint8_t)(provider_kind < 0 || provider_kind > 2 ? 0 : provider_kind);
         g = (g + 1) % ctx->n_gpus;
     }
     for (int gi = 0; gi < ctx->n_gpus; gi++) {
@@ -1399,6 +1402,7 @@ int symrelay_stream_open(symrelay_ctx *ctx, const uint8_t *tx_key, const uint8_t
     const uint32_t slot = ctx->free_slots[g].back();
     ctx->free_slots[g].pop_back();
     ctx->slot_state[slot] = 1;
+    ctx->slot_kind[slot] = (uint8_t)(provider_kind < 0 || provider_kind > 2 ? 0 : provider_kind);
     Shard &sh = ctx->shard[g];
     std::lock_guard<std::mutex> slk(sh.mu);
     sched_slot_reset(ctx, slot);

@@ -261,6 +261,13 @@ class SymRelay:
         self._check(self.lib.symrelay_sched_stats(self.ctx, C.byref(st)))
         return {f: getattr(st, f) for f, _ in st._fields_}
 
+    def extract_stats(self) -> dict:
+        """{provider kind: {"ok", "throw", "unsupported", "other"}} for the front end's F_EXTRACT frames."""
+        c = (C.c_uint64 * 12)()
+        self._check(self.lib.symrelay_extract_stats(self.ctx, c))
+        names = ("ok", "throw", "unsupported", "other")
+        return {k: {nm: int(c[4 * k + j]) for j, nm in enumerate(names)} for k in range(3)}
+
     def probe_int_peak(self, gpu_index: int = 0):
         """(arx_tops, imad_tops): measured integer throughput, the ALU roofline denominators."""
         a, m = C.c_double(0), C.c_double(0)

@@ -182,6 +182,11 @@ def test_relay_loop_mirror_against_reference_semantics(relay):
         if i % 10 == 5 and not aborted:
             assert p.unsupported == [2]
     assert any(p.aborted for p in peers) and any(not p.aborted for p in peers)
+    # the library counted how the fused extractor fared, per provider kind: every connection with the 1e21 chunk that
+    # got that far cost one UNSUPPORTED, every aborted one a THROW
+    st = relay.extract_stats()[sb.PROVIDER_OLLAMA]
+    assert st["unsupported"] == sum(1 for p in peers if p.unsupported) and st["throw"] == sum(1 for p in peers if p.aborted)
+    assert st["ok"] > 0 and st["other"] == 0 and relay.extract_stats()[sb.PROVIDER_DEFAULT]["ok"] == 0
 
 
 def test_deadline_flush_and_latency_stats():
