@@ -713,6 +713,17 @@ def run_ours(args):
         except Exception as e:  # the headline numbers do not depend on it
             latency = {"error": repr(e)}
 
+    # ---------------- the step after the path: what sending the sealed frames costs the host ----------
+    udp = None
+    if job.world == 1 and not args.no_latency:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import udp_bench
+
+            udp = udp_bench.run(frames=2 * n if name == "c2" else 2048, nbytes=84, batches=60)
+        except Exception as e:
+            udp = {"error": repr(e)}
+
     h2d = lay.in_bytes + 2 * n * 16 + x["n_tiles_full"] * 8
     d2h = lay.out_bytes + 2 * n * 4
     e2e_ms = (e2e_sec / K2 * 1e3) if K2 else None
@@ -746,6 +757,8 @@ def run_ours(args):
         line["cpu_baseline"] = cpu
     if latency:
         line["latency"] = latency
+    if udp:
+        line["udp_send"] = udp
     print(json.dumps(line), flush=True)
     job.close()
 

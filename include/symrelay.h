@@ -348,6 +348,31 @@ SYMRELAY_API int symrelay_sched_reset_stats(symrelay_ctx *ctx);
  * Tells an operator how often real provider output leaves the GPU extractor's domain.  No counterpart in the reference. */
 SYMRELAY_API int symrelay_extract_stats(symrelay_ctx *ctx, uint64_t counts[12]);
 
+/* ---- after the path: sealed frames to datagrams, many per system call ----
+ * In the reference each `peer.write` ends in udx-native 1.10.3 (package-lock.json:6241-6253; UDXStream / UDXSocket are
+ * typed at src/types.ts:91-122) giving the kernel ONE packet per frame.  symrelay_udp_send_batch takes the completions
+ * symrelay_poll delivered (sealed frames only; others are skipped), cuts every wire frame into datagrams of at most `mtu`
+ * bytes -- a 16-byte symrelay_udp_hdr plus a slice gathered straight from the pinned ring, no copy -- and hands them to
+ * the kernel up to 1,024 per sendmmsg(2).  dst[i] / dst_len[i]: the destination of completion i (NULL on a connected
+ * socket); conn_id[i]: what the receiver knows the connection by; stream_off[i]: in/out, the connection's outbound byte
+ * count so far (the receiver orders slices by it and feeds them to symrelay_rx_feed).  Returns the number of datagrams
+ * sent, SYMRELAY_EAGAIN when the socket buffer is full (stats say how far it got), SYMRELAY_EINVAL otherwise.  It does not
+ * speak UDX: acknowledgements, retransmission and congestion control stay in udx-native; this is the send primitive.
+ * SYMRELAY_UDP_ONE_PER_CALL reproduces the reference's one system call per packet, for comparison. */
+#define SYMRELAY_UDP_MAGIC 0x554d5953u /* "SYMU" */
+#define SYMRELAY_UDP_HDR 16u
+#define SYMRELAY_UDP_ONE_PER_CALL 1u
+typedef struct symrelay_udp_hdr {
+    uint32_t magic, conn;
+    uint64_t offset; /* of this slice in the connection's outbound byte stream */
+} symrelay_udp_hdr;
+typedef struct symrelay_udp_stats {
+    uint64_t frames, datagrams, syscalls, payload_bytes;
+} symrelay_udp_stats;
+SYMRELAY_API int symrelay_udp_send_batch(int fd, const symrelay_completion *comp, int n, const void *const *dst,
+                                         const uint32_t *dst_len, const uint32_t *conn_id, uint64_t *stream_off, uint32_t mtu,
+                                         uint32_t flags, symrelay_udp_stats *stats);
+
 /* Measurement aid (bench.py): sustained integer throughput of this GPU in
  * Tera-ops/s for ChaCha20's ADD:XOR:ROTATE 1:1:1 mix and for 32x32->64
  * multiply-adds -- the integer roofline denominators.

@@ -22,7 +22,7 @@ EXPORTS = (
     "symrelay_flush", "symrelay_poll", "symrelay_poll_wait", "symrelay_release", "symrelay_sched_stats",
     "symrelay_sched_reset_stats", "symrelay_batch_device_runs", "symrelay_batch_device_runs_static",
     "symrelay_rx_feed", "symrelay_event_fd", "symrelay_connect_batch", "symrelay_rx_expect_header",
-    "symrelay_stream_set_keepalive", "symrelay_extract_stats",
+    "symrelay_stream_set_keepalive", "symrelay_extract_stats", "symrelay_udp_send_batch",
 )
 
 
@@ -37,6 +37,10 @@ class SymrelayCompletion(C.Structure):
     _fields_ = [("ticket", C.c_int64), ("slot", C.c_uint32), ("status", C.c_uint32), ("data", C.c_void_p),
                 ("len", C.c_uint32), ("flags", C.c_uint32), ("delta", C.c_void_p), ("delta_len", C.c_uint32),
                 ("pad", C.c_uint32), ("latency_ns", C.c_uint64)]
+
+
+class SymrelayUdpStats(C.Structure):
+    _fields_ = [("frames", C.c_uint64), ("datagrams", C.c_uint64), ("syscalls", C.c_uint64), ("payload_bytes", C.c_uint64)]
 
 
 class SymrelaySchedStats(C.Structure):
@@ -113,6 +117,8 @@ def load() -> C.CDLL:
     L.symrelay_rx_expect_header.argtypes = [vp, u32, vp, vp]
     L.symrelay_stream_set_keepalive.restype = ci
     L.symrelay_stream_set_keepalive.argtypes = [vp, u32, ci]
+    L.symrelay_udp_send_batch.restype = ci
+    L.symrelay_udp_send_batch.argtypes = [ci, C.POINTER(SymrelayCompletion), ci, vp, vp, vp, vp, u32, u32, C.POINTER(SymrelayUdpStats)]
     L.symrelay_extract_stats.restype = ci
     L.symrelay_extract_stats.argtypes = [vp, C.POINTER(u64)]
     L.symrelay_event_fd.restype = ci

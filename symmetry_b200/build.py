@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsymrelay.so")
-SOURCES = ["symrelay.cu", "plan_scan_avx2.cpp"]
+SOURCES = ["symrelay.cu", "plan_scan_avx2.cpp", "udp_batch.cpp"]
 # everything symrelay.cu includes: stale() rebuilds when any of them is newer than the .so
 HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".inc"))) + [
     os.path.join("..", "..", "include", "symrelay.h")]
