@@ -214,6 +214,36 @@ def test_deadline_flush_and_latency_stats():
         assert st["frames"] == 1000 and 0 < st["p50_us"] < 50000 and st["p99_us"] >= st["p50_us"]
 
 
+def test_transcript_written_from_gpu_extractor_output(relay, tmp_path):
+    """`saveCompletion` (provider.ts:264-269, 277-297) fed with the deltas the GPU extractor produced
+    while sealing -- split surrogate pairs across chunks, a lone surrogate, escapes -- writes the file the reference
+    would have written from its JS string (restated with the oracle's deltas)."""
+    import symmetry_b200 as sb
+    from symmetry_b200 import provider, synth
+
+    rng = random.Random(14)
+    peers, keys = [], []
+    for i in range(40):
+        k, h = rng.randbytes(32), rng.randbytes(24)
+        keys.append(k)
+        slot = relay.open_stream(k, h, None, None, provider=sb.PROVIDER_OLLAMA)
+        chunks = synth.chat_chunks(12, seed=21, stream_id=i)
+        chunks.insert(3, b'data: {"choices":[{"delta":{"content":"\\ud83d"}}]}\n\n')     # halves of one pair in two chunks
+        chunks.insert(4, b'data: {"choices":[{"delta":{"content":"\\ude00 \\ud800! \\"q\\" \\\\ \\n"}}]}\n\n')
+        peers.append(provider.PeerRelayState(slot, f"key-{i}", chunks))
+    provider.handle_inference_requests(relay, peers)
+    msgs = [{"role": "user", "content": "hi"}]
+    for i, p in enumerate(peers):
+        assert not p.aborted
+        want = b"".join(ex.extract("ollama", c)[1] for c in p.frames[1:-1])
+        assert p.completion == want, "GPU deltas differ from the oracle's"
+        a = provider.saveCompletion(p.completion, keys[i], i, msgs, str(tmp_path))
+        b = provider.saveCompletion(want, keys[i], i + 1000, msgs, str(tmp_path))
+        ta, tb = open(a, encoding="utf-8").read(), open(b, encoding="utf-8").read()
+        assert ta == tb and "\U0001F600" in ta and "\\ud800!" in ta
+        assert json.loads(ta)[1]["role"] == "assistant"
+
+
 def test_event_fd_wakes_the_loop_and_flushes_on_deadline():
     """the event loop must never block on the GPU nor poll for it.  The context's eventfd becomes readable
     when a batch has finished, and the watcher thread performs the deadline flush, so a loop that only select()s on
