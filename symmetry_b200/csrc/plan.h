@@ -41,7 +41,8 @@ static inline uint32_t symrelay_seg_lanes(uint32_t nc) {
     while ((nc + k) / k > 5u) k <<= 1;   // ceil((nc + 1) / k) virtual blocks per lane
     return k > 32u ? 32u : k;
 }
-#define SYMRELAY_THREAD_TILE_BIG_BUCKET 8192u   /* a size class with this many frames fills the GPU with thread tiles whatever the frame size */
+#define SYMRELAY_THREAD_TILE_BIG_BUCKET 8192u   /* a size class (<= 32 blocks) with this many frames fills the GPU with thread tiles */
+#define SYMRELAY_THREAD_TILE_HUGE_BATCH 98304u  /* a uniform batch of BIG frames with this many of them (3,072 warps: ~20 per SM) does too */
 
 // Small tiles first (packed, or thread-per-frame tiles: bit 17 of n_kind, 32 consecutive frames with
 // the same block count, one per lane), bulk tiles after them.  Runs on the host's per-batch critical
@@ -125,9 +126,10 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
     if (bad) return SYMRELAY_EINVAL;
     uint64_t n_tiles = 0;
     uint32_t n_bulk = 0;
-    if (n && nc_min == nc_max && nc_max <= 32u) {
+    if (n && nc_min == nc_max && (nc_max <= 32u || n >= SYMRELAY_THREAD_TILE_HUGE_BATCH)) {
         // every frame has the same block count (token streaming, BASELINE config 2): the tiles follow in
         // closed form -- no per-descriptor walk
+        // (frames of more than 32 blocks get here only in a huge uniform batch: one lane per frame, throughput-bound)
         const bool thread_ok = (n >= SYMRELAY_THREAD_TILE_MIN_FRAMES && nc_max <= SYMRELAY_THREAD_TILE_MAX_BLOCKS) ||
                                n >= SYMRELAY_THREAD_TILE_BIG_BUCKET;
         if (!thread_ok && nc_max > SYMRELAY_THREAD_TILE_MAX_BLOCKS) {
@@ -149,6 +151,15 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
                 if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = 32u | (1u << 17); }
                 n_tiles++;
             }
+        if (nc_max > 32u) {   // huge batch of big frames: the last < 32 of them as ordinary bulk tiles
+            const uint32_t rest = n - i;
+            for (; i < n; i++) {
+                if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = 1u | (1u << 16); }
+                n_tiles++;
+            }
+            if (n_bulk_out) *n_bulk_out = rest;
+            return (int64_t)n_tiles;
+        }
         for (; i < n; i += per) {
             const uint32_t k = n - i < per ? n - i : per;
             if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = k; }
