@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const Ss
 #define PK_RUNNING 1u
 #define PK_EXITING 2u
 #define PK_EXITED 3u
-#define PK_CHUNK 8192u     // bytes of results one drain ticket moves to the host
+#define PK_CHUNK 4096u     // bytes of results one drain ticket moves to the host
 
 struct PkSlot {            // 128 bytes; written by the host, read by the poller warp
     const SsDesc *desc;
@@ -443,7 +443,11 @@ __device__ void pk_drain(PkHost *host, PkDev *dev, unsigned long long first_seq,
         pk_fence_sys();
         __syncwarp();
         if (lane == 0 && atomicAdd(&e->sysdone, 1u) + 1u == (uint32_t)(pk_ld_u64(&e->drange) & 0xffffffull)) {
-            pk_fence_sys();
+            // Every drain warp fenced its rows to system scope BEFORE it counted itself (release); this is the
+            // acquire side of that device-scope counter, so a device-scope fence completes the chain: the flag below
+            // is ordered after all of the batch's rows for any observer, the host included.  (A second system-scope
+            // fence here cost 3-5 us of every batch's latency.)
+            pk_fence_gpu();
             host->done[seq % PK_RING].v = seq + 1ull;
             if (ts) ts[(seq % 4096ull) * PK_TS_WORDS + 7] = pk_now();
             atomicAdd(&dev->sys_completed, 1ull);
