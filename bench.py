@@ -501,8 +501,7 @@ def measure_device(job: Job, name: str, K: int, W: int, no_graph: bool, relay=No
         "streams_per_gpu": n,
         "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
-                     "kernel": "ss_packed_kernel" if nb_full == 0 else ("ss_bulk_kernel" if nb_full == len(tiles_full)
-                                                                        else "ss_packed_kernel + ss_bulk_kernel (concurrent)"),
+                     "kernel": kernel_label(tiles_full, nb_full),
                      "algorithmic_bytes_per_launch": alg_bytes,
                      "note": "the path is integer-ALU bound (SURVEY 8(d)); see alu_roofline.  traffic: measured only "
                              "under ncu, see traffic_ncu"},
@@ -519,6 +518,25 @@ def measure_device(job: Job, name: str, K: int, W: int, no_graph: bool, relay=No
     extra = {"lens": lens, "lay": lay, "keys": keys, "hdrs": hdrs, "sample": sample, "window": (t_w0, t_w1),
              "relay": relay, "n_tiles_full": len(tiles_full), "plan_mode": plan_mode, "R": R}
     return res, extra
+
+
+def kernel_label(tiles, n_bulk) -> str:
+    """Which of the library's tile kernels a batch with these tiles launches (see launch_tiles in csrc/symrelay.cu)."""
+    kinds = tiles["n_kind"]
+    small, bulk = kinds[: len(tiles) - n_bulk], kinds[len(tiles) - n_bulk:]
+    names = []
+    if len(small) > 148 * 8:
+        if ((small >> 17) & 1).any():
+            names.append("ss_thread_kernel")
+        if (((small >> 17) & 1) == 0).any():
+            names.append("ss_packed_only_kernel")
+    elif len(small):
+        names.append("ss_packed_kernel")
+    if len(bulk) and (((bulk >> 24) & 63) != 0).any():
+        names.append("ss_strided_kernel")
+    if len(bulk) and (((bulk >> 24) & 63) == 0).any():
+        names.append("ss_bulk_kernel")
+    return " + ".join(names) + (" (concurrent)" if len(names) > 1 else "")
 
 
 def traffic_ncu(name: str):

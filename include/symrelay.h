@@ -311,7 +311,11 @@ SYMRELAY_API int64_t symrelay_submit_open(symrelay_ctx *ctx, uint32_t slot, cons
  *     Returns the number of frames submitted (their tickets in tickets[0..)), *consumed = bytes of `seg`
  *     taken; when the ring is full it returns what it could (or SYMRELAY_EAGAIN if nothing) and the caller
  *     feeds the rest of the segment after draining completions.  A completion with SYMRELAY_ST_RETRY (only
- *     behind a REKEY-tagged frame) must be resubmitted with symrelay_submit_open. */
+ *     behind a REKEY-tagged frame or a counter wrap inside a run) must be resubmitted with symrelay_submit_open, in
+ *     the order the completions arrive.  Frames of that stream that were already submitted behind the RETRY frames
+ *     (a later segment, a later batch) were opened against a state that lags behind them: they are delivered as
+ *     SYMRELAY_ST_RETRY as well, not as SYMRELAY_ST_BAD_MAC -- resubmit them too, after the earlier ones.  Only a
+ *     SYMRELAY_ST_BAD_MAC means what it means in the reference: the stream is dead. */
 SYMRELAY_API int symrelay_rx_feed(symrelay_ctx *ctx, uint32_t slot, const uint8_t *seg, uint32_t n, uint32_t *consumed,
                                   int64_t *tickets, int max_tickets);
 /* symrelay_rx_expect_header  <-  secret-stream's handling of the connection's FIRST message: before any encrypted

@@ -214,6 +214,55 @@ def test_deadline_flush_and_latency_stats():
         assert st["frames"] == 1000 and 0 < st["p50_us"] < 50000 and st["p99_us"] >= st["p50_us"]
 
 
+def test_frames_already_queued_behind_a_rekey_run_come_back_retry_not_forged(relay):
+    """A run stops at a REKEY-tagged frame (the frames behind it used the wrong key: RETRY).  Frames of the same
+    stream that were fed BEFORE the caller saw those completions were opened against the lagging state; they are
+    not forgeries and must come back RETRY too, so that a caller who resubmits every RETRY in arrival order ends up
+    with the whole stream -- the reference, one pull at a time, never sees any of this."""
+    import symmetry_b200 as sb
+
+    rng = random.Random(15)
+    k, h = rng.randbytes(32), rng.randbytes(24)
+    slot = relay.open_stream(None, None, k, h)
+    sender = ls.State(k, h)
+    msgs = [rng.randbytes(n) for n in (10, 70, 0, 300, 64, 5, 1000, 33)]
+    tags = [0, 2, 0, 0, 0, 0, 0, 0]                       # frame 1 carries TAG_REKEY
+    frames = [sender.seal_frame(m, t) for m, t in zip(msgs, tags)]
+    tk1, used = relay.rx_feed(slot, b"".join(frames[:4]))           # one segment: a run of four
+    assert used == sum(map(len, frames[:4])) and len(tk1) == 4
+    relay.flush()
+    tk2, used = relay.rx_feed(slot, b"".join(frames[4:6]))          # the next segment, before any completion was read
+    relay.flush()
+    tk3, used = relay.rx_feed(slot, b"".join(frames[6:]))
+    relay.flush()
+    tickets = tk1 + tk2 + tk3
+    got = {}
+    while len(got) < len(tickets):
+        for c in relay.poll(wait=True):
+            got[c["ticket"]] = c
+    st = [got[t]["status"] for t in tickets]
+    assert st[:2] == [0, 0] and got[tickets[0]]["data"] == msgs[0] and got[tickets[1]]["tag"] == 2
+    assert st[2:] == [sb.relay.ST_RETRY] * 6, st            # none of them BAD_MAC
+    # resubmit in arrival order (a few per batch): everything opens, the chain is libsodium's
+    redo = []
+    for i in range(2, 8):
+        redo.append((relay.submit_open(slot, frames[i]), i))
+        if i % 2:
+            relay.flush()
+    relay.flush()
+    got = {}
+    while len(got) < len(redo):
+        for c in relay.poll(wait=True):
+            got[c["ticket"]] = c
+        relay.flush()
+    for t, i in redo:
+        assert got[t]["status"] == 0 and got[t]["data"] == msgs[i], i
+    mirror = ls.State(k, h)
+    for f in frames:
+        mirror.open_frame(f)
+    assert relay.export(slot)[1] == mirror.raw
+
+
 def test_transcript_written_from_gpu_extractor_output(relay, tmp_path):
     """`saveCompletion` (provider.ts:264-269, 277-297) fed with the deltas the GPU extractor produced
     while sealing -- split surrogate pairs across chunks, a lone surrogate, escapes -- writes the file the reference
