@@ -1589,17 +1589,6 @@ int symrelay_batch_device_runs_static(symrelay_ctx *ctx, int gpu_index, const sy
 // ---- persistent kernel: host side ------------------------------------------------------------
 // Ordinary launches are about to go to s_k: the resident kernel must leave first (stream order then keeps every
 // batch in submission order).  No waiting here -- the launches simply queue behind it.
-// Copy into a pinned block the GPU is about to read, with streaming stores: the lines were last touched by the
-// device's PCIe reads, ordinary stores would first have to pull them back into this core's cache.  dst 16-byte
-// aligned.  Ordered before the doorbell / the launch by the _mm_sfence() there.
-static inline void nt_copy(void *dst, const void *src, size_t bytes) {
-    __m128i *d = reinterpret_cast<__m128i *>(dst);
-    const __m128i *q = reinterpret_cast<const __m128i *>(src);
-    size_t i = 0;
-    for (; i + 16 <= bytes; i += 16) _mm_stream_si128(d++, _mm_loadu_si128(q++));
-    if (i < bytes) memcpy(d, q, bytes - i);
-}
-
 static inline uint32_t pk_version(uint32_t stamp) { return (stamp & 0x7fffffu) | 0x800000u; }   // 24 bits, never 0, repeats every 8 M batches
 
 // Waits until every batch handed to the resident kernel has finished (rare paths only).
@@ -1900,26 +1889,36 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         const uint32_t now = sh.stamp, floor = sh.pk_floor, runf = SYMRELAY_F_OPEN | SYMRELAY_F_RUN;
         // ver[i]: the stamp frame i's stream state has to carry before the resident kernel may use it = the last
         // resident-kernel batch that went through that (slot, direction), 0 when that one is long done (stamps up
-        // to pk_floor were followed by an ordinary launch on the same stream).  Collected in cache, then streamed
-        // behind the descriptors in the control block.
-        static thread_local std::vector<uint32_t> verv;
-        if (verv.size() < n) verv.resize(n);
-        uint32_t *ver = verv.data();
-        uint32_t closed = 0, dup = 0, run_len = 1, too_long = 0, prev_slot = 0xffffffffu, prev_lf = 0;
-        for (uint32_t i = 0; i < n; i++) {
-            const uint32_t slot = desc[i].slot, lf = desc[i].len_flags;
-            const uint32_t idx = slot * 2u + ((lf >> 26) & 1u);
-            const bool cont = slot == prev_slot && (lf & runf) == runf && (prev_lf & runf) == runf;
-            const uint32_t before = stamp[idx];
-            closed |= (uint32_t)(before == SLOT_CLOSED);
-            dup |= (uint32_t)(before == now && !cont);
-            stamp[idx] = before == SLOT_CLOSED ? SLOT_CLOSED : now;
-            ver[i] = before > floor ? pk_version(before) : 0u;
-            run_len = cont ? run_len + 1u : 1u;
-            too_long |= (uint32_t)(run_len > SS_RUN_MAX);
-            prev_slot = slot; prev_lf = lf;
+        // to pk_floor were followed by an ordinary launch on the same stream).  Written behind the descriptors in the
+        // control block.
+        uint32_t *ver = reinterpret_cast<uint32_t *>(st.h_ctrl + ver_off);
+        uint32_t closed = 0, dup = 0, too_long = 0;
+        if (!(any_flags & SYMRELAY_F_RUN)) {
+            // no runs in the batch (every outbound batch, most inbound ones): the short form of the walk below
+            for (uint32_t i = 0; i < n; i++) {
+                const uint32_t idx = desc[i].slot * 2u + ((desc[i].len_flags >> 26) & 1u);
+                const uint32_t before = stamp[idx];
+                closed |= (uint32_t)(before == SLOT_CLOSED);
+                dup |= (uint32_t)(before == now);
+                stamp[idx] = before == SLOT_CLOSED ? SLOT_CLOSED : now;
+                ver[i] = before > floor ? pk_version(before) : 0u;
+            }
+        } else {
+            uint32_t run_len = 1, prev_slot = 0xffffffffu, prev_lf = 0;
+            for (uint32_t i = 0; i < n; i++) {
+                const uint32_t slot = desc[i].slot, lf = desc[i].len_flags;
+                const uint32_t idx = slot * 2u + ((lf >> 26) & 1u);
+                const bool cont = slot == prev_slot && (lf & runf) == runf && (prev_lf & runf) == runf;
+                const uint32_t before = stamp[idx];
+                closed |= (uint32_t)(before == SLOT_CLOSED);
+                dup |= (uint32_t)(before == now && !cont);
+                stamp[idx] = before == SLOT_CLOSED ? SLOT_CLOSED : now;
+                ver[i] = before > floor ? pk_version(before) : 0u;
+                run_len = cont ? run_len + 1u : 1u;
+                too_long |= (uint32_t)(run_len > SS_RUN_MAX);
+                prev_slot = slot; prev_lf = lf;
+            }
         }
-        nt_copy(st.h_ctrl + ver_off, ver, (size_t)n * 4u);
         if (closed) return fail(ctx, SYMRELAY_ENOENT, "a descriptor names a slot that is not open");
         if (dup) return fail(ctx, SYMRELAY_EINVAL, "two frames of one (slot, direction) in a batch: a stream's frames are MAC-chained, put them in consecutive batches (or mark inbound ones SYMRELAY_F_RUN)");
         if (too_long) return fail(ctx, SYMRELAY_EINVAL, "a run of more than %u SYMRELAY_F_RUN frames of one slot", SS_RUN_MAX);
@@ -1942,8 +1941,7 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     if (extract && !st.d_delta_arena) CU(ctx, cudaMalloc(&st.d_delta_arena, ctx->opts.stage_bytes));
     if (runs && !st.d_run_nonce) CU(ctx, cudaMalloc(&st.d_run_nonce, (size_t)ctx->opts.max_batch_frames * sizeof(uint4)));
     PROF_MARK(ctx, 2);
-    if (!bucketed) nt_copy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
-    _mm_sfence();
+    if (!bucketed) memcpy(st.h_ctrl + tiles_bytes, desc, (size_t)n * sizeof(symrelay_desc));
     st.permuted = bucketed;
     const size_t ctrl_bytes = tiles_bytes + (size_t)n * sizeof(symrelay_desc);
     PROF_MARK(ctx, 3);
@@ -1967,10 +1965,14 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
         {   // Template bookkeeping.  A cheap checksum decides whether this batch looks like the previous one; only
             // then are its descriptors kept (a copy per batch would tax traffic that never repeats).
             const uint64_t *w = reinterpret_cast<const uint64_t *>(desc);
-            uint64_t s0 = n, s1 = 0, s2 = 0, s3 = 0;   // four independent sums: vectorises; memcmp has the last word anyway
-            for (uint32_t i = 0; i + 4u <= 2u * n; i += 4u) { s0 += w[i]; s1 += w[i + 1]; s2 += w[i + 2]; s3 += w[i + 3]; }
-            if (n & 1u) { s0 += w[2u * n - 2u]; s1 += w[2u * n - 1u]; }
-            const uint64_t sum = (s0 * 0x9e3779b97f4a7c15ull) ^ (s1 * 0xc2b2ae3d27d4eb4full) ^ (s2 + (s3 << 1)) ^ 1ull;
+            // four interleaved Fletcher-style sums (a += word; b += a): depends on the ORDER of the descriptors too -- the
+            // same frames in another order are another template -- and costs ~0.3 us; memcmp has the last word anyway
+            uint64_t a0 = n, a1 = 0, a2 = 0, a3 = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+            for (uint32_t i = 0; i + 4u <= 2u * n; i += 4u) {
+                a0 += w[i]; b0 += a0; a1 += w[i + 1]; b1 += a1; a2 += w[i + 2]; b2 += a2; a3 += w[i + 3]; b3 += a3;
+            }
+            if (n & 1u) { a0 += w[2u * n - 2u]; b0 += a0; a1 += w[2u * n - 1u]; b1 += a1; }
+            const uint64_t sum = ((b0 ^ (b1 << 7) ^ (b2 << 13) ^ (b3 << 29)) * 0x9e3779b97f4a7c15ull) ^ (a0 + a1 + a2 + a3) ^ 1ull;
             if (sh.tmpl_gen && sum == sh.tmpl_sum && n == sh.tmpl_n && in_bytes == sh.tmpl_in_bytes && out_bytes == sh.tmpl_out_bytes &&
                 memcmp(desc, sh.tmpl_desc.data(), (size_t)n * sizeof(symrelay_desc)) == 0) {
                 sh.tmpl_streak = true;    // same as the installed template: the next identical batch takes the fast path

@@ -20,9 +20,23 @@ static double now(void) {
     return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec;
 }
 
+/* desc_alt (may be NULL): a second descriptor array for the same frames (e.g. in another order), used on odd steps, so
+ * that no two consecutive batches are byte-identical: the library's general path (scan, plan, per-stream stamps) every
+ * time instead of its repeating-batch fast path. */
+double e2e_ring_run2(symrelay_ctx *ctx, const symrelay_desc *desc, const symrelay_desc *desc_alt, uint32_t n, uint8_t *ring_base,
+                     uint64_t slot_bytes, uint64_t in_bytes, uint64_t out_off, uint64_t out_bytes, uint32_t ring, uint32_t depth,
+                     uint64_t first_step, uint32_t steps, uint32_t *status /* ring x n */, double *submit_seconds);
+
 double e2e_ring_run(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, uint8_t *ring_base, uint64_t slot_bytes,
                     uint64_t in_bytes, uint64_t out_off, uint64_t out_bytes, uint32_t ring, uint32_t depth,
                     uint64_t first_step, uint32_t steps, uint32_t *status /* ring x n */, double *submit_seconds) {
+    return e2e_ring_run2(ctx, desc, NULL, n, ring_base, slot_bytes, in_bytes, out_off, out_bytes, ring, depth, first_step, steps,
+                         status, submit_seconds);
+}
+
+double e2e_ring_run2(symrelay_ctx *ctx, const symrelay_desc *desc, const symrelay_desc *desc_alt, uint32_t n, uint8_t *ring_base,
+                     uint64_t slot_bytes, uint64_t in_bytes, uint64_t out_off, uint64_t out_bytes, uint32_t ring, uint32_t depth,
+                     uint64_t first_step, uint32_t steps, uint32_t *status /* ring x n */, double *submit_seconds) {
     int64_t *tickets = (int64_t *)malloc(sizeof(int64_t) * depth);
     for (uint32_t d = 0; d < depth; d++) tickets[d] = -1;
     double sub = 0.0;
@@ -34,7 +48,7 @@ double e2e_ring_run(symrelay_ctx *ctx, const symrelay_desc *desc, uint32_t n, ui
             if (rc) { free(tickets); return (double)rc; }
         }
         const double a = now();
-        *slot = symrelay_batch_submit(ctx, desc, n, ring_base + (i % ring) * slot_bytes, in_bytes,
+        *slot = symrelay_batch_submit(ctx, (desc_alt && (i & 1)) ? desc_alt : desc, n, ring_base + (i % ring) * slot_bytes, in_bytes,
                                       ring_base + ((i + depth) % ring) * slot_bytes + out_off, out_bytes,
                                       status + (size_t)(i % ring) * n, NULL, NULL, 0);
         sub += now() - a;
