@@ -52,9 +52,13 @@ def workload(name: str, n_gpus: int, rank: int = 0):
         return lens, desc, "weak", rank * 1024
     if name == "c3":
         total = 65536
-        lo, hi = shard.shard_streams(total, n_gpus, rank)      # connections shard by key; no data-path collective
+        # BENCH_C3_SHARD_OF=8 on one GPU: the share rank 0 of 8 gets (a one-GPU look at the strong-scaling step)
+        of = int(os.environ.get("BENCH_C3_SHARD_OF", "0") or 0)
+        lo, hi = shard.shard_streams(total, of if of > 1 and n_gpus == 1 else n_gpus, rank)      # connections shard by key; no data-path collective
         lens = synth.power_law_lens(total)[lo:hi]
         desc = "configs[2]: 65,536 streams, power-law frames 32 B-16 KiB (alpha 1.2), sharded by connection over the GPUs, frames in arrival order"
+        if of > 1 and n_gpus == 1:
+            desc += f" [BENCH_C3_SHARD_OF={of}: only the {hi - lo} streams rank 0 of {of} would get]"
         if os.environ.get("BENCH_C3_SORTED", "0") not in ("", "0"):
             lens = np.sort(lens)     # what a gather step that buckets frames by size would hand over
             desc = desc.replace("frames in arrival order", "frames bucketed by size")

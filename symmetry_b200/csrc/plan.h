@@ -42,6 +42,19 @@ static inline uint32_t symrelay_seg_lanes(uint32_t nc) {
     return k > 32u ? 32u : k;
 }
 #define SYMRELAY_THREAD_TILE_BIG_BUCKET 8192u   /* a size class (<= 32 blocks) with this many frames fills the GPU with thread tiles */
+/* Wide tiles: a frame of 128 blocks and more (8 KiB payload; size class 7 and up) gets a whole 128-thread block -- when the
+ * batch holds only a few such frames, so that it would wait for single warps walking them (BASELINE config 3).  Many
+ * big frames (config 4) are throughput-bound: one warp each is the efficient shape, the wide form adds block barriers. */
+#define SYMRELAY_WIDE_MIN_BLOCKS 127u
+#define SYMRELAY_WIDE_MAX_FRAMES 2048u
+/* ... and only while the whole batch is small enough to be waiting for its longest frame: with a block or more of work for
+ * every thread the GPU can hold (148 SMs x 2,048) the batch is bound by total work, and the wide form's barriers and extra
+ * launch cost more than the shorter tail saves (BASELINE config 3 on one GPU: 71 -> 74 us with it, measured). */
+#define SYMRELAY_WIDE_MAX_BATCH_BLOCKS 262144u
+static inline bool symrelay_wide_ok(uint32_t n_big, uint64_t batch_blocks) {
+    static const bool off = getenv("SYMRELAY_WIDE") && atoi(getenv("SYMRELAY_WIDE")) == 0;   // kill switch (measurements)
+    return !off && n_big != 0u && n_big <= SYMRELAY_WIDE_MAX_FRAMES && batch_blocks < SYMRELAY_WIDE_MAX_BATCH_BLOCKS;
+}
 #define SYMRELAY_THREAD_TILE_HUGE_BATCH 98304u  /* a uniform batch of BIG frames with this many of them (3,072 warps: ~20 per SM) does too */
 
 // Small tiles first (packed, or thread-per-frame tiles: bit 17 of n_kind, 32 consecutive frames with
@@ -205,9 +218,16 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
         n_tiles++;
     }
     if (n_bulk) {
+        uint32_t n_big = 0;
+        uint64_t blocks = 0;
+        for (uint32_t i = 0; i < n; i++) { n_big += nc[i] > SYMRELAY_WIDE_MIN_BLOCKS ? 1u : 0u; blocks += nc[i]; }
+        const bool wide = symrelay_wide_ok(n_big, blocks);
         for (uint32_t i = 0; i < n; i++) {
             if (nc[i] > 32u) {
-                if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = i; tiles[n_tiles].n_kind = 1u | (1u << 16); }
+                if (tiles && n_tiles < max_tiles) {
+                    tiles[n_tiles].first = i;
+                    tiles[n_tiles].n_kind = 1u | (1u << 16) | ((wide && nc[i] > SYMRELAY_WIDE_MIN_BLOCKS) ? (1u << 18) : 0u);
+                }
                 n_tiles++;
             }
         }
@@ -242,8 +262,10 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
     // (power-of-two ranges of the block count), LARGEST FIRST: a 16 KiB frame keeps its warp nine times as long as a
     // 2 KiB one, so the long ones must start first or they finish last.
     uint32_t count[32] = {0}, bulk_class[20] = {0};
+    uint64_t batch_blocks = 0;
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t c = nc[i];
+        batch_blocks += c;
         count[(c > 32u ? 33u : c) - 2u]++;
         if (c > 32u) bulk_class[31 - __builtin_clz(c)]++;   // c in [33, 2^18 + 2]: classes 5..18
     }
@@ -285,9 +307,17 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
             m -= cnt; s += cnt;
         }
     }
-    for (uint32_t k = 0; k < count[31]; k++) {
-        if (tiles && n_tiles < max_tiles) { tiles[n_tiles].first = base[31] + k; tiles[n_tiles].n_kind = 1u | (1u << 16); }
-        n_tiles++;
+    {   // big frames: largest size class first (see the sort below), so the wide ones are the first n_big of them
+        uint32_t n_big = 0;
+        for (uint32_t k = 7u; k < 20u; k++) n_big += bulk_class[k];   // classes 7..: more than SYMRELAY_WIDE_MIN_BLOCKS blocks
+        const uint32_t n_wide = symrelay_wide_ok(n_big, batch_blocks) ? n_big : 0u;
+        for (uint32_t k = 0; k < count[31]; k++) {
+            if (tiles && n_tiles < max_tiles) {
+                tiles[n_tiles].first = base[31] + k;
+                tiles[n_tiles].n_kind = 1u | (1u << 16) | (k < n_wide ? (1u << 18) : 0u);
+            }
+            n_tiles++;
+        }
     }
     if (n_bulk_out) *n_bulk_out = count[31] + n_strided;
     if (tiles && sorted && perm) {

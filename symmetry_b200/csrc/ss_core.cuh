@@ -52,6 +52,13 @@ SS_DEV uint4 *ss_stage_buffer() {
     __shared__ __align__(16) uint4 stage[4][SS_STAGE_BYTES / 16u];
     return stage[(threadIdx.x >> 5) & 3u];
 }
+// wide tiles: one frame per 128-thread block (four warps walk its blocks with stride 128)
+SS_DEV uint32_t ss_wide_tid() { return threadIdx.x & 127u; }
+SS_DEV void ss_wide_sync() { __syncthreads(); }
+SS_DEV uint32_t *ss_wide_buffer() {
+    __shared__ uint32_t wb[32];   // [0..3] Poly1305 r words, [4] verdict, [8..27] the four warps' partial sums
+    return wb;
+}
 SS_DEV uint32_t ss_popc(uint32_t v) { return (uint32_t)__popc(v); }
 SS_DEV uint32_t ss_clz(uint32_t v) { return (uint32_t)__clz((int)v); }
 SS_DEV uint32_t ss_rotl16(uint32_t x) { return __byte_perm(x, 0, 0x1032); }
@@ -488,9 +495,14 @@ SS_DEV void ss_load_mac(const uint8_t *p, uint32_t w[4]) {
 // one dependent read over PCIe fewer), else it is read from a.tiles.
 // SEG (with BULK): the tile may hold several frames with fewer than 32 lanes each; SEG == false keeps the one-frame-per-
 // warp case free of the bookkeeping (its register budget is tight: 72, seven blocks of 128 threads per SM).
-template <bool BULK, bool VOL = false, bool SEG = false>
+// WIDE (with BULK, not SEG): one frame per 128-thread BLOCK -- the four warps walk the frame's blocks with stride 128
+// and combine their partial MACs through shared memory.  For the few frames of 8 KiB and more in a ragged batch:
+// one warp needs nine rounds for 16 KiB, which is what such a batch then waits for (BASELINE config 3); four warps
+// need three.  A batch of many big frames (config 4) is throughput-bound and keeps one warp per frame.
+template <bool BULK, bool VOL = false, bool SEG = false, bool WIDE = false>
 SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
+    const uint32_t fl = WIDE ? ss_wide_tid() : 0u;   // wide tiles: this thread's lane number among the frame's 128
     ss_dbg_stamp(a, tile_idx, lane, 0);
     ss_pdl_launch_dependents();   // the next batch's kernel may start its own prologue now
     if (!(a.flags & SS_ARG_INPUT_INDEPENDENT)) ss_pdl_wait();   // descriptors may come from the previous kernel
@@ -679,12 +691,13 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
     bool have_A = false;
     // strided tiles walk virtual blocks 0..nc of every frame; the loop is warp-uniform (it holds shuffles), so it runs
     // for the longest frame of the tile (the planner groups frames of one block count)
-    const uint32_t niter = !BULK ? 1u : (SEG ? ss_reduce_max(valid ? (nc + segw) / segw : 0u) : ((nc + 1u + 31u) >> 5));
-    const uint32_t stride = BULK ? segw : 32u;
+    const uint32_t niter = !BULK ? 1u : (SEG ? ss_reduce_max(valid ? (nc + segw) / segw : 0u)
+                                             : (WIDE ? ((nc + 1u + 127u) >> 7) : ((nc + 1u + 31u) >> 5)));
+    const uint32_t stride = WIDE ? 128u : (BULK ? segw : 32u);
 
 #pragma unroll 1
     for (uint32_t it = 0; it < niter; ++it) {
-        const uint32_t b = (lane - st) + stride * it;
+        const uint32_t b = (WIDE ? fl : lane - st) + stride * it;
         const bool has_block = valid && b < nc;
         const bool need_ks = has_block;
         // (Bulk tiles load after the rounds: they have enough warps in flight, and holding the
@@ -702,8 +715,15 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
 
         if (it == 0) {
             // Poly1305 key: r to every lane of the frame, s stays on the leader.
-            const uint32_t t0 = ss_shfl(x[0], st), t1 = ss_shfl(x[1], st), t2 = ss_shfl(x[2], st),
-                           t3 = ss_shfl(x[3], st);
+            uint32_t t0, t1, t2, t3;
+            if (WIDE) {   // block 0 was computed by thread 0 of the block: hand r to the other warps through shared memory
+                uint32_t *wb = ss_wide_buffer();
+                if (fl == 0u) { wb[0] = x[0]; wb[1] = x[1]; wb[2] = x[2]; wb[3] = x[3]; }
+                ss_wide_sync();
+                t0 = wb[0]; t1 = wb[1]; t2 = wb[2]; t3 = wb[3];
+            } else {
+                t0 = ss_shfl(x[0], st); t1 = ss_shfl(x[1], st); t2 = ss_shfl(x[2], st); t3 = ss_shfl(x[3], st);
+            }
             ss_r_limbs(t0, t1, t2, t3, r);
             sw[0] = x[4]; sw[1] = x[5]; sw[2] = x[6]; sw[3] = x[7];
             if (BULK) {
@@ -717,7 +737,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
                     ss_store_power(pw, r); ss_store_power(pw + 9, t); ss_store_power(pw + 18, t3); ss_store_power(pw + 27, r128);
                 }
 #pragma unroll 1
-                for (uint32_t w = 1; w < segw; w <<= 1) {  // r^8 .. r^(4*segw): the step between a lane's consecutive windows
+                for (uint32_t w = 1; w < (WIDE ? 128u : segw); w <<= 1) {  // r^8 .. r^(4*stride): the step between a lane's consecutive windows
                     ss_pmul(t, r128, r128);
 #pragma unroll
                     for (int j = 0; j < 5; j++) r128[j] = t[j];
@@ -870,9 +890,28 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
         }
     }
     const uint32_t tag_b1 = ss_shfl(tagval, st + 1u);  // st+1 <= 31 always (every frame has >= 2 lanes)
+    if (WIDE) {   // the four warps' sums meet in shared memory; thread 0 of the block is the frame's leader
+        uint32_t *wb = ss_wide_buffer();
+        if (lane == 0u) {
+            // a warp's sum of 32 partials uses up to 31 bits per limb: carry it back under 2^26 before four of them meet
+            uint32_t c;
+            c = A[0] >> 26; A[0] &= 0x3ffffffu; A[1] += c;
+            c = A[1] >> 26; A[1] &= 0x3ffffffu; A[2] += c;
+            c = A[2] >> 26; A[2] &= 0x3ffffffu; A[3] += c;
+            c = A[3] >> 26; A[3] &= 0x3ffffffu; A[4] += c;
+            c = A[4] >> 26; A[4] &= 0x3ffffffu; A[0] += c * 5u;
+#pragma unroll
+            for (int i = 0; i < 5; i++) wb[8u + 5u * (fl >> 5) + (uint32_t)i] = A[i];
+        }
+        ss_wide_sync();
+        if (fl == 0u) {
+#pragma unroll
+            for (int i = 0; i < 5; i++) A[i] = wb[8 + i] + wb[13 + i] + wb[18 + i] + wb[23 + i];
+        }
+    }
 
     // ---- leader: tag, verdict, nonce chain -----------------------------------
-    const bool leader = valid && lane == st;
+    const bool leader = valid && (WIDE ? fl == 0u : lane == st);
     uint32_t ok = 1;
     uint32_t mac[4] = {0, 0, 0, 0};
     if (leader) {
@@ -883,6 +922,12 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
             ok = ((wmac[0] ^ mac[0]) | (wmac[1] ^ mac[1]) | (wmac[2] ^ mac[2]) | (wmac[3] ^ mac[3])) == 0 ? 1u : 0u;
         }
     }
+    if (WIDE) {
+        uint32_t *wb = ss_wide_buffer();
+        if (fl == 0u) wb[4] = ok;
+        ss_wide_sync();
+        ok = wb[4];
+    } else
     ok = ss_shfl(ok, st);
 
     if (is_open && ok) {
@@ -902,7 +947,7 @@ SS_DEV void ss_process_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *gi
             for (int i = 0; i < 16; i++) z[i] = 0;
 #pragma unroll 1
             for (uint32_t it = 0; it < niter; ++it) {
-                const uint32_t b = (lane - st) + stride * it;
+                const uint32_t b = (WIDE ? fl : lane - st) + stride * it;
                 if (b >= 2u && b < nc) {
                     const uint32_t j = b - 2u;
                     const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;

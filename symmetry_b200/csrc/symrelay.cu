@@ -93,8 +93,22 @@ __global__ void __launch_bounds__(128, SS_BULK_MIN_BLOCKS) ss_bulk_kernel(SsArgs
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
     const SsTile tile = a.tiles[warp];
-    if ((tile.n_kind >> 24) & 63u) return;   // a strided tile: ss_strided_kernel's
+    if (((tile.n_kind >> 24) & 63u) || (tile.n_kind & (1u << 18))) return;   // a strided or a wide tile: another kernel's
     ss_process_tile<true>(a, warp, &tile);
+}
+
+// Wide tiles (plan.h): one frame of more than 8 KiB per 128-thread BLOCK, for batches that hold only a few of them and
+// would otherwise wait for single warps walking those frames.  a.tiles points at the first bulk-class tile of the range
+// the caller picked; blocks that find another kind's tile leave.
+#ifndef SS_WIDE_MIN_BLOCKS
+#define SS_WIDE_MIN_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, SS_WIDE_MIN_BLOCKS) ss_wide_kernel(SsArgs a) {
+    const uint32_t t = blockIdx.x;   // (block-uniform: every thread of a block takes the same branch)
+    if (t >= a.n_tiles) return;
+    const SsTile tile = a.tiles[t];
+    if (!(tile.n_kind & (1u << 18))) return;
+    ss_process_tile<true, false, false, true>(a, t, &tile);
 }
 
 // Strided tiles (plan.h): 32/k mid-size frames of one block count per warp, k lanes each.  Launched over the same
@@ -740,8 +754,8 @@ struct Shard {
     int pending_wb = -1;                           // stage whose results still sit in device staging
     unsigned long long *d_ts = nullptr;            // SYMRELAY_TS=1: 4 time stamps per batch, 4096 batches round-robin
     uint64_t ts_n = 0;
-    cudaStream_t s_aux = nullptr, s_aux2 = nullptr, s_aux3 = nullptr;   // side streams: the tile kinds of one batch run next to each other
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr, ev_join3 = nullptr;
+    cudaStream_t s_aux = nullptr, s_aux2 = nullptr, s_aux3 = nullptr, s_aux4 = nullptr;   // side streams: the tile kinds of one batch run next to each other
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr, ev_join3 = nullptr, ev_join4 = nullptr;
     std::vector<Stage> stages;
     SsInitRec *h_init = nullptr, *d_init = nullptr;  // staging for stream_open
     uint32_t init_cap = 0;
@@ -932,11 +946,18 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     //   strided tiles (mid-size frames)                                    -> side stream 2
     //   packed tiles of a large batch                                      -> side stream 3
     const bool big = n_packed > 148u * 8u && !write_back;   // large batch: split the small tiles by kind (see ss_thread_kernel)
-    bool has_thread = n_packed != 0, has_packed = big, has_strided = n_bulk != 0, has_bulk = n_bulk != 0;
+    bool has_thread = n_packed != 0, has_packed = big, has_strided = n_bulk != 0, has_bulk = n_bulk != 0, has_wide = n_bulk != 0;
+    uint32_t wide_lo = 0, wide_hi = n_bulk;   // the range of bulk-class tiles the wide kernel is launched over
     if (host_tiles) {   // the tile list is in host memory: launch only what is there
-        has_strided = has_bulk = false;
+        has_strided = has_bulk = has_wide = false;
+        wide_lo = n_bulk; wide_hi = 0;
         for (uint32_t i = n_packed; i < n_tiles; i++) {
-            if ((host_tiles[i].n_kind >> 24) & 63u) has_strided = true; else has_bulk = true;
+            if ((host_tiles[i].n_kind >> 24) & 63u) has_strided = true;
+            else if (host_tiles[i].n_kind & (1u << 18)) {
+                has_wide = true;
+                if (i - n_packed < wide_lo) wide_lo = i - n_packed;
+                wide_hi = i - n_packed + 1u;
+            } else has_bulk = true;
         }
         if (big) {
             has_thread = has_packed = false;
@@ -945,10 +966,10 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
             }
         }
     }
-    const int kinds = (n_packed ? (big ? (int)has_thread + (int)has_packed : 1) : 0) + (int)has_strided + (int)has_bulk;
+    const int kinds = (n_packed ? (big ? (int)has_thread + (int)has_packed : 1) : 0) + (int)has_strided + (int)has_bulk + (int)has_wide;
     const bool side = fork && kinds > 1;
     if (side) CU(ctx, cudaEventRecord(fork->ev_fork, stream));
-    cudaEvent_t joins[3];
+    cudaEvent_t joins[4];
     int n_joins = 0;
     // the stream for a kind that has a side stream: that stream (made to wait on the fork) when the batch forks at all
     auto side_stream = [&](cudaStream_t s_side, cudaEvent_t ev) -> cudaStream_t {
@@ -967,6 +988,15 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
         // measured and is worse: 71 -> 80 us on BASELINE config 3.)
         const uint32_t threads = n_bulk <= 148u * 8u ? 32u : 128u;
         const uint32_t wpb = threads / 32u;
+        if (has_wide) {   // the longest frames of the batch: first
+            SsArgs w = b;
+            w.tiles = b.tiles + wide_lo;
+            w.n_tiles = wide_hi - wide_lo;
+            cudaStream_t s = side_stream(fork ? fork->s_aux4 : nullptr, fork ? fork->ev_join4 : nullptr);
+            CU(ctx, launch_pdl(ss_wide_kernel, w.n_tiles, 128, s, false, w));
+            ctx->launches++;
+            if (s != stream) CU(ctx, cudaEventRecord(fork->ev_join4, s));
+        }
         if (has_bulk) {
             cudaStream_t s = side_stream(fork ? fork->s_aux : nullptr, fork ? fork->ev_join : nullptr);
             CU(ctx, launch_pdl(ss_bulk_kernel, (n_bulk + wpb - 1) / wpb, threads, s, pdl && !side, b));
@@ -1086,6 +1116,7 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
         CU(ctx, cudaStreamCreateWithPriority(&sh.s_aux2, cudaStreamNonBlocking, hi));
     }
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_aux3, cudaStreamNonBlocking));
+    CU(ctx, cudaStreamCreateWithFlags(&sh.s_aux4, cudaStreamNonBlocking));
     CU(ctx, cudaStreamCreateWithFlags(&sh.s_init, cudaStreamNonBlocking));
     CU(ctx, cudaHostAlloc(&sh.pk_host, sizeof(PkHost), cudaHostAllocMapped | cudaHostAllocPortable));
     memset(sh.pk_host, 0, sizeof(PkHost));
@@ -1095,6 +1126,7 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
     CU(ctx, cudaEventCreateWithFlags(&sh.ev_join, cudaEventDisableTiming));
     CU(ctx, cudaEventCreateWithFlags(&sh.ev_join2, cudaEventDisableTiming));
     CU(ctx, cudaEventCreateWithFlags(&sh.ev_join3, cudaEventDisableTiming));
+    CU(ctx, cudaEventCreateWithFlags(&sh.ev_join4, cudaEventDisableTiming));
     {
         std::vector<uint16_t> table(SX_TABLE_ENTRIES);
         sx::build_table(table.data());
@@ -1230,8 +1262,10 @@ static void shard_free(Shard &sh) {
     if (sh.s_aux) cudaStreamDestroy(sh.s_aux);
     if (sh.s_aux2) cudaStreamDestroy(sh.s_aux2);
     if (sh.s_aux3) cudaStreamDestroy(sh.s_aux3);
+    if (sh.s_aux4) cudaStreamDestroy(sh.s_aux4);
     if (sh.ev_join2) cudaEventDestroy(sh.ev_join2);
     if (sh.ev_join3) cudaEventDestroy(sh.ev_join3);
+    if (sh.ev_join4) cudaEventDestroy(sh.ev_join4);
     if (sh.ev_fork) cudaEventDestroy(sh.ev_fork);
     if (sh.ev_join) cudaEventDestroy(sh.ev_join);
 }

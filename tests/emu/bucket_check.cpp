@@ -18,7 +18,7 @@ int main(){ const uint32_t n=131072; std::vector<symrelay_desc> d(n), s(n); std:
  double best=1e9; for(int k=0;k<30;k++){ double a=now(); r=symrelay_plan_bucketed(d.data(),n,t.data(),n,&nb,&chk,s.data(),perm.data()); best=std::min(best,now()-a);} 
  // validate: tiles cover every sorted descriptor exactly once, block sums <= 32, perm is a permutation
  std::vector<int> seen(n,0), pseen(n,0); uint64_t lanes=0; bool ok=true;
- for(int64_t k=0;k<r;k++){ uint32_t f=t[k].first, cnt=t[k].n_kind&0xffff, kind=t[k].n_kind>>16; uint32_t sum=0; for(uint32_t j=0;j<cnt;j++){ seen[f+j]++; uint32_t c=2+(((s[f+j].len_flags&0xffffff)+63)>>6); sum+=c; if(kind==2 && c!=2+(((s[f].len_flags&0xffffff)+63)>>6)) ok=false; if(kind==1 && c<=32) ok=false; if(kind!=1 && c>32) ok=false;} if(kind==0 && sum>32) ok=false; if(kind==2 && cnt!=32) ok=false; lanes+=sum; }
+ for(int64_t k=0;k<r;k++){ uint32_t f=t[k].first, cnt=t[k].n_kind&0xffff, kind=t[k].n_kind>>16; const bool wide=(kind&4u)!=0; if(wide) kind&=~4u; uint32_t sum=0; for(uint32_t j=0;j<cnt;j++){ seen[f+j]++; uint32_t c=2+(((s[f+j].len_flags&0xffffff)+63)>>6); sum+=c; if(kind==2 && c!=2+(((s[f].len_flags&0xffffff)+63)>>6)) ok=false; if(kind==1 && c<=32) ok=false; if(wide && (kind!=1 || c<128)) ok=false; if(kind!=1 && c>32) ok=false;} if(kind==0 && sum>32) ok=false; if(kind==2 && cnt!=32) ok=false; lanes+=sum; }
  for(uint32_t i=0;i<n;i++){ if(seen[i]!=1) ok=false; pseen[perm[i]]++; if(memcmp(&s[i],&d[perm[i]],16)) ok=false; }
  for(uint32_t i=0;i<n;i++) if(pseen[i]!=1) ok=false;
  uint32_t nb2; int64_t r2=symrelay_plan_inline(d.data(),n,t.data(),n,&nb2,&chk);

@@ -78,6 +78,11 @@ static uint4 emu_stage[SS_STAGE_BYTES / 16u];   // one warp runs at a time
 static inline uint4 *ss_stage_buffer() { return emu_stage; }
 static uint32_t emu_powers[16 * 48];   // SS_MAX_SEG_FRAMES frames per warp
 static inline uint32_t *ss_powers_buffer() { return emu_powers; }
+// wide tiles (one frame per four-warp block) are never instantiated under the emulator: stubs so that the template parses
+static inline uint32_t ss_wide_tid() { return emu_lane_id; }
+static inline void ss_wide_sync() { emu_sync(); }
+static uint32_t emu_wide[32];
+static inline uint32_t *ss_wide_buffer() { return emu_wide; }
 static inline uint32_t ss_popc(uint32_t v) { return (uint32_t)__builtin_popcount(v); }
 static inline uint32_t ss_clz(uint32_t v) { return v ? (uint32_t)__builtin_clz(v) : 32u; }
 static inline uint32_t emu_rotl(uint32_t x, int n) { return (x << n) | (x >> (32 - n)); }

@@ -48,6 +48,50 @@ def test_planner_and_desc_check_are_host_only():
     assert L.symrelay_desc_check(d[:1].ctypes.data) == -22
 
 
+def test_planner_marks_wide_tiles_only_when_big_frames_are_few():
+    """Frames of 128 blocks and more (> 8,000 payload bytes) get a whole 128-thread block (tile bit 18) when the batch
+    holds at most 2,048 of them and fewer than 262,144 ChaCha20 blocks in all (beyond that it is bound by total work, not
+    by its longest frame); a batch of many big frames keeps one warp per frame.  Both planners agree."""
+    import ctypes as C
+
+    import numpy as np
+
+    import batch_util as bu
+    from symmetry_b200 import _lib
+
+    L = _lib.load()
+
+    def plan(lens, sorted_):
+        p, _ = bu.plain_layout(lens)
+        w, _ = bu.wire_layout(lens)
+        d = bu.make_descs(np.arange(len(lens)), lens, p, w)
+        tiles = np.zeros((len(lens), 2), dtype=np.uint32)
+        nb = C.c_uint32(0)
+        if sorted_:
+            sd = np.zeros_like(d)
+            perm = np.zeros(len(lens), dtype=np.uint32)
+            nt = L.symrelay_plan_sorted(d.ctypes.data, len(d), tiles.ctypes.data, len(tiles), C.byref(nb), sd.ctypes.data,
+                                        perm.ctypes.data)
+            d = sd
+        else:
+            nt = L.symrelay_plan(d.ctypes.data, len(d), tiles.ctypes.data, len(tiles), C.byref(nb))
+        assert nt > 0
+        return tiles[:nt], d
+
+    for sorted_ in (False, True):
+        lens = [64] * 40 + [700] * 9 + [8000, 8001, 16384, 3000, 70000]
+        tiles, d = plan(lens, sorted_)
+        wide = [int(d["len_flags"][t[0]]) & 0xFFFFFF for t in tiles if t[1] & (1 << 18)]
+        assert sorted(wide) == [8001, 16384, 70000], (sorted_, wide)
+        assert all((t[1] & 0xFFFF) == 1 and (t[1] & (1 << 16)) and not (t[1] >> 24) for t in tiles if t[1] & (1 << 18))
+        tiles, d = plan([64] * 10 + [8001] * 2049, sorted_)
+        assert not any(t[1] & (1 << 18) for t in tiles), sorted_
+        tiles, d = plan([64] * 10 + [8001] * 2047, sorted_)           # 2,047 x 128 + 10 x 3 = 262,046 blocks
+        assert sum(1 for t in tiles if t[1] & (1 << 18)) == 2047, sorted_
+        tiles, d = plan([64] * 100 + [8001] * 2047, sorted_)          # 262,316 blocks: bound by total work
+        assert not any(t[1] & (1 << 18) for t in tiles), sorted_
+
+
 def test_no_cpu_fallback_without_a_device():
     import torch
 

@@ -173,6 +173,18 @@ def test_strided_tiles_mid_size_frames(dbe, length):
     pc.seal_open_roundtrip(dbe, [length] * n, tags, seed=1000 + length, chain=2, corrupt=(0, 5, 36), speculative_min_len=385)
 
 
+@pytest.mark.parametrize("lens", [
+    [8000, 8001, 8064, 8065, 8192, 12345, 16192, 16193, 16256, 16257, 65536, 200000],   # 8,001 bytes = 128 blocks: the first wide count; 16,193: a third round
+    [8192] * 5 + [100, 700, 3000, 5000] * 3 + [24500, 8127],               # mixed with packed, strided and one-warp tiles
+])
+def test_wide_tiles_few_big_frames(dbe, lens):
+    """A batch with only a few frames of 8 KiB and more: each gets a 128-thread block (four warps, stride 128, partial
+    MACs through shared memory, r^512 between a thread's windows).  Block counts around multiples of 128, tags incl.
+    REKEY, forged frames wiped, two frames per stream chained over two batches."""
+    tags = [(i * 7 + 1) & 3 for i in range(len(lens))]
+    pc.seal_open_roundtrip(dbe, lens, tags, seed=4242 + len(lens), chain=2, corrupt=(0, 4, len(lens) - 1), speculative_min_len=385)
+
+
 def test_counter_wrap_rekeys(be):
     key, hdr = bytes(range(32)), bytes(24)
     raw = bytearray(ls.State(key, hdr).raw)
