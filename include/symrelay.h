@@ -58,6 +58,8 @@ extern "C" {
 #define SYMRELAY_ST_TOO_SHORT 2u          /* wire frame shorter than 17 bytes after the prefix */
 #define SYMRELAY_ST_EXTRACT_THROW 3u      /* the reference would throw a TypeError here (utils.ts:38-50) */
 #define SYMRELAY_ST_EXTRACT_UNSUPPORTED 4u /* value shape outside the GPU extractor's domain: use the JS helper */
+/* (3 and 4: the chunk is NOT sealed -- that slot's state is untouched and its wire bytes are left untouched or zeroed:
+ *  the seal kernel may run beside the extractor and takes back what it sealed ahead of such a verdict) */
 #define SYMRELAY_ST_RETRY 5u /* frame of a run behind a failed or REKEY frame: not processed, resubmit it */
 #define SYMRELAY_ST_FAILED 6u /* per-frame front end only: the batch this frame sat in was refused as a whole
                                 (symrelay_last_error() says why); nothing was sealed or opened, state untouched */

@@ -137,6 +137,8 @@ SS_DEV void ss_dep_wait(const uint32_t *seq, uint32_t need) {
 #define SS_ARG_STAGE_OUTPUT 4u       // SsArgs.flags: assemble each packed tile's output in shared memory, store whole lines
 #define SS_ARG_CHAIN 8u              // SsArgs.flags: resident kernel -- hand the stream states over through their stamps
 #define SS_ARG_CHAIN_UNIFORM 16u     // ... and every frame expects the stamp ver_all (no per-descriptor array)
+#define SS_ARG_VERDICT_LATE 32u      // SsArgs.flags: the kernel was launched as a programmatic dependent of the batch's extractor:
+                                     // thread tiles seal SS_F_EXTRACT frames while it still runs and ask for its verdict last
 
 #define SS_F_OPEN 0x04000000u
 #define SS_F_EXTRACT 0x08000000u
@@ -1023,7 +1025,11 @@ template <bool VOL = false>
 SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_pdl_launch_dependents();
-    if (!(a.flags & SS_ARG_INPUT_INDEPENDENT)) ss_pdl_wait();
+    // SS_ARG_VERDICT_LATE: the kernel this one depends on is the batch's extractor, which writes status words and deltas
+    // only.  Both kernels are one serial chain per frame with a few warps per SM, so they run side by side: this one seals
+    // while the verdicts are being worked out and waits for them at the very end (a refused chunk is then taken back).
+    const bool late_ok = (a.flags & SS_ARG_VERDICT_LATE) != 0;
+    if (!(a.flags & SS_ARG_INPUT_INDEPENDENT) && !late_ok) ss_pdl_wait();
     const SsTile tile = given ? *given : a.tiles[tile_idx];
     const uint32_t nfr = tile.n_kind & 0xffffu;
     bool valid = lane < nfr;
@@ -1034,7 +1040,7 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
         d.slot = dv.x; d.in_off = dv.y; d.out_off = dv.z; d.len_flags = dv.w;
         if (a.desc_fill) *reinterpret_cast<uint4 *>(a.desc_fill + tile.first + lane) = dv;
     }
-    ss_pdl_wait();
+    if (!late_ok) ss_pdl_wait();
     ss_dep_wait(a.dep_seq, a.dep_need);
     ss_write_back(a, tile_idx, a.n_tiles, lane);
     const bool chain = (a.flags & SS_ARG_CHAIN) != 0;
@@ -1049,7 +1055,8 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
         }
     }
     const uint32_t lf = d.len_flags;
-    if (valid && (lf & SS_F_EXTRACT) && !(lf & SS_F_OPEN) && a.status[tile.first + lane] != SS_ST_OK) valid = false;
+    const bool wants_verdict = (lf & SS_F_EXTRACT) && !(lf & SS_F_OPEN);
+    if (valid && wants_verdict && !late_ok && a.status[tile.first + lane] != SS_ST_OK) valid = false;
     if (valid && (lf & (SS_F_RUN | SS_F_OPEN)) == (SS_F_RUN | SS_F_OPEN) &&
         (!a.run_nonce || a.run_nonce[tile.first + lane].w >= SS_RUN_CAP)) {   // see ss_process_tile
         a.status[tile.first + lane] = SS_ST_RETRY;
@@ -1131,6 +1138,24 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
         }
     }
     const uint32_t frame_idx = tile.first + lane;
+    if (late_ok) {
+        ss_pdl_wait();   // the extractor has finished: its status words are visible
+        if (wants_verdict && *reinterpret_cast<const volatile uint32_t *>(a.status + frame_idx) != SS_ST_OK) {
+            // refused (the reference throws before peer.write, or the host must extract): the stream state stays as it
+            // was, the status word is the extractor's, and the wire bytes sealed ahead of the verdict are wiped
+            uint32_t z[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) z[i] = 0;
+            *reinterpret_cast<uint32_t *>(a.out + d.out_off) = 0u;
+#pragma unroll 1
+            for (uint32_t j = 0; j < npay; j++) {
+                const int cbytes = (int)(mlen - 64u * j) < 64 ? (int)(mlen - 64u * j) : 64;
+                ss_store64(dst + 64u * (size_t)j, cbytes, z);
+            }
+            ss_store_mac(dst + mlen, z);
+            return;
+        }
+    }
     uint32_t *verp = reinterpret_cast<uint32_t *>(sp + 2) + 3;
     const uint32_t ver_word = (s2.w & 0xffu) | (a.new_ver << 8);
     if (!ok) { a.status[frame_idx] = SS_ST_BAD_MAC; if (chain) ss_st_release_u32(verp, ver_word); return; }

@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const Ss
     // slice of shared memory with 16-byte loads that are all in flight together, and the byte loop then
     // runs against shared memory (chunk, class table and grammar table).
     extern __shared__ __align__(16) uint8_t sx_smem[];
+    ss_pdl_launch_dependents();   // the batch's seal kernel may start beside this one (SS_ARG_VERDICT_LATE, ss_core.cuh)
     uint64_t *fast = reinterpret_cast<uint64_t *>(sx_smem);
     uint8_t *cls = sx_smem + SX_FAST_ENTRIES * 8u;
     uint8_t *sx_stage = cls + 256u;
@@ -804,6 +805,7 @@ struct symrelay_ctx {
     bool defer_wb = true;   // SYMRELAY_DEFER=0: pipelined zero-copy batches write their results to the host themselves
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
     uint64_t inject_refusal = 0;   // SYMRELAY_INJECT_REFUSAL=k: the front end's k-th batch is refused (tests of the error path)
+    bool extract_overlap = true;   // SYMRELAY_EXTRACT_OVERLAP=0: the seal kernel of an extract batch starts only when the extractor is done
     uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
     // SYMRELAY_PROF=1: where a host batch spends its time (printed by symrelay_destroy)
     bool prof = false;
@@ -968,6 +970,10 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     }
     const int kinds = (n_packed ? (big ? (int)has_thread + (int)has_packed : 1) : 0) + (int)has_strided + (int)has_bulk + (int)has_wide;
     const bool side = fork && kinds > 1;
+    // A batch with an extractor pass whose small tiles all go to one kernel right behind it on this stream: that kernel is
+    // launched as the extractor's programmatic dependent and its thread tiles ask for the verdicts last (ss_core.cuh).
+    const bool late = d_delta && d_delta_arena && ctx->extract_overlap && !d_run_nonce && !write_back && kinds == 1 && n_packed;
+    if (late) a.flags |= SS_ARG_VERDICT_LATE;
     if (side) CU(ctx, cudaEventRecord(fork->ev_fork, stream));
     cudaEvent_t joins[4];
     int n_joins = 0;
@@ -1033,7 +1039,7 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
                 if (s != stream) CU(ctx, cudaEventRecord(fork->ev_join3, s));
             }
             if (has_thread) {   // the caller's stream
-                CU(ctx, launch_pdl(ss_thread_kernel, grid, threads, stream, false, a));
+                CU(ctx, launch_pdl(ss_thread_kernel, grid, threads, stream, late, a));
                 ctx->launches++;
             }
         } else if (host_tiles && n_packed <= SS_INLINE_TILES && ctx->inline_tiles) {
@@ -1047,11 +1053,11 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
             attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
             attr[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = attr;
-            cfg.numAttrs = (pdl && !side) ? 1 : 0;
+            cfg.numAttrs = ((pdl && !side) || late) ? 1 : 0;
             CU(ctx, cudaLaunchKernelEx(&cfg, ss_packed_inline_kernel, a, tb));
             ctx->launches++;
         } else {
-            CU(ctx, launch_pdl(ss_packed_kernel, grid, threads, stream, pdl && !side, a));
+            CU(ctx, launch_pdl(ss_packed_kernel, grid, threads, stream, (pdl && !side) || late, a));
             ctx->launches++;
         }
     }
@@ -1302,6 +1308,7 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (const char *m = getenv("SYMRELAY_INJECT_REFUSAL")) ctx->inject_refusal = strtoull(m, nullptr, 10);
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
+    if (const char *m = getenv("SYMRELAY_EXTRACT_OVERLAP")) ctx->extract_overlap = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE_DEV")) ctx->device_arg_flags = atoi(m) ? (SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT) : 0u;
     ctx->n_gpus = n_gpus;
     for (int g = 0; g < n_gpus; g++) {

@@ -19,6 +19,7 @@ def relay(request):
     import symmetry_b200 as sb
 
     r = sb.SymRelay(gpu_ids=(0,), max_streams=1 << 16, zero_copy=request.param == "zero_copy")
+    r.test_mode = request.param
     yield r
     r.close()
 
@@ -143,6 +144,63 @@ def test_fuzzed_chunks_match_the_oracle(relay, provider):
             want = ref.seal_frame(chunks[i])
             assert bytes(wire[w_offs[i] : w_offs[i] + len(want)]) == want
         assert relay.export(int(slots[i]))[0] == ref.raw
+    # a refused chunk leaves no ciphertext behind (the seal kernel may run beside the extractor and takes back what it sealed
+    # ahead of a bad verdict): its wire slot is all zeros, as the arena was.  (Staged batches copy the whole device arena
+    # back, gaps and refused slots included, so there the slot holds whatever an earlier batch left in the staging.)
+    for i, c in enumerate(chunks):
+        if relay.test_mode == "zero_copy" and int(st[i]) & 0xFF != 0:
+            assert not wire[w_offs[i] : w_offs[i] + len(c) + 20].any(), (i, c)
+    for s_ in slots:
+        relay.close_stream(int(s_))
+
+
+def test_seal_beside_the_extractor_takes_back_refused_chunks(relay):
+    """8,192 chunks of one size class (thread tiles, one kernel): the seal kernel is launched as the extractor's
+    programmatic dependent and asks for the verdicts last.  Every fifth chunk is one the reference throws on or the GPU
+    hands back: status from the extractor, stream state untouched, no ciphertext left in its wire slot; all others
+    sealed bit-exactly with the right delta.  A second batch on the same streams shows the chains moved (or not)."""
+    import json
+
+    import symmetry_b200 as sb
+
+    n = 8192
+    rng = np.random.default_rng(99)
+    keys = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    hdrs = rng.integers(0, 256, (n, 24), dtype=np.uint8)
+    slots = relay.open_streams(keys, hdrs, None, None, provider=sb.provider_kind("litellm"))
+    refs = [ls.State(bytes(keys[i]), bytes(hdrs[i])) for i in range(n)]
+    bad = [b'data: {"choices":[]}', b'data: {"choices":[{"delta":{"content":1e300}}]}', b'data: {"id":1}',
+           b'data: {"choices":[{"index":0}]}']
+    for step in range(2):
+        chunks = []
+        for i in range(n):
+            if (i + step) % 5 == 0:
+                c = bad[(i // 5) % len(bad)]
+            else:
+                ev = {"id": f"chatcmpl-{i:06d}", "object": "chat.completion.chunk", "model": "llama3:8b",
+                      "choices": [{"index": 0, "delta": {"role": "assistant", "content": f"tok{i}s{step}"}, "finish_reason": None}]}
+                c = b"data: " + json.dumps(ev, separators=(",", ":")).encode()
+            assert len(c) <= 250
+            chunks.append(c + b" " * (200 + (i * 7) % 51 - len(c)) if len(c) < 200 + (i * 7) % 51 else c)
+        assert all(193 <= len(c) <= 256 for c in chunks)   # four payload blocks each: one thread tile per 32 frames
+        st, deltas, wire, w_offs = run_extract_batch(relay, slots, chunks)
+        n_bad = 0
+        for i, c in enumerate(chunks):
+            code = int(st[i]) & 0xFF
+            want_code, want = ex.extract("litellm", c)
+            if (i + step) % 5 == 0:
+                n_bad += 1
+                assert code in (sb.relay.ST_EXTRACT_THROW, sb.relay.ST_EXTRACT_UNSUPPORTED), (i, c, code)
+                assert code == sb.relay.ST_EXTRACT_UNSUPPORTED or want_code == ex.THROW
+                if relay.test_mode == "zero_copy":
+                    assert not wire[w_offs[i] : w_offs[i] + len(c) + 20].any(), (i, c)
+            else:
+                assert code == 0 and want_code == ex.OK and deltas[i] == want, (i, c, code)
+                frame = refs[i].seal_frame(c)
+                assert bytes(wire[w_offs[i] : w_offs[i] + len(frame)]) == frame, i
+            if i % 13 == 0 or (i + step) % 5 == 0:
+                assert relay.export(int(slots[i]))[0] == refs[i].raw, i
+        assert n_bad > 1600
     for s_ in slots:
         relay.close_stream(int(s_))
 
