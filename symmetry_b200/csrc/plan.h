@@ -51,9 +51,13 @@ static inline uint32_t symrelay_seg_lanes(uint32_t nc) {
  * every thread the GPU can hold (148 SMs x 2,048) the batch is bound by total work, and the wide form's barriers and extra
  * launch cost more than the shorter tail saves (BASELINE config 3 on one GPU: 71 -> 74 us with it, measured). */
 #define SYMRELAY_WIDE_MAX_BATCH_BLOCKS 262144u
-static inline bool symrelay_wide_ok(uint32_t n_big, uint64_t batch_blocks) {
+/* ... and at most this many descriptors: the device-resident entry points get their tile list in device memory and cannot
+ * look for wide tiles; with this cap they know from the descriptor count alone when the wide kernel has nothing to do. */
+#define SYMRELAY_WIDE_MAX_BATCH_FRAMES 32768u
+static inline bool symrelay_wide_ok(uint32_t n_big, uint64_t batch_blocks, uint32_t n_frames) {
     static const bool off = getenv("SYMRELAY_WIDE") && atoi(getenv("SYMRELAY_WIDE")) == 0;   // kill switch (measurements)
-    return !off && n_big != 0u && n_big <= SYMRELAY_WIDE_MAX_FRAMES && batch_blocks < SYMRELAY_WIDE_MAX_BATCH_BLOCKS;
+    return !off && n_big != 0u && n_big <= SYMRELAY_WIDE_MAX_FRAMES && batch_blocks < SYMRELAY_WIDE_MAX_BATCH_BLOCKS &&
+           n_frames <= SYMRELAY_WIDE_MAX_BATCH_FRAMES;
 }
 #define SYMRELAY_THREAD_TILE_HUGE_BATCH 98304u  /* a uniform batch of BIG frames with this many of them (3,072 warps: ~20 per SM) does too */
 
@@ -221,7 +225,7 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
         uint32_t n_big = 0;
         uint64_t blocks = 0;
         for (uint32_t i = 0; i < n; i++) { n_big += nc[i] > SYMRELAY_WIDE_MIN_BLOCKS ? 1u : 0u; blocks += nc[i]; }
-        const bool wide = symrelay_wide_ok(n_big, blocks);
+        const bool wide = symrelay_wide_ok(n_big, blocks, n);
         for (uint32_t i = 0; i < n; i++) {
             if (nc[i] > 32u) {
                 if (tiles && n_tiles < max_tiles) {
@@ -310,7 +314,7 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
     {   // big frames: largest size class first (see the sort below), so the wide ones are the first n_big of them
         uint32_t n_big = 0;
         for (uint32_t k = 7u; k < 20u; k++) n_big += bulk_class[k];   // classes 7..: more than SYMRELAY_WIDE_MIN_BLOCKS blocks
-        const uint32_t n_wide = symrelay_wide_ok(n_big, batch_blocks) ? n_big : 0u;
+        const uint32_t n_wide = symrelay_wide_ok(n_big, batch_blocks, n) ? n_big : 0u;
         for (uint32_t k = 0; k < count[31]; k++) {
             if (tiles && n_tiles < max_tiles) {
                 tiles[n_tiles].first = base[31] + k;

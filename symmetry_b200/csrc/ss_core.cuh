@@ -1021,14 +1021,16 @@ SS_DEV void ss_thread_window(uint32_t acc[5], uint32_t w[16], uint32_t q, uint32
     ss_phorner(acc, w, (uint32_t)nbytes, r);
 }
 
-template <bool VOL = false>
+// LATE: the instantiation that understands SS_ARG_VERDICT_LATE (kept out of the kernels that never see it: the extra
+// live values cost ss_thread_kernel a spill and BASELINE config 3 two microseconds).
+template <bool VOL = false, bool LATE = false>
 SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_pdl_launch_dependents();
     // SS_ARG_VERDICT_LATE: the kernel this one depends on is the batch's extractor, which writes status words and deltas
     // only.  Both kernels are one serial chain per frame with a few warps per SM, so they run side by side: this one seals
     // while the verdicts are being worked out and waits for them at the very end (a refused chunk is then taken back).
-    const bool late_ok = (a.flags & SS_ARG_VERDICT_LATE) != 0;
+    const bool late_ok = LATE && (a.flags & SS_ARG_VERDICT_LATE) != 0;
     if (!(a.flags & SS_ARG_INPUT_INDEPENDENT) && !late_ok) ss_pdl_wait();
     const SsTile tile = given ? *given : a.tiles[tile_idx];
     const uint32_t nfr = tile.n_kind & 0xffffu;

@@ -44,7 +44,7 @@ static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) =
 __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
-    if (a.tiles[warp].n_kind & (1u << 17)) ss_process_thread_tile(a, warp);   // warp-uniform: whole tile is one kind
+    if (a.tiles[warp].n_kind & (1u << 17)) ss_process_thread_tile<false, true>(a, warp);   // warp-uniform: whole tile is one kind
     else ss_process_tile<false>(a, warp);
 }
 
@@ -60,6 +60,14 @@ __global__ void __launch_bounds__(128, SS_THREAD_MIN_BLOCKS) ss_thread_kernel(Ss
     const SsTile tile = a.tiles[warp];
     if (!(tile.n_kind & (1u << 17))) return;
     ss_process_thread_tile(a, warp, &tile);
+}
+// ... and the form for batches with an extractor pass (SS_ARG_VERDICT_LATE, ss_core.cuh)
+__global__ void __launch_bounds__(128, SS_THREAD_MIN_BLOCKS) ss_thread_late_kernel(SsArgs a) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= a.n_tiles) return;
+    const SsTile tile = a.tiles[warp];
+    if (!(tile.n_kind & (1u << 17))) return;
+    ss_process_thread_tile<false, true>(a, warp, &tile);
 }
 __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_only_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -80,7 +88,7 @@ __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_inline_ke
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
     const SsTile tile = tb.t[warp];
-    if (tile.n_kind & (1u << 17)) ss_process_thread_tile(a, warp, &tile);
+    if (tile.n_kind & (1u << 17)) ss_process_thread_tile<false, true>(a, warp, &tile);
     else ss_process_tile<false>(a, warp, &tile);
 }
 
@@ -948,7 +956,8 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     //   strided tiles (mid-size frames)                                    -> side stream 2
     //   packed tiles of a large batch                                      -> side stream 3
     const bool big = n_packed > 148u * 8u && !write_back;   // large batch: split the small tiles by kind (see ss_thread_kernel)
-    bool has_thread = n_packed != 0, has_packed = big, has_strided = n_bulk != 0, has_bulk = n_bulk != 0, has_wide = n_bulk != 0;
+    bool has_thread = n_packed != 0, has_packed = big, has_strided = n_bulk != 0, has_bulk = n_bulk != 0,
+         has_wide = n_bulk != 0 && n <= SYMRELAY_WIDE_MAX_BATCH_FRAMES;   // (the planner forms no wide tiles in larger batches)
     uint32_t wide_lo = 0, wide_hi = n_bulk;   // the range of bulk-class tiles the wide kernel is launched over
     if (host_tiles) {   // the tile list is in host memory: launch only what is there
         has_strided = has_bulk = has_wide = false;
@@ -1039,7 +1048,8 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
                 if (s != stream) CU(ctx, cudaEventRecord(fork->ev_join3, s));
             }
             if (has_thread) {   // the caller's stream
-                CU(ctx, launch_pdl(ss_thread_kernel, grid, threads, stream, late, a));
+                if (late) CU(ctx, launch_pdl(ss_thread_late_kernel, grid, threads, stream, true, a));
+                else CU(ctx, launch_pdl(ss_thread_kernel, grid, threads, stream, false, a));
                 ctx->launches++;
             }
         } else if (host_tiles && n_packed <= SS_INLINE_TILES && ctx->inline_tiles) {

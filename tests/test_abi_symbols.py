@@ -50,8 +50,8 @@ def test_planner_and_desc_check_are_host_only():
 
 def test_planner_marks_wide_tiles_only_when_big_frames_are_few():
     """Frames of 128 blocks and more (> 8,000 payload bytes) get a whole 128-thread block (tile bit 18) when the batch
-    holds at most 2,048 of them and fewer than 262,144 ChaCha20 blocks in all (beyond that it is bound by total work, not
-    by its longest frame); a batch of many big frames keeps one warp per frame.  Both planners agree."""
+    holds at most 2,048 of them, fewer than 262,144 ChaCha20 blocks in all and at most 32,768 frames (beyond that it is
+    bound by total work, not by its longest frame); a batch of many big frames keeps one warp per frame.  Both planners agree."""
     import ctypes as C
 
     import numpy as np
@@ -89,6 +89,10 @@ def test_planner_marks_wide_tiles_only_when_big_frames_are_few():
         tiles, d = plan([64] * 10 + [8001] * 2047, sorted_)           # 2,047 x 128 + 10 x 3 = 262,046 blocks
         assert sum(1 for t in tiles if t[1] & (1 << 18)) == 2047, sorted_
         tiles, d = plan([64] * 100 + [8001] * 2047, sorted_)          # 262,316 blocks: bound by total work
+        assert not any(t[1] & (1 << 18) for t in tiles), sorted_
+        tiles, d = plan([64] * 32767 + [9000], sorted_)
+        assert sum(1 for t in tiles if t[1] & (1 << 18)) == 1, sorted_
+        tiles, d = plan([64] * 32768 + [9000], sorted_)               # 32,769 frames
         assert not any(t[1] & (1 << 18) for t in tiles), sorted_
 
 
