@@ -37,6 +37,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 L2_BYTES = 126 << 20
 METRIC = "sealed_frames_per_sec"
+GATE_CYCLES = 400_000                       # ~200 us at 1.965 GHz: the spin kernel ahead of the device-timed region
 DEFAULT_STEPS = {"c2": 20000, "c3": 200, "c4": 64, "c5": 360, "c1": 20, "c4sweep": 8}
 SUB_STEPS = {"c4": 64, "c3": 200}          # steps of the sub-lines riding on the default line
 
@@ -131,6 +132,9 @@ def make_config(name: str, n_gpus: int, K: int, no_graph: bool, plan_mode: str) 
                    f"GPU arm: {n_replays} replays of a CUDA graph holding {R} steps + one graph of the last {K - n_replays * R} "
                    "steps, each replayed once untimed first (graph upload)")
                   + "; CPU arm: a pool of host threads started and warmed before the timed steps",
+        "timing": "GPU arm: CUDA events on the launching stream around exactly K steps, max over ranks; a ~200 us spin kernel "
+                  "ahead of the start event lets the host queue the timed launches first, so host launch latency is outside "
+                  "the window; CPU arm: each worker thread's own clock, latest end minus earliest start",
     }
 
 
@@ -449,6 +453,12 @@ def measure_device(job: Job, name: str, K: int, W: int, no_graph: bool, relay=No
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = relay.launches
     t_w0 = time.perf_counter()
+    # A spin kernel (no memory traffic) keeps the stream busy while the host queues the start event, the timed launches
+    # and the end event: the two events then bracket device time only.  Without it the driver's 20-step run (one graph
+    # launch of ~130 us of work) also times the host's cudaGraphLaunch call, which with eight ranks sharing the host cores
+    # was the whole "scaling loss" of the device-resident number.
+    if hasattr(torch.cuda, "_sleep"):
+        torch.cuda._sleep(GATE_CYCLES)
     e0.record()
     for _ in range(n_replays):
         graph.replay()
