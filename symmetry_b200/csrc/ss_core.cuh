@@ -188,6 +188,7 @@ struct SsArgs {
     SsDesc *desc_fill = nullptr;   // resident kernel: also leave a copy of the tile's descriptors here (device memory), for the
                                    // next batch that repeats them -- it then reads them from HBM instead of over PCIe
     uint32_t ver_all = 0;     // SS_ARG_CHAIN_UNIFORM: every descriptor expects this stamp (the batch repeats its predecessor's streams)
+    const volatile uint32_t *verdicts = nullptr;   // fused extract+seal kernel: the 32 verdict words (shared memory) of this tile's chunks
 };
 
 SS_DEV void ss_dbg_stamp(const SsArgs &a, uint32_t tile_idx, uint32_t lane, uint32_t which) {
@@ -1021,16 +1022,23 @@ SS_DEV void ss_thread_window(uint32_t acc[5], uint32_t w[16], uint32_t q, uint32
     ss_phorner(acc, w, (uint32_t)nbytes, r);
 }
 
-// LATE: the instantiation that understands SS_ARG_VERDICT_LATE (kept out of the kernels that never see it: the extra
-// live values cost ss_thread_kernel a spill and BASELINE config 3 two microseconds).
-template <bool VOL = false, bool LATE = false>
+// LATE = 1: the instantiation that understands SS_ARG_VERDICT_LATE (kept out of the kernels that never see it: the extra
+// live values cost ss_thread_kernel a spill and BASELINE config 3 two microseconds).  LATE = 2: the tile runs inside
+// the fused extract+seal kernel: same order of work, but the verdict of frame `lane` arrives in a.verdicts[lane]
+// (shared memory, SS_VERDICT_EMPTY until the chunk's bookkeeping thread in the same block has written it).
+#define SS_VERDICT_EMPTY 0xffffffffu
+template <bool VOL = false, int LATE = 0>
 SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsTile *given = nullptr) {
     const uint32_t lane = ss_lane();
     ss_pdl_launch_dependents();
     // SS_ARG_VERDICT_LATE: the kernel this one depends on is the batch's extractor, which writes status words and deltas
     // only.  Both kernels are one serial chain per frame with a few warps per SM, so they run side by side: this one seals
     // while the verdicts are being worked out and waits for them at the very end (a refused chunk is then taken back).
-    const bool late_ok = LATE && (a.flags & SS_ARG_VERDICT_LATE) != 0;
+    const bool late_ok = LATE == 2 || (LATE == 1 && (a.flags & SS_ARG_VERDICT_LATE) != 0);
+#ifdef SS_PROBE_TIMELINE
+    if (LATE && tile_idx == 0 && lane == 0) PROBE_SET(2);
+    if (LATE && lane == 0) PROBE_MAX(8);
+#endif
     if (!(a.flags & SS_ARG_INPUT_INDEPENDENT) && !late_ok) ss_pdl_wait();
     const SsTile tile = given ? *given : a.tiles[tile_idx];
     const uint32_t nfr = tile.n_kind & 0xffffu;
@@ -1140,9 +1148,24 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
         }
     }
     const uint32_t frame_idx = tile.first + lane;
+#ifdef SS_PROBE_TIMELINE
+    if (LATE && lane == 0) PROBE_MAX(5);
+#endif
     if (late_ok) {
-        ss_pdl_wait();   // the extractor has finished: its status words are visible
-        if (wants_verdict && *reinterpret_cast<const volatile uint32_t *>(a.status + frame_idx) != SS_ST_OK) {
+        uint32_t verdict = SS_ST_OK;
+        if (LATE == 2) {
+            if (wants_verdict) {
+                verdict = a.verdicts[lane];
+                for (uint32_t spins = 0; verdict == SS_VERDICT_EMPTY && spins < (1u << 24); spins++) {
+                    ss_nanosleep(200);
+                    verdict = a.verdicts[lane];
+                }
+            }
+        } else {
+            ss_pdl_wait();   // the extractor has finished: its status words are visible
+            if (wants_verdict) verdict = *reinterpret_cast<const volatile uint32_t *>(a.status + frame_idx);
+        }
+        if (verdict != SS_ST_OK) {
             // refused (the reference throws before peer.write, or the host must extract): the stream state stays as it
             // was, the status word is the extractor's, and the wire bytes sealed ahead of the verdict are wiped
             uint32_t z[16];
@@ -1177,4 +1200,7 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
     sp[2] = t2;
     if (chain) ss_st_release_u32(verp, ver_word);
     a.status[frame_idx] = SS_ST_OK | (tag << 8);
+#ifdef SS_PROBE_TIMELINE
+    if (LATE && lane == 0) PROBE_MAX(3);
+#endif
 }

@@ -580,7 +580,6 @@ enum : uint32_t { QSEL_AFTER = 0, QSEL_COMMA = 1, QSEL_CLOSE_OBJ = 2, QSEL_CLOSE
 #define SX_FAST_MAX_LEN 4095u       /* positions are stored in 12 bits */
 #define SX_FAST_MAX_DEPTH 13u       /* deeper chunks are left to the single pass */
 #define SX_FAST_STACK_WORDS (SX_FAST_MAX_DEPTH + 3u)
-#define SX_FAST_SCRATCH_WORDS(ev_cap) (SX_FAST_STACK_WORDS + (ev_cap) + 1u)
 #define SX_CTX_TOP ((uint32_t)sx::Q_AFTER_T)                          /* comma, '}' and ']' are errors at top level */
 #define SX_CTX_OBJ ((uint32_t)sx::Q_AFTER_O | (sx::Q_OBJ_KEY << 8))   /* | state after this object's '}' << 16 */
 #define SX_CTX_ARR ((uint32_t)sx::Q_AFTER_A | (sx::Q_VALUE << 8))     /* | state after this array's ']' << 24 */
@@ -758,147 +757,280 @@ SS_DEV uint32_t permute(uint32_t a, uint32_t b, uint32_t sel) {
 #endif
 }
 
+// t must be readable up to t[s + 7] (every caller's text is readable 8 bytes past its end).  No loop: the lanes of the
+// bookkeeping warp run this for every key of every chunk, and eight independent byte loads cost less than a loop
+// that shifts a 64-bit word into place byte by byte.
 SS_DEV uint32_t match_key_plain(const uint8_t *t, uint32_t s, uint32_t e) {
     const uint32_t len = e - s;
     if (len != 1u && len != 5u && len != 7u) return KEY_NONE;
-    uint64_t k = 0;
-    for (uint32_t i = 0; i < len; i++) k |= (uint64_t)t[s + i] << (8u * i);
-    return k == 0x0073656369'6f6863ull ? KEY_CHOICES : k == 0x00746e65'746e6f63ull ? KEY_CONTENT
-         : k == 0x000000'61746c6564ull ? KEY_DELTA : k == 0x30ull ? KEY_ZERO : KEY_NONE;
+    const uint8_t *q = t + s;
+    const uint32_t lo = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+    const uint32_t hi = (uint32_t)q[4] | ((uint32_t)q[5] << 8) | ((uint32_t)q[6] << 16);
+    if (len == 1u) return (lo & 0xffu) == 0x30u ? KEY_ZERO : KEY_NONE;
+    if (len == 5u) return (lo == 0x746c6564u && (hi & 0xffu) == 0x61u) ? KEY_DELTA : KEY_NONE;            // "delt" "a"
+    return (lo == 0x696f6863u && hi == 0x00736563u) ? KEY_CHOICES                                          // "choi" "ces"
+         : (lo == 0x746e6f63u && hi == 0x00746e65u) ? KEY_CONTENT : KEY_NONE;                              // "cont" "ent"
 }
 
-// Returns false if the chunk is left to extract_chunk: more events than `ev_cap`, or nesting deeper than
-// SX_FAST_MAX_DEPTH.  text: 4-byte aligned, n <= SX_FAST_MAX_LEN, readable up to text + n + 8; F, cls8:
-// build_fast_tables(); scratch: SX_FAST_SCRATCH_WORDS(ev_cap) words.
-SS_DEV bool extract_fast(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap, const uint64_t *F,
-                         const uint8_t *cls8, uint32_t *scratch, uint32_t ev_cap, Result *res) {
-    uint32_t pos = 0, end = n;
-    const bool prefixed = n >= 5 && text[0] == 'd' && text[1] == 'a' && text[2] == 't' && text[3] == 'a' && text[4] == ':';
-    if (prefixed) pos = 5;
+// ---- the two passes as three roles ------------------------------------------------------------------
+// One thread per chunk runs ~12,000 dependent instructions (25 us for 16,384 chunks of ~216 B with one warp per
+// scheduler).  The work splits into three stages that only talk through small queues, so the kernel gives a chunk
+// to three threads in three different warps of a block and the stages run side by side:
+//   A  fast_grammar   the byte loop proper: class look-up, table entry, the two permutes, the container stack.
+//                     Per four input bytes it publishes ONE word holding the four entries' flag bytes.
+//   B  fast_record    turns flag bytes into the event list (value start positions, one word per event).
+//   C  fast_bookkeep  the per-event bookkeeping (which value is this?), then the provider switch / ToString.
+// Queues are arrays in shared memory pre-filled with SX_PIPE_EMPTY: a consumer polls the word it needs next, so a
+// word is its own "ready" flag and nothing needs a fence (no real flag word or event word has all bits set).  A
+// publishes a trailer word last (final state, "ended inside a number"); B ends the event list with an SX_E_END
+// word that also carries the deepest nesting and the "second data: somewhere unusual" flag.  A never waits for anyone; B and C give up after SX_PIPE_SPIN_LIMIT empty polls (the chunk then takes the
+// single pass), so no interleaving can hang.  Run one after the other by one thread (extract_fast below, the
+// emulator's form) the same code needs no pre-fill: every poll finds its word.
+#define SX_PIPE_EMPTY 0xffffffffu
+#define SX_PIPE_SPIN_LIMIT (1u << 20)
+#define SX_E_END 13u                /* event type of the terminator word: | deepest nesting << 8 | SX_END_* */
+#define SX_TRAILER_VALID 0x80000000u
+#define SX_END_OVERFLOW 1u             /* terminator word: the event list may have overflowed (or B gave up) */
+#define SX_END_SPLIT 2u                /* terminator word: a second "data:" somewhere unusual (QF_SPLIT seen) */
+#define SX_TRAILER_NUMEND 0x00020000u  /* the input ended inside a number: one more E_NUM event at `end` */
+#define SX_FAST_FLAG_WORDS(n) (((n) + 3u) >> 2)
+#define SX_FAST_SCRATCH_WORDS_N(ev_cap, n) (SX_FAST_STACK_WORDS + 1u + SX_FAST_FLAG_WORDS(n) + (ev_cap) + 1u)
 
-    // ---- pass 1: grammar only.  Written without branches: each lane of a warp is at a different place in
-    // its own chunk, so any branch here is taken by some lane in nearly every iteration.  A warp of these
-    // runs alone on its scheduler and most instructions wait for the one before: what counts is how few
-    // instructions a byte takes. ----
-    //  - saved[d] holds the ctx of the container d levels up.  Every byte stores the current ctx at its own
-    //    depth (harmless unless the byte opens a container, when that slot becomes live) and reloads the
-    //    slot below, so that a closing bracket finds its parent's ctx in a register.
-    //  - every byte also stores an event word at ev[nev]; only bytes that carry an event advance nev.
-    uint32_t *saved = scratch + 1;                       // saved[-1] is read at depth 0
-    uint32_t *ev = scratch + SX_FAST_STACK_WORDS;
-    uint32_t state = Q_VALUE, ctx = SX_CTX_TOP, popctx = SX_CTX_TOP, depth = 0, max_depth = 0, vs12 = 0, nev = 0, seen = 0;
+SS_DEV bool fast_prefixed(const uint8_t *text, uint32_t n) {
+    return n >= 5 && text[0] == 'd' && text[1] == 'a' && text[2] == 't' && text[3] == 'a' && text[4] == ':';
+}
+// Waiting: the first few empty polls follow each other directly (the producer is usually a fraction of a microsecond
+// away), after that each is followed by a short sleep so that a consumer far ahead of its producer leaves the issue
+// slots to the warps that have work.  (A sleep after EVERY empty poll made the consumers the bottleneck: the lanes of
+// a warp move on together, so one late word puts 32 chunks to sleep; 0.8 us per poll turned ~20 rounds into 16 us.)
+#ifdef __CUDA_ARCH__
+SS_DEV void pipe_backoff(uint32_t spins) { if (spins >= 8u) __nanosleep(100); }
+#else
+SS_DEV void pipe_backoff(uint32_t) {}
+#endif
+
+// Role A.  text: 4-byte aligned, n <= SX_FAST_MAX_LEN, readable up to text + n + 8; stack: SX_FAST_STACK_WORDS words
+// of scratch; fl: SX_FAST_FLAG_WORDS(n) words (the queue to B); trailer: one word.
+SS_DEV void fast_grammar(const uint8_t *text, uint32_t n, const uint64_t *F, const uint8_t *cls8, uint32_t *stack,
+                         volatile uint32_t *fl, volatile uint32_t *trailer) {
+    uint32_t pos = fast_prefixed(text, n) ? 5u : 0u;
+    const uint32_t end = n;
+    // Written without branches: each lane of a warp is at a different place in its own chunk, so any branch here is
+    // taken by some lane in nearly every iteration.  A warp of these runs alone on its scheduler and most instructions
+    // wait for the one before: what counts is how few instructions a byte takes.
+    //  - saved[d] holds the ctx of the container d levels up.  Every byte stores the current ctx at its own depth
+    //    (harmless unless the byte opens a container, when that slot becomes live) and reloads the slot below, so that
+    //    a closing bracket finds its parent's ctx in a register.
+    uint32_t *saved = stack + 1;                       // saved[-1] is read at depth 0
+    uint32_t state = Q_VALUE, ctx = SX_CTX_TOP, popctx = SX_CTX_TOP, depth = 0;
     const char *Fb = reinterpret_cast<const char *>(F);
-    auto step = [&](const char *col, uint32_t p) {   // col: the byte's column of the table
+    auto step = [&](const char *col) -> uint32_t {   // col: the byte's column of the table; returns the entry's flag byte
         const uint64_t ent = *reinterpret_cast<const uint64_t *>(col + state * (SX_FAST_CLASSES * 8u));
         const uint32_t lo = (uint32_t)ent, hi = (uint32_t)(ent >> 32);
         state = permute(ctx, lo, lo);              // loop-carried: table load -> permute -> address -> table load
-        seen |= lo;
         const uint32_t dclamp = depth < SX_FAST_MAX_DEPTH + 1u ? depth : SX_FAST_MAX_DEPTH + 1u;   // also catches a wrapped depth
         saved[dclamp] = ctx;
         ctx = (int32_t)lo < 0 ? popctx : permute(ctx, hi, hi);   // a bracket of the wrong kind lands in Q_ERR, where nothing matters any more
         depth += (uint32_t)((int32_t)lo >> 30);
-        max_depth = depth > max_depth && (int32_t)depth > 0 ? depth : max_depth;
         const uint32_t dnew = depth < SX_FAST_MAX_DEPTH + 1u ? depth : SX_FAST_MAX_DEPTH + 1u;
         popctx = saved[(int32_t)dnew - 1];
-        vs12 = (lo & (QF_START << 24)) ? (p << 12) : vs12;
-        ev[nev] = (lo & 0x0f000000u) | vs12 | p;
-        nev += (lo & 0x0f000000u) != 0u;
-        nev = nev < ev_cap ? nev : ev_cap;
+        return lo >> 24;      // (the deepest nesting and the QF_SPLIT bit are B's to collect: both are in the flag bytes)
     };
     // the class of a byte does not depend on the state: fetch four bytes ahead of the chain
     const char *k[4], *kn[4];
 #pragma unroll
     for (uint32_t j = 0; j < 4; j++) k[j] = Fb + cls8[text[pos + j]];
+    uint32_t g = 0;
     while (pos + 4u <= end) {
 #pragma unroll
         for (uint32_t j = 0; j < 4; j++) kn[j] = Fb + cls8[text[pos + 4u + j]];
+        uint32_t w = 0;
 #pragma unroll
-        for (uint32_t j = 0; j < 4; j++) step(k[j], pos + j);
+        for (uint32_t j = 0; j < 4; j++) w |= step(k[j]) << (8u * j);
+        fl[g++] = w;
 #pragma unroll
         for (uint32_t j = 0; j < 4; j++) k[j] = kn[j];
         pos += 4u;
     }
+    if (pos < end) {
+        uint32_t w = 0;
 #pragma unroll
-    for (uint32_t j = 0; j < 3; j++)
-        if (pos + j < end) step(k[j], pos + j);
+        for (uint32_t j = 0; j < 3; j++)
+            if (pos + j < end) w |= step(k[j]) << (8u * j);
+        fl[g++] = w;
+    }
+    uint32_t t = SX_TRAILER_VALID;
     if (state == Q_NZERO || state == Q_NINT || state == Q_NFRAC || state == Q_NEXP) {   // a number may end with the input
-        ev[nev] = (E_NUM << 24) | vs12 | end;
-        nev = nev + 1u < ev_cap ? nev + 1u : ev_cap;
+        t |= SX_TRAILER_NUMEND;
         state = ctx & 0xffu;
     }
-    if (nev >= ev_cap || max_depth > SX_FAST_MAX_DEPTH) return false;   // nev stops at ev_cap: the list may have overflowed
-    if (prefixed && (seen & (QF_SPLIT << 24))) return false;            // a second "data:" somewhere unusual
-    if (!prefixed && state == Q_CUT) return false;                      // no split without the prefix: parse it all
-    const bool parsed = state == Q_AFTER_T || (prefixed && state == Q_DONE);   // Q_AFTER_T is only reachable outside every container
+    *trailer = t | state;
+}
 
-    // ---- pass 2: which of the values on the path did the chunk hold? ----
-    Tracked tr;
-    tr.root = tr.choices = tr.elem0 = tr.delta = V_ABSENT;
-    tr.choices_nonempty = false;
-    tr.content.kind = tr.rcontent.kind = V_ABSENT;
-    tr.content.s = tr.content.e = tr.content.flags = 0;
-    tr.rcontent.s = tr.rcontent.e = tr.rcontent.flags = 0;
-    if (parsed) {
-        uint32_t d2 = 0, lastkey = KEY_NONE, last_started = T_NONE;
-        bool root_obj = false, d2_obj = false, act2 = false, act3 = false, act4 = false, first2 = false;
-        for (uint32_t k = 0; k < nev; k++) {
-            const uint32_t e = ev[k], type = (e >> 24) & 15u, vs = (e >> 12) & 0xfffu, p = e & 0xfffu;
-            if (type == E_KEY || type == E_KEY_ESC) {
-                lastkey = type == E_KEY ? match_key_plain(text, vs + 1u, p) : match_key(text, vs + 1u, p, true);
-                continue;
-            }
-            if (type <= E_LIT_N) {
-                const uint32_t slot =
-                    d2 == 0 ? T_ROOT
-                    : d2 == 1 && root_obj && lastkey == KEY_CHOICES ? T_CHOICES
-                    : d2 == 1 && root_obj && lastkey == KEY_CONTENT ? T_RCONTENT
-                    : d2 == 2 && act2 && (d2_obj ? lastkey == KEY_ZERO : first2) ? T_ELEM0
-                    : d2 == 3 && act3 && lastkey == KEY_DELTA ? T_DELTA
-                    : d2 == 4 && act4 && lastkey == KEY_CONTENT ? T_CONTENT
-                    : T_NONE;
-                const uint32_t vk = type == E_OPEN_OBJ ? V_OBJECT : type == E_OPEN_ARR ? V_ARRAY : type == E_STR ? V_STRING
-                                  : type <= E_NUM_CLOSE ? V_NUMBER : type == E_LIT_T ? V_TRUE : type == E_LIT_F ? V_FALSE : V_NULL;
-                // (re)assigned: it and everything below start over (duplicate keys: last wins)
-                if (slot == T_ROOT) tr.root = vk;
-                if (slot == T_CHOICES) {
-                    tr.choices = vk; tr.choices_nonempty = type == E_STR && p > vs + 1u;
-                    tr.elem0 = tr.delta = tr.content.kind = V_ABSENT; act2 = act3 = act4 = false;
-                }
-                if (slot == T_ELEM0) { tr.elem0 = vk; tr.delta = tr.content.kind = V_ABSENT; act3 = act4 = false; }
-                if (slot == T_DELTA) { tr.delta = vk; tr.content.kind = V_ABSENT; act4 = false; }
-                if (slot == T_CONTENT || slot == T_RCONTENT) {
-                    Val v;
-                    v.kind = vk; v.s = v.e = v.flags = 0;
-                    if (type == E_STR) { v.s = vs + 1u; v.e = p; }
-                    if (vk == V_NUMBER) { v.s = vs; v.e = p; v.flags = number_flags(text, vs, p); }
-                    if (slot == T_CONTENT) tr.content = v; else tr.rcontent = v;
-                }
-                if (d2 == 2 && act2 && !d2_obj) first2 = false;
-                last_started = slot;
-                if (type == E_OPEN_OBJ || type == E_OPEN_ARR) {
-                    const bool obj = type == E_OPEN_OBJ;
-                    if (d2 == 0) root_obj = obj;
-                    if (d2 == 1) d2_obj = obj;
-                    d2++;
-                    if (slot == T_CHOICES) { act2 = true; first2 = !obj; }
-                    if (slot == T_ELEM0) act3 = obj;
-                    if (slot == T_DELTA) act4 = obj;
-                }
-            }
-            if (type == E_NUM_CLOSE || type >= E_CLOSE) {
-                if (type == E_CLOSE_EMPTY) {   // "[]": the value that opened it is the most recent one
-                    if (last_started == T_CONTENT && tr.content.kind == V_ARRAY) tr.content.flags |= AF_EMPTY;
-                    if (last_started == T_RCONTENT && tr.rcontent.kind == V_ARRAY) tr.rcontent.flags |= AF_EMPTY;
-                }
-                d2--;
-                if (d2 < 2) act2 = false;
-                if (d2 < 3) act3 = false;
-                if (d2 < 4) act4 = false;
-            }
+// Polls *q until it holds something; false after SX_PIPE_SPIN_LIMIT empty polls.
+SS_DEV bool pipe_take(volatile const uint32_t *q, uint32_t *w) {
+    uint32_t v = *q;
+    for (uint32_t spins = 0; v == SX_PIPE_EMPTY; spins++) {
+        if (spins >= SX_PIPE_SPIN_LIMIT) return false;
+        pipe_backoff(spins);
+        v = *q;
+    }
+    *w = v;
+    return true;
+}
+
+// Role B.  ev: ev_cap + 1 words (the queue to C).  Every flag byte is handled by the same few instructions; an
+// event is one predicated store.
+SS_DEV void fast_record(uint32_t n, bool prefixed, volatile const uint32_t *fl, volatile const uint32_t *trailer,
+                        volatile uint32_t *ev, uint32_t ev_cap) {
+    const uint32_t pos0 = prefixed ? 5u : 0u;
+    const uint32_t groups = n > pos0 ? (n - pos0 + 3u) >> 2 : 0u;
+    uint32_t vs12 = 0, nev = 0, depth = 0, max_depth = 0, seen = 0;
+    bool dead = false;
+    for (uint32_t g = 0; g < groups && !dead; g++) {
+        uint32_t w;
+        if (!pipe_take(fl + g, &w)) { dead = true; break; }
+        seen |= w;
+#pragma unroll
+        for (uint32_t j = 0; j < 4; j++) {
+            const uint32_t f = (w >> (8u * j)) & 0xffu, p = pos0 + 4u * g + j;
+            depth += (uint32_t)((int32_t)(f << 24) >> 30);   // the flag byte's top two bits: +1 a container opens, -1 one closes
+            max_depth = depth > max_depth && (int32_t)depth > 0 ? depth : max_depth;
+            vs12 = (f & QF_START) ? (p << 12) : vs12;
+            if ((f & 15u) && nev < ev_cap) ev[nev] = ((f & 15u) << 24) | vs12 | p;
+            nev += (f & 15u) != 0u;
         }
     }
-    *res = finish(text, parsed, false, tr, kind, out, cap);
+    uint32_t t = 0;
+    if (!dead && !pipe_take(trailer, &t)) dead = true;   // (the trailer slot starts as SX_PIPE_EMPTY too)
+    if (!dead && (t & SX_TRAILER_NUMEND)) {
+        if (nev < ev_cap) ev[nev] = (E_NUM << 24) | vs12 | n;
+        nev++;
+    }
+    const bool overflow = dead || nev >= ev_cap;   // as in the one-thread form: a full list may have overflowed
+    const bool split = (seen & (QF_SPLIT * 0x01010101u)) != 0u;
+    ev[nev < ev_cap ? nev : ev_cap] = (SX_E_END << 24) | ((max_depth < 255u ? max_depth : 255u) << 8) |
+                                     (overflow ? SX_END_OVERFLOW : 0u) | (split ? SX_END_SPLIT : 0u);
+}
+
+// The bookkeeping of one event (what the single pass does inside its byte loop).
+struct Book {
+    Tracked tr;
+    uint32_t d2, lastkey, last_started;
+    bool root_obj, d2_obj, act2, act3, act4, first2;
+};
+SS_DEV void book_init(Book &b) {
+    b.tr.root = b.tr.choices = b.tr.elem0 = b.tr.delta = V_ABSENT;
+    b.tr.choices_nonempty = false;
+    b.tr.content.kind = b.tr.rcontent.kind = V_ABSENT;
+    b.tr.content.s = b.tr.content.e = b.tr.content.flags = 0;
+    b.tr.rcontent.s = b.tr.rcontent.e = b.tr.rcontent.flags = 0;
+    b.d2 = 0; b.lastkey = KEY_NONE; b.last_started = T_NONE;
+    b.root_obj = b.d2_obj = b.act2 = b.act3 = b.act4 = b.first2 = false;
+}
+SS_DEV void book_event(Book &b, const uint8_t *text, uint32_t e) {
+    Tracked &tr = b.tr;
+    const uint32_t type = (e >> 24) & 15u, vs = (e >> 12) & 0xfffu, p = e & 0xfffu;
+    if (type == E_KEY || type == E_KEY_ESC) {
+        b.lastkey = type == E_KEY ? match_key_plain(text, vs + 1u, p) : match_key(text, vs + 1u, p, true);
+        return;
+    }
+    if (type <= E_LIT_N) {
+        const uint32_t slot =
+            b.d2 == 0 ? T_ROOT
+            : b.d2 == 1 && b.root_obj && b.lastkey == KEY_CHOICES ? T_CHOICES
+            : b.d2 == 1 && b.root_obj && b.lastkey == KEY_CONTENT ? T_RCONTENT
+            : b.d2 == 2 && b.act2 && (b.d2_obj ? b.lastkey == KEY_ZERO : b.first2) ? T_ELEM0
+            : b.d2 == 3 && b.act3 && b.lastkey == KEY_DELTA ? T_DELTA
+            : b.d2 == 4 && b.act4 && b.lastkey == KEY_CONTENT ? T_CONTENT
+            : T_NONE;
+        const uint32_t vk = type == E_OPEN_OBJ ? V_OBJECT : type == E_OPEN_ARR ? V_ARRAY : type == E_STR ? V_STRING
+                          : type <= E_NUM_CLOSE ? V_NUMBER : type == E_LIT_T ? V_TRUE : type == E_LIT_F ? V_FALSE : V_NULL;
+        // (re)assigned: it and everything below start over (duplicate keys: last wins)
+        if (slot == T_ROOT) tr.root = vk;
+        if (slot == T_CHOICES) {
+            tr.choices = vk; tr.choices_nonempty = type == E_STR && p > vs + 1u;
+            tr.elem0 = tr.delta = tr.content.kind = V_ABSENT; b.act2 = b.act3 = b.act4 = false;
+        }
+        if (slot == T_ELEM0) { tr.elem0 = vk; tr.delta = tr.content.kind = V_ABSENT; b.act3 = b.act4 = false; }
+        if (slot == T_DELTA) { tr.delta = vk; tr.content.kind = V_ABSENT; b.act4 = false; }
+        if (slot == T_CONTENT || slot == T_RCONTENT) {
+            Val v;
+            v.kind = vk; v.s = v.e = v.flags = 0;
+            if (type == E_STR) { v.s = vs + 1u; v.e = p; }
+            if (vk == V_NUMBER) { v.s = vs; v.e = p; v.flags = number_flags(text, vs, p); }
+            if (slot == T_CONTENT) tr.content = v; else tr.rcontent = v;
+        }
+        if (b.d2 == 2 && b.act2 && !b.d2_obj) b.first2 = false;
+        b.last_started = slot;
+        if (type == E_OPEN_OBJ || type == E_OPEN_ARR) {
+            const bool obj = type == E_OPEN_OBJ;
+            if (b.d2 == 0) b.root_obj = obj;
+            if (b.d2 == 1) b.d2_obj = obj;
+            b.d2++;
+            if (slot == T_CHOICES) { b.act2 = true; b.first2 = !obj; }
+            if (slot == T_ELEM0) b.act3 = obj;
+            if (slot == T_DELTA) b.act4 = obj;
+        }
+    }
+    if (type == E_NUM_CLOSE || type >= E_CLOSE) {
+        if (type == E_CLOSE_EMPTY) {   // "[]": the value that opened it is the most recent one
+            if (b.last_started == T_CONTENT && tr.content.kind == V_ARRAY) tr.content.flags |= AF_EMPTY;
+            if (b.last_started == T_RCONTENT && tr.rcontent.kind == V_ARRAY) tr.rcontent.flags |= AF_EMPTY;
+        }
+        b.d2--;
+        if (b.d2 < 2) b.act2 = false;
+        if (b.d2 < 3) b.act3 = false;
+        if (b.d2 < 4) b.act4 = false;
+    }
+}
+
+// Role C.  Returns false if the chunk is left to extract_chunk: more events than the list holds, nesting deeper than
+// SX_FAST_MAX_DEPTH, a second "data:" somewhere unusual, or a producer that never delivered.  The bookkeeping runs
+// on every chunk as its events arrive -- whether the chunk parsed is known only at the end, and a chunk that did not
+// parse discards what was tracked (the events of such a chunk may be unbalanced: nothing here minds).
+SS_DEV bool fast_bookkeep(const uint8_t *text, uint32_t n, bool prefixed, uint32_t kind, uint8_t *out, uint32_t cap,
+                          volatile const uint32_t *ev, volatile const uint32_t *trailer, uint32_t ev_cap, Result *res) {
+    Book b;
+    book_init(b);
+    uint32_t e = 0;
+    for (uint32_t k = 0;; k++) {
+        if (k > ev_cap || !pipe_take(ev + k, &e)) return false;
+#ifdef SS_PROBE_TIMELINE
+        if ((threadIdx.x & 31u) == 0u && k == 0) PROBE_MAX(10);
+        if ((threadIdx.x & 31u) == 0u && k == 10) PROBE_MAX(11);
+        if ((threadIdx.x & 31u) == 0u && k == 20) PROBE_MAX(12);
+#endif
+        if (((e >> 24) & 15u) == SX_E_END) break;
+        book_event(b, text, e);
+    }
+#ifdef SS_PROBE_TIMELINE
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(9);
+#endif
+    if (e & SX_END_OVERFLOW) return false;                               // the list may have overflowed (or B gave up)
+    uint32_t t;
+    if (!pipe_take(trailer, &t)) return false;                           // (B has seen it already)
+    const uint32_t state = t & 0xffu, max_depth = (e >> 8) & 0xffu;
+    if (max_depth > SX_FAST_MAX_DEPTH) return false;
+    if (prefixed && (e & SX_END_SPLIT)) return false;                    // a second "data:" somewhere unusual
+    if (!prefixed && state == Q_CUT) return false;                       // no split without the prefix: parse it all
+    const bool parsed = state == Q_AFTER_T || (prefixed && state == Q_DONE);   // Q_AFTER_T is only reachable outside every container
+    if (!parsed) book_init(b);
+    *res = finish(text, parsed, false, b.tr, kind, out, cap);
     return true;
+}
+
+// The three roles one after the other in one thread (the emulator's form; the kernel runs them in three warps).
+// Returns false if the chunk is left to extract_chunk.  text: 4-byte aligned, n <= SX_FAST_MAX_LEN, readable up to
+// text + n + 8; F, cls8: build_fast_tables(); scratch: SX_FAST_SCRATCH_WORDS_N(ev_cap, n) words.
+SS_DEV bool extract_fast(const uint8_t *text, uint32_t n, uint32_t kind, uint8_t *out, uint32_t cap, const uint64_t *F,
+                         const uint8_t *cls8, uint32_t *scratch, uint32_t ev_cap, Result *res) {
+    uint32_t *stack = scratch, *trailer = scratch + SX_FAST_STACK_WORDS, *fl = trailer + 1u,
+             *ev = fl + SX_FAST_FLAG_WORDS(n);
+    const bool prefixed = fast_prefixed(text, n);
+    fast_grammar(text, n, F, cls8, stack, fl, trailer);
+    fast_record(n, prefixed, fl, trailer, ev, ev_cap);
+    return fast_bookkeep(text, n, prefixed, kind, out, cap, ev, trailer, ev_cap, res);
 }
 
 }  // namespace sx

@@ -29,6 +29,21 @@
 
 #include "../../include/symrelay.h"
 #include "plan.h"
+#ifdef SS_PROBE_TIMELINE   // measurement builds only (tools/probes/c5_timeline.py): when do the two kernels of an extract batch run?
+__device__ unsigned long long g_probe[16];
+__device__ __forceinline__ unsigned long long probe_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define PROBE_SET(i) (g_probe[i] = probe_now())
+#define PROBE_MAX(i) atomicMax(&g_probe[i], probe_now())
+extern "C" __attribute__((visibility("default"))) int symrelay_probe_timeline(unsigned long long *out, int reset) {
+    if (out && cudaMemcpyFromSymbol(out, g_probe, sizeof(g_probe)) != cudaSuccess) return -1;
+    if (reset) { unsigned long long z[16] = {0}; if (cudaMemcpyToSymbol(g_probe, z, sizeof(z)) != cudaSuccess) return -1; }
+    return 0;
+}
+#else
+#define PROBE_SET(i) ((void)0)
+#define PROBE_MAX(i) ((void)0)
+#endif
+
 #include "ss_core.cuh"
 #include "ss_extract.cuh"
 #include "ss_runs.cuh"
@@ -44,7 +59,7 @@ static_assert(sizeof(symrelay_desc) == sizeof(SsDesc) && sizeof(symrelay_tile) =
 __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
-    if (a.tiles[warp].n_kind & (1u << 17)) ss_process_thread_tile<false, true>(a, warp);   // warp-uniform: whole tile is one kind
+    if (a.tiles[warp].n_kind & (1u << 17)) ss_process_thread_tile<false, 1>(a, warp);   // warp-uniform: whole tile is one kind
     else ss_process_tile<false>(a, warp);
 }
 
@@ -67,7 +82,7 @@ __global__ void __launch_bounds__(128, SS_THREAD_MIN_BLOCKS) ss_thread_late_kern
     if (warp >= a.n_tiles) return;
     const SsTile tile = a.tiles[warp];
     if (!(tile.n_kind & (1u << 17))) return;
-    ss_process_thread_tile<false, true>(a, warp, &tile);
+    ss_process_thread_tile<false, 1>(a, warp, &tile);
 }
 __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_only_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -88,7 +103,7 @@ __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_inline_ke
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (warp >= a.n_tiles) return;
     const SsTile tile = tb.t[warp];
-    if (tile.n_kind & (1u << 17)) ss_process_thread_tile<false, true>(a, warp, &tile);
+    if (tile.n_kind & (1u << 17)) ss_process_thread_tile<false, 1>(a, warp, &tile);
     else ss_process_tile<false>(a, warp, &tile);
 }
 
@@ -146,79 +161,159 @@ __global__ void __launch_bounds__(128) ss_run_commit_kernel(const SsDesc *desc, 
     ss_run_commit(desc, n, in, states, status, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
-// Delta extraction, one thread per frame that carries
-// SYMRELAY_F_EXTRACT.  Runs before the seal kernel of the same batch: it leaves
-// its verdict in status[i] (the seal kernel skips frames whose verdict is not
-// OK) and the delta bytes at delta_arena + in_off (the plaintext layout, so no
+// Delta extraction for the frames that carry SYMRELAY_F_EXTRACT.  Runs before (and, see
+// SS_ARG_VERDICT_LATE, beside) the seal kernel of the same batch: it leaves its verdict in status[i] (frames whose
+// verdict is not OK are not sealed) and the delta bytes at delta_arena + in_off (the plaintext layout, so no
 // allocation or scratch is needed: every frame slot holds >= max(16, mlen) bytes).
-#define SS_EXTRACT_THREADS 64
-#define SS_EXTRACT_STAGE 384u    // chunks up to this size are staged in shared memory and take the two-pass extractor
-#define SS_EXTRACT_EVENTS 95u    // events per thread; a chunk with more falls back to the single pass
-// per thread: the staged chunk (+4 bytes the prefix search may read), then the extractor's scratch.  209 words: lanes hit distinct banks
-#define SS_EXTRACT_STRIDE (SS_EXTRACT_STAGE + 4u + 4u * SX_FAST_SCRATCH_WORDS(SS_EXTRACT_EVENTS))
-#define SS_EXTRACT_SMEM (SX_FAST_ENTRIES * 8u + 256u + SS_EXTRACT_THREADS * SS_EXTRACT_STRIDE)
+// A block takes 64 chunks and gives each chunk to THREE threads in three different warps -- grammar, event recording,
+// bookkeeping (ss_extract.cuh: "the two passes as three roles") -- that hand their results on through small queues in
+// shared memory, so the stages of one chunk run side by side instead of one after the other.  Warps 2 and 3 run the
+// grammar (the long chain): with one block per SM each of them has a scheduler to itself; the lighter roles share
+// the other two schedulers.
+#define SS_EXTRACT_CHUNKS 64u    // chunks per block
+#define SS_EXTRACT_THREADS 192u  // two warps per role
+#define SS_EXTRACT_STAGE 384u    // chunks up to this size are staged in shared memory and take the three-role extractor
+#define SS_EXTRACT_EVENTS 95u    // events per chunk; a chunk with more falls back to the single pass
+// per chunk, in words: the staged chunk (+4 bytes the prefix search may read) | container stack | trailer | flag queue |
+// event queue.  307 words: the lanes of a warp hit distinct banks
+#define SS_EXTRACT_TEXT_W ((SS_EXTRACT_STAGE + 4u) / 4u)
+#define SS_EXTRACT_STRIDE_W (SS_EXTRACT_TEXT_W + SX_FAST_STACK_WORDS + 1u + SX_FAST_FLAG_WORDS(SS_EXTRACT_STAGE) + SS_EXTRACT_EVENTS + 2u)
+#define SS_EXTRACT_SMEM (SX_FAST_ENTRIES * 8u + 256u + SS_EXTRACT_CHUNKS * SS_EXTRACT_STRIDE_W * 4u)
+static_assert(SS_EXTRACT_STRIDE_W % 2u == 1u, "an odd stride keeps the lanes on distinct banks");
 
 // The two-pass tables (grammar by byte class, then the 256 class codes) live in a cudaMalloc'd block per
 // GPU, not in file-scope __device__ arrays: 15 KB more of module-global data moved later allocations and
 // cost the C2 step 8 % (4.92 -> 5.31 us, same kernel code, measured with and without the arrays).
 #define SX_FAST_BLOCK_BYTES (SX_FAST_ENTRIES * 8u + 256u)                 /* what the kernel stages in shared memory */
 #define SX_TABLES_BYTES (SX_FAST_BLOCK_BYTES + SX_TABLE_ENTRIES * 2u)   /* + the single-pass table (fallback, long chunks) */
-__global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const SsDesc *desc, uint32_t n, const uint8_t *in,
-                                                                       const uint4 *states, uint32_t *status,
-                                                                       symrelay_delta *delta, uint8_t *delta_arena,
-                                                                       const uint4 *fast_block) {
-    // The grammar pass consumes its chunk one byte at a time, each step depending on the last: read from
-    // global memory that is ~600 cycles per byte.  So each thread first pulls its chunk into a private
-    // slice of shared memory with 16-byte loads that are all in flight together, and the byte loop then
-    // runs against shared memory (chunk, class table and grammar table).
+// role: 0 grammar, 1 recording, 2 bookkeeping, 3 none (a seal warp of the fused kernel: it only helps to set up).
+// verdicts: fused kernel only -- the block's 64 verdict words in shared memory (written for every chunk; the status word
+// of an accepted chunk is then left to the seal thread, which writes the tag into it).
+__device__ __forceinline__ void ss_extract_block(const SsDesc *desc, uint32_t n, const uint8_t *in, const uint4 *states,
+                                                 uint32_t *status, symrelay_delta *delta, uint8_t *delta_arena,
+                                                 const uint4 *fast_block, uint32_t role, uint32_t group,
+                                                 volatile uint32_t *verdicts) {
+    // The grammar consumes its chunk one byte at a time, each step depending on the last: read from global memory
+    // that is ~600 cycles per byte.  So the chunk is first pulled into shared memory with 16-byte loads that are all
+    // in flight together, and the byte loop then runs against shared memory (chunk, class table and grammar table).
     extern __shared__ __align__(16) uint8_t sx_smem[];
-    ss_pdl_launch_dependents();   // the batch's seal kernel may start beside this one (SS_ARG_VERDICT_LATE, ss_core.cuh)
     uint64_t *fast = reinterpret_cast<uint64_t *>(sx_smem);
     uint8_t *cls = sx_smem + SX_FAST_ENTRIES * 8u;
-    uint8_t *sx_stage = cls + 256u;
+    uint32_t *sx_stage = reinterpret_cast<uint32_t *>(cls + 256u);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t c = group * 32u + lane;                              // this thread's chunk within the block
+    const uint32_t i = blockIdx.x * SS_EXTRACT_CHUNKS + c;
     // Three things come from global memory and two of them are a dependent chain (descriptor -> chunk and
     // provider kind): start the chain first, copy the tables while it is in flight.
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     SsDesc d;
     d.slot = 0; d.in_off = 0; d.out_off = 0; d.len_flags = 0;
     if (i < n) d = desc[i];
     const bool mine_to_do = (d.len_flags & SS_F_EXTRACT) && !(d.len_flags & SS_F_OPEN);
     const uint32_t mlen = d.len_flags & 0xffffffu;
     const uint8_t *text = in + d.in_off;
-    uint8_t *mine = sx_stage + (size_t)threadIdx.x * SS_EXTRACT_STRIDE;
+    uint32_t *base = sx_stage + (size_t)c * SS_EXTRACT_STRIDE_W;
+    uint8_t *mine = reinterpret_cast<uint8_t *>(base);
+    uint32_t *stack = base + SS_EXTRACT_TEXT_W, *trailer = stack + SX_FAST_STACK_WORDS, *fl = trailer + 1u,
+             *ev = fl + SX_FAST_FLAG_WORDS(SS_EXTRACT_STAGE);
     const bool staged = mine_to_do && mlen <= SS_EXTRACT_STAGE;
     uint32_t kind = 0;
-    if (mine_to_do) kind = states[((size_t)d.slot * 2u) * 3u + 2u].w & 0xffu;   // provider kind: low byte of the tx state's meta word
-    if (staged) {
+    if (staged && role == 0u) {
         const uint4 *src = reinterpret_cast<const uint4 *>(text);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(mine);
         const uint32_t n16 = (mlen + 15u) >> 4;
 #pragma unroll 4
         for (uint32_t b = 0; b < n16; b++) {
             const uint4 v = src[b];
-            dst[4 * b] = v.x; dst[4 * b + 1] = v.y; dst[4 * b + 2] = v.z; dst[4 * b + 3] = v.w;
+            base[4 * b] = v.x; base[4 * b + 1] = v.y; base[4 * b + 2] = v.z; base[4 * b + 3] = v.w;
         }
+    }
+    if (staged && role == 1u) {   // the queues start empty
+        const uint32_t nw = SX_FAST_FLAG_WORDS(mlen);
+        *trailer = SX_PIPE_EMPTY;
+        for (uint32_t w = 0; w < nw; w++) fl[w] = SX_PIPE_EMPTY;
+    }
+    if (mine_to_do && role == 2u) {
+        kind = states[((size_t)d.slot * 2u) * 3u + 2u].w & 0xffu;   // provider kind: low byte of the tx state's meta word
+        if (staged)
+            for (uint32_t w = 0; w <= SS_EXTRACT_EVENTS; w++) ev[w] = SX_PIPE_EMPTY;
     }
     {
         uint4 *dst = reinterpret_cast<uint4 *>(fast);   // the class codes follow the grammar table in both places
         for (uint32_t j = threadIdx.x; j < SX_FAST_BLOCK_BYTES / 16u; j += blockDim.x) dst[j] = fast_block[j];
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) PROBE_SET(0);
     __syncthreads();
-    if (!mine_to_do) return;
+    if (lane == 0) PROBE_MAX(6);
+    if (role == 3u) return;
+    if (!mine_to_do) {
+        if (verdicts && role == 2u) verdicts[c] = SS_ST_OK;   // nothing to extract: nothing to hold the seal back for
+        return;
+    }
+    if (role == 0u) {
+        if (staged) sx::fast_grammar(mine, mlen, fast, cls, stack, fl, trailer);
+        if (lane == 0) PROBE_MAX(4);
+        return;
+    }
+    if (role == 1u) {
+        if (staged) sx::fast_record(mlen, sx::fast_prefixed(mine, mlen), fl, trailer, ev, SS_EXTRACT_EVENTS);
+        if (lane == 0) PROBE_MAX(7);
+        return;
+    }
     const uint32_t cap = mlen < 16u ? 16u : ((mlen + 15u) & ~15u);
     sx::Result r;
     bool done = false;
     if (staged) {
         text = mine;
-        done = sx::extract_fast(mine, mlen, kind, delta_arena + d.in_off, cap, fast, cls,
-                                reinterpret_cast<uint32_t *>(mine + SS_EXTRACT_STAGE + 4u), SS_EXTRACT_EVENTS, &r);
+        done = sx::fast_bookkeep(mine, mlen, sx::fast_prefixed(mine, mlen), kind, delta_arena + d.in_off, cap, ev, trailer,
+                                 SS_EXTRACT_EVENTS, &r);
     }
     if (!done)
         r = sx::extract_chunk(text, mlen, kind, delta_arena + d.in_off, cap,
                               reinterpret_cast<const uint16_t *>(reinterpret_cast<const uint8_t *>(fast_block) + SX_FAST_BLOCK_BYTES));
-    status[i] = r.status;
+    if (!verdicts || r.status != SS_ST_OK) status[i] = r.status;
     delta[i].off = d.in_off;
     delta[i].len = r.len;
+    if (verdicts) verdicts[c] = r.status;
+    if (lane == 0) PROBE_MAX(1);
+}
+
+__global__ void __launch_bounds__(SS_EXTRACT_THREADS) ss_extract_kernel(const SsDesc *desc, uint32_t n, const uint8_t *in,
+                                                                       const uint4 *states, uint32_t *status,
+                                                                       symrelay_delta *delta, uint8_t *delta_arena,
+                                                                       const uint4 *fast_block) {
+    ss_pdl_launch_dependents();   // the batch's seal kernel may start beside this one (SS_ARG_VERDICT_LATE, ss_core.cuh)
+    const uint32_t warp = threadIdx.x >> 5;
+    // warps 2,3: grammar (the long chain; with one block per SM each has a scheduler to itself); 0,1: recording; 4,5: bookkeeping
+    ss_extract_block(desc, n, in, states, status, delta, delta_arena, fast_block, (warp & 2u) ? 0u : (warp < 2u ? 1u : 2u),
+                     warp & 1u, nullptr);
+}
+
+// Extractor and seal of one batch in ONE kernel, for batches whose frames all sit in thread tiles of 32 consecutive
+// descriptors (many chunks of one size class: BASELINE config 5).  A block takes 64 frames: six warps extract (three
+// roles x two groups of 32 chunks) and two warps seal the same 64 frames, one lane per frame, while the verdicts are
+// being worked out; a seal lane then polls its chunk's verdict word in shared memory and commits or takes the frame
+// back.  Two kernels side by side (SS_ARG_VERDICT_LATE) do the same in principle, but the block scheduler packs the
+// seal kernel's blocks onto the SMs the extractor left emptiest -- measured: the seal took 26 us instead of 13 -- here
+// every SM gets the same mix by construction.
+#define SS_FUSED_THREADS 256u
+#define SS_FUSED_SMEM (SS_EXTRACT_SMEM + SS_EXTRACT_CHUNKS * 4u)
+__global__ void __launch_bounds__(SS_FUSED_THREADS, 2) ss_extract_seal_kernel(SsArgs a, uint32_t n, symrelay_delta *delta,
+                                                                             uint8_t *delta_arena, const uint4 *fast_block) {
+    extern __shared__ __align__(16) uint8_t sx_smem[];
+    volatile uint32_t *verdicts = reinterpret_cast<volatile uint32_t *>(sx_smem + SS_EXTRACT_SMEM);
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, group = warp & 1u;
+    // warps 0,1: grammar; 2,3: seal; 4,5: recording; 6,7: bookkeeping -- per scheduler (warp % 4): a grammar warp with a
+    // recording warp (which mostly sleeps), a seal warp with a bookkeeping warp
+    const uint32_t role = warp < 2u ? 0u : (warp < 4u ? 3u : (warp < 6u ? 1u : 2u));
+    if (role == 3u) verdicts[group * 32u + lane] = SS_VERDICT_EMPTY;
+    ss_extract_block(a.desc, n, a.in, a.states, a.status, delta, delta_arena, fast_block, role, group, verdicts);
+    if (role != 3u) return;
+    const uint32_t first = blockIdx.x * SS_EXTRACT_CHUNKS + group * 32u;
+    if (first >= n) return;
+    SsTile tile;
+    tile.first = first;
+    tile.n_kind = (n - first < 32u ? n - first : 32u) | (1u << 17);
+    a.verdicts = verdicts + group * 32u;
+    ss_process_thread_tile<false, 2>(a, blockIdx.x * 2u + group, &tile);
 }
 
 
@@ -813,6 +908,7 @@ struct symrelay_ctx {
     bool defer_wb = true;   // SYMRELAY_DEFER=0: pipelined zero-copy batches write their results to the host themselves
     bool stage_input = true;       // SYMRELAY_STAGE=0: zero-copy batches read the arena lane by lane
     uint64_t inject_refusal = 0;   // SYMRELAY_INJECT_REFUSAL=k: the front end's k-th batch is refused (tests of the error path)
+    bool extract_fused = true;     // SYMRELAY_EXTRACT_FUSED=0: never the fused extract+seal kernel (two kernels, see extract_overlap)
     bool extract_overlap = true;   // SYMRELAY_EXTRACT_OVERLAP=0: the seal kernel of an extract batch starts only when the extractor is done
     uint32_t device_arg_flags = 0; // SYMRELAY_STAGE_DEV=1: also stage on the device-resident entry points (experiment)
     // SYMRELAY_PROF=1: where a host batch spends its time (printed by symrelay_destroy)
@@ -927,12 +1023,20 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
         ctx->launches++;
         arg_flags &= ~SS_ARG_INPUT_INDEPENDENT;   // the tile kernel now depends on the pre-pass
     }
+    // Every frame in a thread tile of 32 (the planner's choice for many small frames of one size class), nothing else in
+    // the batch: extractor and seal go into one kernel (ss_extract_seal_kernel), which cuts the descriptors into groups of
+    // 32 itself -- any frame can be a thread tile's lane, so the tile list is only the planner's opinion that this is the
+    // throughput shape.
+    const bool fused = d_delta && d_delta_arena && ctx->extract_fused && !d_run_nonce && !write_back && n_bulk == 0 &&
+                       n_tiles != 0 && (uint64_t)n_tiles * 32u == n;
+    const uint4 *fast_block = nullptr;   // the extractor tables of the GPU that owns this state table
     if (d_delta && d_delta_arena) {
-        const uint4 *fast_block = nullptr;   // the tables of the GPU that owns this state table
         for (int g = 0; g < ctx->n_gpus; g++)
             if (ctx->shard[g].d_states == d_states) fast_block = ctx->shard[g].d_sx_fast;
         if (!fast_block) return fail(ctx, SYMRELAY_EINVAL, "extract: no extractor tables for this state table");
-        ss_extract_kernel<<<(n + SS_EXTRACT_THREADS - 1) / SS_EXTRACT_THREADS, SS_EXTRACT_THREADS,
+    }
+    if (d_delta && d_delta_arena && !fused) {
+        ss_extract_kernel<<<(n + SS_EXTRACT_CHUNKS - 1) / SS_EXTRACT_CHUNKS, SS_EXTRACT_THREADS,
                             SS_EXTRACT_SMEM, stream>>>(
             reinterpret_cast<const SsDesc *>(d_desc), n, d_in, d_states, d_status, d_delta, d_delta_arena, fast_block);
         ctx->launches++;
@@ -945,6 +1049,16 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     a.status = d_status;
     a.flags = arg_flags;
     a.run_nonce = d_run_nonce;
+    if (fused) {
+        a.tiles = nullptr;
+        a.n_tiles = n_tiles;
+        a.flags &= ~(SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT);
+        ss_extract_seal_kernel<<<(n + SS_EXTRACT_CHUNKS - 1) / SS_EXTRACT_CHUNKS, SS_FUSED_THREADS, SS_FUSED_SMEM, stream>>>(
+            a, n, d_delta, d_delta_arena, fast_block);
+        ctx->launches++;
+        CU(ctx, cudaGetLastError());
+        return 0;
+    }
     // PDL only where it was measured to help: the host zero-copy path (16.2 -> 10.9 us per C2 batch).
     // Device-resident launches replayed from a CUDA graph got slower with it (6.3 -> 10.3 us).
     const bool pdl = ctx->pdl && (arg_flags & SS_ARG_INPUT_INDEPENDENT);
@@ -1154,6 +1268,11 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
         memcpy(sh.h_sx_fast.data(), fast.data(), SX_FAST_ENTRIES * sizeof(uint64_t));
         memcpy(sh.h_sx_fast.data() + SX_FAST_ENTRIES * sizeof(uint64_t), cls, 256);
         CU(ctx, cudaFuncSetAttribute(ss_extract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_EXTRACT_SMEM));
+        // Two of its blocks fill 190 KB of an SM; left to itself the runtime then configures 196 KB of shared memory and
+        // the seal kernel that is meant to run beside it (SS_ARG_VERDICT_LATE) finds no room for its 8 KB blocks.
+        CU(ctx, cudaFuncSetAttribute(ss_extract_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+        CU(ctx, cudaFuncSetAttribute(ss_extract_seal_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_FUSED_SMEM));
+        CU(ctx, cudaFuncSetAttribute(ss_extract_seal_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     }
     sh.init_cap = 4096;
     CU(ctx, cudaHostAlloc(&sh.h_init, sizeof(SsInitRec) * sh.init_cap, cudaHostAllocDefault));
@@ -1319,6 +1438,7 @@ symrelay_ctx *symrelay_create(const int *gpu_ids, int n_gpus, const symrelay_opt
     if (const char *m = getenv("SYMRELAY_PDL")) ctx->pdl = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE")) ctx->stage_input = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_EXTRACT_OVERLAP")) ctx->extract_overlap = atoi(m) != 0;
+    if (const char *m = getenv("SYMRELAY_EXTRACT_FUSED")) ctx->extract_fused = atoi(m) != 0;
     if (const char *m = getenv("SYMRELAY_STAGE_DEV")) ctx->device_arg_flags = atoi(m) ? (SS_ARG_STAGE_INPUT | SS_ARG_STAGE_OUTPUT) : 0u;
     ctx->n_gpus = n_gpus;
     for (int g = 0; g < n_gpus; g++) {

@@ -118,7 +118,7 @@ extern "C" uint32_t emu_extract(const uint8_t *text, uint32_t n, uint32_t kind, 
         if (!n_cls) { n_cls = sx::build_fast_tables(fast, cls); if (!n_cls) return 0xdeaeu; }
         if (n <= SX_FAST_MAX_LEN) {
             static std::vector<uint8_t> out3;
-            static uint32_t ev[SX_FAST_SCRATCH_WORDS(95u)];   // 95 events, as in the kernel
+            static uint32_t ev[SX_FAST_SCRATCH_WORDS_N(95u, SX_FAST_MAX_LEN)];   // 95 events, as in the kernel
             out3.assign((size_t)cap + 16, 0);
             sx::Result r3;
             emu_fast_calls++;
