@@ -94,6 +94,26 @@ SS_DEV void put_lit(Out &o, const char *s) {
 // decoded string === 'undefined' (src/utils.ts:46).
 SS_DEV bool decode_string(const uint8_t *t, uint32_t s, uint32_t e, Out &o) {
     const char *und = "undefined";
+    {
+        // Most deltas are a few plain ASCII characters: copy them as they are and only come back for the full decoder if
+        // a backslash or a byte >= 0x80 turns up (this loop is a fifth of the decoder's instructions per character, and
+        // the decoder sits at the very end of a chunk's critical path).
+        const uint32_t n0 = o.n;
+        const bool ov0 = o.overflow;
+        uint32_t j = s;
+        for (; j < e; j++) {
+            const uint32_t c = t[j];
+            if (c == 0x5c || c >= 0x80) break;
+            put(o, c);
+        }
+        if (j == e) {
+            if (e - s != 9u) return false;
+            bool is_und = true;
+            for (uint32_t q = 0; q < 9u; q++) is_und &= t[s + q] == (uint8_t)und[q];
+            return is_und;
+        }
+        o.n = n0; o.overflow = ov0;
+    }
     uint32_t um = 0;       // matched prefix length of "undefined", 0xff = mismatch
     uint32_t i = s;
     while (i < e) {
@@ -1016,7 +1036,13 @@ SS_DEV bool fast_bookkeep(const uint8_t *text, uint32_t n, bool prefixed, uint32
     if (!prefixed && state == Q_CUT) return false;                       // no split without the prefix: parse it all
     const bool parsed = state == Q_AFTER_T || (prefixed && state == Q_DONE);   // Q_AFTER_T is only reachable outside every container
     if (!parsed) book_init(b);
+#ifdef SS_PROBE_TIMELINE
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(13);
+#endif
     *res = finish(text, parsed, false, b.tr, kind, out, cap);
+#ifdef SS_PROBE_TIMELINE
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(14);
+#endif
     return true;
 }
 

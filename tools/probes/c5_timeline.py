@@ -42,7 +42,7 @@ for step in range(6):
     t0 = out[0]
     names = {6: "extract: last block past its set-up", 4: "extract: last grammar warp done", 7: "extract: last recording warp done",
              10: "extract: bookkeeping has event 0", 11: "extract: bookkeeping has event 10", 12: "extract: bookkeeping has event 20",
-             9: "extract: bookkeeping saw the end of the list", 1: "extract: last bookkeeping warp done", 2: "seal: tile 0 starts", 8: "seal: last tile starts",
+             9: "extract: bookkeeping saw the end of the list", 13: "extract: before finish()", 14: "extract: after finish()", 1: "extract: last bookkeeping warp done", 2: "seal: tile 0 starts", 8: "seal: last tile starts",
              5: "seal: last tile done computing", 3: "seal: last tile done"}
     print(f"step {step} (mean chunk {np.mean(lens):.0f} B):")
     for k, v in names.items():
