@@ -1165,6 +1165,7 @@ SS_DEV void ss_process_thread_tile(const SsArgs &a, uint32_t tile_idx, const SsT
             ss_pdl_wait();   // the extractor has finished: its status words are visible
             if (wants_verdict) verdict = *reinterpret_cast<const volatile uint32_t *>(a.status + frame_idx);
         }
+        if (LATE == 2 && verdict == SS_VERDICT_EMPTY) a.status[frame_idx] = SS_ST_RETRY;   // (never seen: the bookkeeping thread always delivers)
         if (verdict != SS_ST_OK) {
             // refused (the reference throws before peer.write, or the host must extract): the stream state stays as it
             // was, the status word is the extractor's, and the wire bytes sealed ahead of the verdict are wiped

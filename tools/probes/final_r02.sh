@@ -7,7 +7,8 @@ python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/r02_bench_re
 python bench.py > gpurun_out/r02_bench_default_long.json 2>> gpurun_out/f1.err
 python bench.py --workload c1 > gpurun_out/r02_bench_c1.json 2>> gpurun_out/f1.err
 python bench.py --workload c5 > gpurun_out/r02_bench_c5.json 2>> gpurun_out/f1.err
-SYMRELAY_EXTRACT_OVERLAP=0 python bench.py --workload c5 > gpurun_out/r02_bench_c5_no_overlap.json 2>> gpurun_out/f1.err
+SYMRELAY_EXTRACT_FUSED=0 python bench.py --workload c5 > gpurun_out/r02_bench_c5_two_kernels.json 2>> gpurun_out/f1.err
+SYMRELAY_EXTRACT_FUSED=0 SYMRELAY_EXTRACT_OVERLAP=0 python bench.py --workload c5 > gpurun_out/r02_bench_c5_no_overlap.json 2>> gpurun_out/f1.err
 python bench.py --workload c4sweep > gpurun_out/r02_bench_c4sweep.json 2>> gpurun_out/f1.err
 python bench.py --workload c3 --no-latency --no-cpu > gpurun_out/r02_bench_c3.json 2>> gpurun_out/f1.err
 BENCH_C3_SHARD_OF=8 python bench.py --workload c3 --no-latency --no-cpu > gpurun_out/r02_bench_c3_one_eighth.json 2>> gpurun_out/f1.err
@@ -27,10 +28,17 @@ ncu --set full --clock-control none --cache-control none --import-source on -k r
 ncu --set full --clock-control none --cache-control none --import-source on -k regex:ss_thread_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r02_c3_thread $B --workload c3 --steps 10 --warmup 3 > gpurun_out/ncu_c3t.log 2>&1
 ncu --set full --clock-control none --cache-control none --import-source on -k regex:ss_strided_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r02_c3_strided $B --workload c3 --steps 10 --warmup 3 > gpurun_out/ncu_c3s.log 2>&1
 ncu --set full --clock-control none --cache-control none --import-source on -k regex:ss_bulk_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r02_c3_bulk $B --workload c3 --steps 10 --warmup 3 > gpurun_out/ncu_c3b.log 2>&1
-ncu --set full --clock-control none --cache-control none --import-source on -k regex:ss_extract_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r02_c5_extract $B --workload c5 --steps 10 --warmup 3 > gpurun_out/ncu_c5e.log 2>&1
+ncu --set full --clock-control none --cache-control none --import-source on -k regex:ss_extract_seal_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r02_c5_extract_seal $B --workload c5 --steps 10 --warmup 3 > gpurun_out/ncu_c5f.log 2>&1
+SYMRELAY_EXTRACT_FUSED=0 SYMRELAY_EXTRACT_OVERLAP=0 ncu --set full --clock-control none --cache-control none --import-source on -k regex:ss_extract_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r02_c5_extract $B --workload c5 --steps 10 --warmup 3 > gpurun_out/ncu_c5e.log 2>&1
+SYMRELAY_EXTRACT_FUSED=0 SYMRELAY_EXTRACT_OVERLAP=0 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none -c 60 --csv --log-file gpurun_out/r02_c5_two_kernels_launches.csv $B --workload c5 --steps 10 --warmup 3 > gpurun_out/ncu_c5l2.log 2>&1
 BENCH_C3_SHARD_OF=8 ncu --set full --clock-control none --cache-control none --import-source on -k regex:ss_wide_kernel --launch-skip 6 --launch-count 1 -o gpurun_out/r02_c3_one_eighth_wide $B --workload c3 --steps 10 --warmup 3 > gpurun_out/ncu_c3w.log 2>&1
-for f in r02_c2_packed r02_c4_bulk r02_c3_thread r02_c3_strided r02_c3_bulk r02_c5_extract r02_c3_one_eighth_wide; do
+for f in r02_c2_packed r02_c4_bulk r02_c3_thread r02_c3_strided r02_c3_bulk r02_c5_extract r02_c5_extract_seal r02_c3_one_eighth_wide; do
   ncu -i gpurun_out/$f.ncu-rep --page details > gpurun_out/${f}_ncu_full.txt 2>&1
   ncu -i gpurun_out/$f.ncu-rep --page raw --csv > gpurun_out/${f}_raw.csv 2>&1
 done
+ncu -i gpurun_out/r02_c2_packed.ncu-rep --page source --csv --print-source sass > gpurun_out/r02_c2_packed_source.csv 2>&1
 ls -la gpurun_out/*.ncu-rep
+python -c "from symmetry_b200 import build; build.build(force=True, extra=['-DSS_PROBE_TIMELINE'], out='/root/repo/symmetry_b200/libsymrelay_probe.so')" > /dev/null 2>&1
+SYMRELAY_SO=symmetry_b200/libsymrelay_probe.so python tools/probes/c5_timeline.py > gpurun_out/r02_c5_timeline_fused.txt 2>&1
+SYMRELAY_EXTRACT_FUSED=0 SYMRELAY_SO=symmetry_b200/libsymrelay_probe.so python tools/probes/c5_timeline.py > gpurun_out/r02_c5_timeline_two_kernels.txt 2>&1
+rm -f symmetry_b200/libsymrelay_probe.so
