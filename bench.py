@@ -961,10 +961,11 @@ def run_c5(args):
         "gb_per_s": mean_len * n * steps / (ms * 1e-3) / 1e9,
         "roofline": {"bound": "hbm", "achieved": alg_bytes / (per_step * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                      "frac": alg_bytes / (per_step * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": hbm_src,
-                     "kernel": "ss_extract_kernel + ss_packed_kernel (whole step)",
+                     "kernel": ("ss_extract_seal_kernel (extractor and seal in one kernel)" if per_lap == R else
+                                "ss_extract_kernel + ss_packed_kernel (whole step)"),
                      "algorithmic_bytes_per_step": alg_bytes,
                      "note": "2*mlen+92 bytes per frame (SURVEY 8(d)); the step is bound by the extractor's serial "
-                             "per-chunk instruction stream, see alu_roofline and DESIGN.md 4.1"},
+                             "per-chunk instruction streams, see alu_roofline and DESIGN.md 4.6"},
         "alu_roofline": {"bound": "int_alu", "achieved": ops / (per_step * 1e-3) / 1e12, "peak": arx, "unit": "Tint-op/s",
                          "frac": ops / (per_step * 1e-3) / 1e12 / arx},
         "gpu_launches": reps * per_lap, "launches_per_step": per_lap / R, "clocks": clk,
