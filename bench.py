@@ -2,7 +2,7 @@
 """bench.py -- batched secretstream seal+open throughput on B200(s).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c1|c3|c4|c5|c4sweep]
-                    [--impl ours|reference] [--sub c4,c3|none]
+                    [--impl ours|reference] [--sub c4,c3,c5|none]
 
 A "step" is one pass of the relay hot path over one batch: every stream seals
 one outbound frame AND opens one inbound frame (one mixed batch = one kernel
@@ -39,7 +39,7 @@ L2_BYTES = 126 << 20
 METRIC = "sealed_frames_per_sec"
 GATE_CYCLES = 400_000                       # ~200 us at 1.965 GHz: the spin kernel ahead of the device-timed region
 DEFAULT_STEPS = {"c2": 20000, "c3": 200, "c4": 64, "c5": 360, "c1": 20, "c4sweep": 8}
-SUB_STEPS = {"c4": 64, "c3": 200}          # steps of the sub-lines riding on the default line
+SUB_STEPS = {"c4": 64, "c3": 200, "c5": 360}          # steps of the sub-lines riding on the default line
 
 
 # ------------------------------------------------------------------ workload --
@@ -746,7 +746,7 @@ def run_ours(args):
     # ---------------- sub-lines: the other single-kernel claims, measured in this same run ----------
     subs = {}
     for sub in ([] if args.sub in ("", "none") else args.sub.split(",")):
-        if sub == name:
+        if sub == name or sub == "c5":   # (c5 is one GPU's figure: rank 0 measures it below)
             continue
         r, _ = measure_device(job, sub, SUB_STEPS.get(sub, 32), max(3, min(W, 8)), args.no_graph)
         r["config"] = make_config(sub, job.n_gpus, r["steps"], args.no_graph, plan_mode_for(sub))
@@ -792,6 +792,13 @@ def run_ours(args):
             udp = udp_bench.run(frames=2 * n if name == "c2" else 2048, nbytes=84, batches=60)
         except Exception as e:
             udp = {"error": repr(e)}
+
+    # ---------------- BASELINE config 5 (extract + seal fused), one GPU's figure, rank 0 ----------
+    if "c5" in ([] if args.sub in ("", "none") else args.sub.split(",")) and name != "c5":
+        try:
+            subs["c5"] = c5_line(SUB_STEPS["c5"], 5)
+        except Exception as e:
+            subs["c5"] = {"error": repr(e)}
 
     h2d = lay.in_bytes + 2 * n * 16 + x["n_tiles_full"] * 8
     d2h = lay.out_bytes + 2 * n * 4
@@ -845,8 +852,12 @@ def hbm_peak_gbs():
 
 # ------------------------------------------------------------------------- c5 --
 def run_c5(args):
+    print(json.dumps(c5_line(args.steps, args.warmup)), flush=True)
+
+
+def c5_line(K: int, W: int) -> dict:
     """configs[4]: fused relay -- per batch one synthetic chat-completion chunk per stream:
-    prefix test + JSON validation + delta extraction + seal (device-resident)."""
+    prefix test + JSON validation + delta extraction + seal (device-resident).  One GPU (the current device's figure)."""
     import torch
 
     import batch_util as bu
@@ -858,7 +869,6 @@ def run_c5(args):
     torch.cuda.set_device(0)
     dev = torch.device("cuda:0")
     n, n_kinds = int(os.environ.get("BENCH_C5_STREAMS", "16384")), 16   # configs[4] says 16k; the env knob is for the batch-size note in DESIGN.md
-    K, W = args.steps, args.warmup
     relay = sb.SymRelay(gpu_ids=(0,), max_streams=2 * n)
     keys, hdrs = synth.stream_keys(n)
     slots = relay.open_streams(keys, hdrs, None, None, provider=sb.PROVIDER_OLLAMA)
@@ -971,8 +981,8 @@ def run_c5(args):
         "gpu_launches": reps * per_lap, "launches_per_step": per_lap / R, "clocks": clk,
         "parity": "deltas == oracle/extract.py on sampled frames of every ring slot; chains == libsodium",
     }
-    print(json.dumps(line), flush=True)
     relay.close()
+    return line
 
 
 def main():
@@ -982,7 +992,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=200)
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--sub", default=None, help="sub-lines carried by the default (c2) line: 'c4,c3' (default) or 'none'")
+    ap.add_argument("--sub", default=None, help="sub-lines carried by the default (c2) line: 'c4,c3,c5' (default) or 'none'")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-latency", action="store_true", help="skip the p50 added-latency leg (64k streams, Poisson)")
@@ -995,7 +1005,7 @@ def main():
     if args.steps is None:   # a step of c3/c4/c5 is 10-400x a step of c2
         args.steps = DEFAULT_STEPS.get(args.workload, 20000)
     if args.sub is None:
-        args.sub = "c4,c3" if args.workload == "c2" else "none"
+        args.sub = "c4,c3,c5" if args.workload == "c2" else "none"
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":
