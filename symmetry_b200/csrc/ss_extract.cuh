@@ -94,26 +94,8 @@ SS_DEV void put_lit(Out &o, const char *s) {
 // decoded string === 'undefined' (src/utils.ts:46).
 SS_DEV bool decode_string(const uint8_t *t, uint32_t s, uint32_t e, Out &o) {
     const char *und = "undefined";
-    {
-        // Most deltas are a few plain ASCII characters: copy them as they are and only come back for the full decoder if
-        // a backslash or a byte >= 0x80 turns up (this loop is a fifth of the decoder's instructions per character, and
-        // the decoder sits at the very end of a chunk's critical path).
-        const uint32_t n0 = o.n;
-        const bool ov0 = o.overflow;
-        uint32_t j = s;
-        for (; j < e; j++) {
-            const uint32_t c = t[j];
-            if (c == 0x5c || c >= 0x80) break;
-            put(o, c);
-        }
-        if (j == e) {
-            if (e - s != 9u) return false;
-            bool is_und = true;
-            for (uint32_t q = 0; q < 9u; q++) is_und &= t[s + q] == (uint8_t)und[q];
-            return is_und;
-        }
-        o.n = n0; o.overflow = ov0;
-    }
+    // (A separate copy loop for plain ASCII deltas was measured and dropped: among the 32 chunks of a warp one nearly
+    // always holds an escape or a multi-byte character, so the warp ran both loops: config 5 24.8 -> 25.1 us.)
     uint32_t um = 0;       // matched prefix length of "undefined", 0xff = mismatch
     uint32_t i = s;
     while (i < e) {
