@@ -54,7 +54,10 @@ extern "C" {
 /* per-frame status word written by the kernels: bits 0..7 code, bits 8..15 opened tag */
 #define SYMRELAY_ST_OK 0u
 #define SYMRELAY_ST_BAD_MAC 1u            /* pull returned -1: that slot's state is untouched; no plaintext is released
-                                             (the frame's output bytes are left untouched or zeroed) */
+                                             (the frame's output bytes are left untouched or zeroed; the host batch calls
+                                             never let unauthenticated plaintext reach the caller's memory, the
+                                             device-resident entry points may write a big frame's plaintext to the
+                                             caller's HBM buffer and wipe it before the kernel ends) */
 #define SYMRELAY_ST_TOO_SHORT 2u          /* wire frame shorter than 17 bytes after the prefix */
 #define SYMRELAY_ST_EXTRACT_THROW 3u      /* the reference would throw a TypeError here (utils.ts:38-50) */
 #define SYMRELAY_ST_EXTRACT_UNSUPPORTED 4u /* value shape outside the GPU extractor's domain: use the JS helper */

@@ -2121,7 +2121,11 @@ static int64_t submit_locked(symrelay_ctx *ctx, int gpu_index, const symrelay_de
     // payload straight from pinned host memory over PCIe and writes wire bytes and status straight back
     // -- no staging copies, a third of the driver calls, and a much shorter path for latency.  Larger
     // batches keep the DMA pipeline below (copy engines overlap the kernels of neighbouring batches).
-    const bool zero_copy = in_bytes + out_bytes <= ctx->zero_copy_max && is_library_pinned(ctx, in, in_bytes) &&
+    // (Not for inbound frames of more than 384 bytes: strided, bulk and wide tiles decrypt in the same pass as the MAC
+    // and wipe a forged frame afterwards -- in device memory nobody sees the interval, in the caller's host memory the
+    // application could.  Such batches are staged: their results are copied out after the kernel has finished.)
+    const bool spec_open = n_bulk != 0 && (any_flags & SYMRELAY_F_OPEN) != 0;
+    const bool zero_copy = !spec_open && in_bytes + out_bytes <= ctx->zero_copy_max && is_library_pinned(ctx, in, in_bytes) &&
                            is_library_pinned(ctx, out, out_bytes) &&
                            (!extract || is_library_pinned(ctx, delta_arena, in_bytes < delta_arena_bytes ? in_bytes : delta_arena_bytes));
     if (zero_copy && ctx->persist && n_bulk == 0 && !extract && !runs && n_tiles > 0 && sh.stages.size() <= PK_RING) {
