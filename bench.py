@@ -592,6 +592,38 @@ def pcie_peaks(job: Job):
     return nbytes / (best[0] * 1e-3) / 1e9, nbytes / (best[1] * 1e-3) / 1e9
 
 
+def pcie_concurrent(job: Job):
+    """What the box's host-memory/PCIe path gives when EVERY rank copies in BOTH directions at once (copy engines, pinned
+    64 MiB buffers, two streams per GPU, ranks released together): per-rank GB/s each way and the sum over ranks.  This is
+    the ceiling the N-GPU end-to-end number lives under; the one-at-a-time peaks of pcie_peaks() are not."""
+    torch = job.torch
+    nbytes, reps = 64 << 20, 4
+    h_in = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    d_in = torch.empty(nbytes, dtype=torch.uint8, device=job.dev)
+    d_out = torch.empty(nbytes, dtype=torch.uint8, device=job.dev)
+    s_up, s_down = torch.cuda.Stream(device=job.dev), torch.cuda.Stream(device=job.dev)
+    for timed in (False, True):
+        job.barrier()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        with torch.cuda.stream(s_up):
+            ev[0].record()
+            for _ in range(reps):
+                d_in.copy_(h_in, non_blocking=True)
+            ev[1].record()
+        with torch.cuda.stream(s_down):
+            ev[2].record()
+            for _ in range(reps):
+                h_out.copy_(d_out, non_blocking=True)
+            ev[3].record()
+        torch.cuda.synchronize()
+    up = nbytes * reps / (ev[0].elapsed_time(ev[1]) * 1e-3) / 1e9
+    down = nbytes * reps / (ev[2].elapsed_time(ev[3]) * 1e-3) / 1e9
+    return {"h2d_gbs_this_rank": up, "d2h_gbs_this_rank": down,
+            "h2d_gbs_all_ranks": job.sum_over_ranks(up), "d2h_gbs_all_ranks": job.sum_over_ranks(down),
+            "what": "pinned 64 MiB cudaMemcpyAsync in both directions at once on every rank, ranks released together"}
+
+
 def run_ours(args):
     import symmetry_b200 as sb
     from oracle import libsodium as ls
@@ -742,6 +774,7 @@ def run_ours(args):
     relay.close()
     relay = None
     h2d_peak, d2h_peak = pcie_peaks(job)
+    pcie_all = pcie_concurrent(job)
 
     # ---------------- sub-lines: the other single-kernel claims, measured in this same run ----------
     subs = {}
@@ -815,6 +848,10 @@ def run_ours(args):
                            "h2d_peak_gbs": h2d_peak, "d2h_peak_gbs": d2h_peak,
                            "peak_source": "pinned 64 MiB cudaMemcpyAsync each way, measured in this run; peak = both "
                                           "directions' bytes over the slower direction's time at its peak (full duplex)"}
+    if K2:
+        # the same traffic against what the box gives when all N ranks copy both ways at once (the N-GPU ceiling)
+        t_all = max(h2d / (pcie_all["h2d_gbs_this_rank"] * 1e9), d2h / (pcie_all["d2h_gbs_this_rank"] * 1e9))
+        e2e["roofline"]["all_ranks_copying"] = dict(pcie_all, frac=t_all / (e2e_ms * 1e-3))
     if batch_lat:
         e2e["batch_latency"] = batch_lat
     if general:
