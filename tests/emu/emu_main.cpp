@@ -11,6 +11,7 @@
 #include "../../symmetry_b200/csrc/ss_runs.cuh"
 
 #include <cstring>
+#include <thread>
 #include <vector>
 
 static uint32_t emu_arg_flags = 0;   // SsArgs.flags for the next batches (tests flip SS_ARG_STAGE_INPUT)
@@ -128,6 +129,33 @@ extern "C" uint32_t emu_extract(const uint8_t *text, uint32_t n, uint32_t kind, 
                     return 0xdeafu;
                 for (uint32_t i = cap; i < cap + 16; i++) if (out3[i]) return 0xdeb0u;
             }
+        }
+    }
+    {
+        // ... and the same three roles as the GPU runs them: three threads at once, queues pre-filled with the "empty"
+        // pattern, each consumer polling for its next word (real interleavings of the hand-over, on CPU threads)
+        static uint64_t fast2[SX_FAST_ENTRIES];
+        static uint8_t cls2[256];
+        static bool built2 = false;
+        if (!built2) { if (!sx::build_fast_tables(fast2, cls2)) return 0xdeb1u; built2 = true; }
+        if (n <= 384u) {   // the kernel stages chunks up to this size
+            static std::vector<uint8_t> out4;
+            out4.assign((size_t)cap + 16, 0);
+            static uint32_t scratch[SX_FAST_SCRATCH_WORDS_N(95u, 384u)];
+            uint32_t *stack = scratch, *trailer = scratch + SX_FAST_STACK_WORDS, *fl = trailer + 1u,
+                     *evq = fl + SX_FAST_FLAG_WORDS(n);
+            *trailer = SX_PIPE_EMPTY;
+            for (uint32_t w = 0; w < SX_FAST_FLAG_WORDS(n); w++) fl[w] = SX_PIPE_EMPTY;
+            for (uint32_t w = 0; w <= 95u; w++) evq[w] = SX_PIPE_EMPTY;
+            const bool prefixed = sx::fast_prefixed(al, n);
+            sx::Result r4;
+            bool done4 = false;
+            std::thread ta([&] { sx::fast_grammar(al, n, fast2, cls2, stack, fl, trailer); });
+            std::thread tb([&] { sx::fast_record(n, prefixed, fl, trailer, evq, 95u); });
+            std::thread tc([&] { done4 = sx::fast_bookkeep(al, n, prefixed, kind, out4.data(), cap, evq, trailer, 95u, &r4); });
+            ta.join(); tb.join(); tc.join();
+            if (done4 && (r4.status != r.status || r4.len != r.len || (r.status == 0 && memcmp(out4.data(), out, r.len < cap ? r.len : cap))))
+                return 0xdeb2u;
         }
     }
     *len_out = r.len;
