@@ -278,12 +278,13 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
     uint64_t n_tiles = 0;
     uint32_t n_strided = 0;
     uint32_t sbase[32], scount[32];   // per bucket: the part that becomes strided tiles (second pass, bulk class)
-    for (uint32_t b = 0; b < 32u; b++) {
-        base[b] = at;
-        uint32_t m = count[b], s = at;
-        at += m;
-        sbase[b] = 0; scount[b] = 0;
-        if (b == 31u) break;   // bulk tiles are appended after every packed tile
+    for (uint32_t b = 0; b < 32u; b++) { base[b] = at; at += count[b]; sbase[b] = 0; scount[b] = 0; }
+    // Tiles are emitted with the LONGEST first (six-block frames before two-block ones): the tile list's order is the
+    // order in which warps are started, a batch of this size needs about two rounds of resident warps, and whatever
+    // starts in the second round decides when the step ends -- with the short tiles there it ends sooner (BASELINE
+    // config 3, measured with the timeline probe: the six-block thread tiles started at 30 us and ended at 61).
+    for (uint32_t b = 31u; b-- > 0u;) {   // (bucket 31 = bulk tiles: appended after every small tile, below)
+        uint32_t m = count[b], s = base[b];
         const uint32_t c = b + 2u;
         const bool threads = thread_ok && (c <= SYMRELAY_THREAD_TILE_MAX_BLOCKS || m >= SYMRELAY_THREAD_TILE_BIG_BUCKET);
         if (!threads && c > SYMRELAY_THREAD_TILE_MAX_BLOCKS) { sbase[b] = s; scount[b] = m; continue; }
@@ -302,7 +303,7 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
             m -= k; s += k;
         }
     }
-    for (uint32_t b = 0; b < 31u; b++) {
+    for (uint32_t b = 31u; b-- > 0u;) {
         const uint32_t c = b + 2u, k = symrelay_seg_lanes(c), per_s = 32u / k;
         for (uint32_t m = scount[b], s = sbase[b]; m; ) {
             const uint32_t cnt = m < per_s ? m : per_s;
