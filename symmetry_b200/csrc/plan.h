@@ -28,7 +28,9 @@ static inline int symrelay_desc_check_inline(const symrelay_desc *d) {
 #define SYMRELAY_THREAD_TILE_MIN_FRAMES 8192u /* batches smaller than this are latency-bound: packed tiles only */
 #endif
 #ifndef SYMRELAY_THREAD_TILE_MAX_BLOCKS
+#ifndef SYMRELAY_THREAD_TILE_MAX_BLOCKS
 #define SYMRELAY_THREAD_TILE_MAX_BLOCKS 6u   /* frames of up to 4 payload blocks (256 B) */
+#endif
 #endif
 
 // Strided tiles (bit 16 of n_kind, bits 24..29 = lanes per frame): frames of 7..32 blocks (385 B .. 1,920 B) whose bucket
@@ -55,8 +57,9 @@ static inline uint32_t symrelay_seg_lanes(uint32_t nc) {
  * look for wide tiles; with this cap they know from the descriptor count alone when the wide kernel has nothing to do. */
 #define SYMRELAY_WIDE_MAX_BATCH_FRAMES 32768u
 static inline bool symrelay_wide_ok(uint32_t n_big, uint64_t batch_blocks, uint32_t n_frames) {
-    static const bool off = getenv("SYMRELAY_WIDE") && atoi(getenv("SYMRELAY_WIDE")) == 0;   // kill switch (measurements)
-    return !off && n_big != 0u && n_big <= SYMRELAY_WIDE_MAX_FRAMES && batch_blocks < SYMRELAY_WIDE_MAX_BATCH_BLOCKS &&
+    static const int mode = getenv("SYMRELAY_WIDE") ? atoi(getenv("SYMRELAY_WIDE")) : 1;   // 0: never (kill switch); 2: whatever the batch size (measurements)
+    if (mode == 2) return n_big != 0u && n_big <= SYMRELAY_WIDE_MAX_FRAMES;
+    return mode != 0 && n_big != 0u && n_big <= SYMRELAY_WIDE_MAX_FRAMES && batch_blocks < SYMRELAY_WIDE_MAX_BATCH_BLOCKS &&
            n_frames <= SYMRELAY_WIDE_MAX_BATCH_FRAMES;
 }
 #define SYMRELAY_THREAD_TILE_HUGE_BATCH 98304u  /* a uniform batch of BIG frames with this many of them (3,072 warps: ~20 per SM) does too */

@@ -1071,7 +1071,8 @@ static int launch_tiles(symrelay_ctx *ctx, const symrelay_desc *d_desc, uint32_t
     //   packed tiles of a large batch                                      -> side stream 3
     const bool big = n_packed > 148u * 8u && !write_back;   // large batch: split the small tiles by kind (see ss_thread_kernel)
     bool has_thread = n_packed != 0, has_packed = big, has_strided = n_bulk != 0, has_bulk = n_bulk != 0,
-         has_wide = n_bulk != 0 && n <= SYMRELAY_WIDE_MAX_BATCH_FRAMES;   // (the planner forms no wide tiles in larger batches)
+         has_wide = n_bulk != 0 && (n <= SYMRELAY_WIDE_MAX_BATCH_FRAMES ||   // (the planner forms no wide tiles in larger batches ...
+                                    (getenv("SYMRELAY_WIDE") && atoi(getenv("SYMRELAY_WIDE")) == 2));   // ... unless told to, for measurements)
     uint32_t wide_lo = 0, wide_hi = n_bulk;   // the range of bulk-class tiles the wide kernel is launched over
     if (host_tiles) {   // the tile list is in host memory: launch only what is there
         has_strided = has_bulk = has_wide = false;
