@@ -30,13 +30,13 @@
 #include "../../include/symrelay.h"
 #include "plan.h"
 #ifdef SS_PROBE_TIMELINE   // measurement builds only (tools/probes/c5_timeline.py): when do the two kernels of an extract batch run?
-__device__ unsigned long long g_probe[16];
+__device__ unsigned long long g_probe[32];
 __device__ __forceinline__ unsigned long long probe_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #define PROBE_SET(i) (g_probe[i] = probe_now())
 #define PROBE_MAX(i) atomicMax(&g_probe[i], probe_now())
 extern "C" __attribute__((visibility("default"))) int symrelay_probe_timeline(unsigned long long *out, int reset) {
     if (out && cudaMemcpyFromSymbol(out, g_probe, sizeof(g_probe)) != cudaSuccess) return -1;
-    if (reset) { unsigned long long z[16] = {0}; if (cudaMemcpyToSymbol(g_probe, z, sizeof(z)) != cudaSuccess) return -1; }
+    if (reset) { unsigned long long z[32] = {0}; if (cudaMemcpyToSymbol(g_probe, z, sizeof(z)) != cudaSuccess) return -1; }
     return 0;
 }
 #else
@@ -74,7 +74,9 @@ __global__ void __launch_bounds__(128, SS_THREAD_MIN_BLOCKS) ss_thread_kernel(Ss
     if (warp >= a.n_tiles) return;
     const SsTile tile = a.tiles[warp];
     if (!(tile.n_kind & (1u << 17))) return;
+    if ((threadIdx.x & 31u) == 0u) { if (warp == 0) PROBE_SET(22); PROBE_MAX(28); }   // (tools/probes/c3_timeline.py)
     ss_process_thread_tile(a, warp, &tile);
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(23);
 }
 // ... and the form for batches with an extractor pass (SS_ARG_VERDICT_LATE, ss_core.cuh)
 __global__ void __launch_bounds__(128, SS_THREAD_MIN_BLOCKS) ss_thread_late_kernel(SsArgs a) {
@@ -89,7 +91,9 @@ __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_only_kern
     if (warp >= a.n_tiles) return;
     const SsTile tile = a.tiles[warp];
     if (tile.n_kind & (1u << 17)) return;
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(20);
     ss_process_tile<false>(a, warp, &tile);
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(21);
 }
 
 // The same kernel for small host batches: the tile list rides in the launch parameters (constant bank), so a
@@ -117,7 +121,9 @@ __global__ void __launch_bounds__(128, SS_BULK_MIN_BLOCKS) ss_bulk_kernel(SsArgs
     if (warp >= a.n_tiles) return;
     const SsTile tile = a.tiles[warp];
     if (((tile.n_kind >> 24) & 63u) || (tile.n_kind & (1u << 18))) return;   // a strided or a wide tile: another kernel's
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(29);
     ss_process_tile<true>(a, warp, &tile);
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(27);
 }
 
 // Wide tiles (plan.h): one frame of more than 8 KiB per 128-thread BLOCK, for batches that hold only a few of them and
@@ -142,7 +148,9 @@ __global__ void __launch_bounds__(128, 4) ss_strided_kernel(SsArgs a) {
     if (warp >= a.n_tiles) return;
     const SsTile tile = a.tiles[warp];
     if (!((tile.n_kind >> 24) & 63u)) return;
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(30);
     ss_process_tile<true, false, true>(a, warp, &tile);
+    if ((threadIdx.x & 31u) == 0u) PROBE_MAX(25);
 }
 
 // Posts a deferred batch's results to the caller's host memory when no later batch carries them.
@@ -1274,6 +1282,20 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
         CU(ctx, cudaFuncSetAttribute(ss_extract_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
         CU(ctx, cudaFuncSetAttribute(ss_extract_seal_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_FUSED_SMEM));
         CU(ctx, cudaFuncSetAttribute(ss_extract_seal_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+        // The tile kernels of one batch run side by side on the same SMs, and an SM keeps one shared-memory configuration
+        // for everything resident on it.  Left to the runtime each kernel asks for its own (0 KB for thread tiles, ~100 KB
+        // for seven blocks of bulk tiles ...) and which SMs can take which kernel then depends on what ran before:
+        // BASELINE config 3 took 58 us on a fresh context and 63 us right behind config 4.  One common configuration that
+        // is large enough for all of them makes every SM eligible for every kind.
+        if (!getenv("SYMRELAY_CARVEOUT") || atoi(getenv("SYMRELAY_CARVEOUT")) != 0) {
+            const int pct = getenv("SYMRELAY_CARVEOUT") ? atoi(getenv("SYMRELAY_CARVEOUT")) : 40;   // 100 KB: seven blocks of bulk tiles; measured 40/50/75/100 %: 57.8/57.9/58.1/58.9 us
+            CU(ctx, cudaFuncSetAttribute(ss_packed_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            CU(ctx, cudaFuncSetAttribute(ss_packed_only_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            CU(ctx, cudaFuncSetAttribute(ss_thread_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            CU(ctx, cudaFuncSetAttribute(ss_strided_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            CU(ctx, cudaFuncSetAttribute(ss_bulk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            CU(ctx, cudaFuncSetAttribute(ss_wide_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        }
     }
     sh.init_cap = 4096;
     CU(ctx, cudaHostAlloc(&sh.h_init, sizeof(SsInitRec) * sh.init_cap, cudaHostAllocDefault));
