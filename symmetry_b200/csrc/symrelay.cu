@@ -67,7 +67,8 @@ __global__ void __launch_bounds__(128, SS_PACKED_MIN_BLOCKS) ss_packed_kernel(Ss
 // only its own kind): the thread-per-frame path needs far fewer registers than the packed one, and BASELINE config 3 is
 // 3,750 thread tiles that want to be resident all at once.
 #ifndef SS_THREAD_MIN_BLOCKS
-#define SS_THREAD_MIN_BLOCKS 6
+#define SS_THREAD_MIN_BLOCKS 5   // 90 registers, no spills, 20 warps per SM.  Measured on config 3 / the 512 B and 4 KiB points of the size
+                                 // sweep: 4 -> 59.3 us; 5 -> 57.2 us, 88.9 %, 87.4 %; 6 (80 registers) -> 57.9 us, 87.6 %, 85.7 %; 7 (72, spills) -> 60.9 us
 #endif
 __global__ void __launch_bounds__(128, SS_THREAD_MIN_BLOCKS) ss_thread_kernel(SsArgs a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -1289,12 +1290,16 @@ static int shard_init(symrelay_ctx *ctx, Shard &sh, int dev) {
         // is large enough for all of them makes every SM eligible for every kind.
         if (!getenv("SYMRELAY_CARVEOUT") || atoi(getenv("SYMRELAY_CARVEOUT")) != 0) {
             const int pct = getenv("SYMRELAY_CARVEOUT") ? atoi(getenv("SYMRELAY_CARVEOUT")) : 40;   // 100 KB: seven blocks of bulk tiles; measured 40/50/75/100 %: 57.8/57.9/58.1/58.9 us
-            CU(ctx, cudaFuncSetAttribute(ss_packed_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-            CU(ctx, cudaFuncSetAttribute(ss_packed_only_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-            CU(ctx, cudaFuncSetAttribute(ss_thread_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-            CU(ctx, cudaFuncSetAttribute(ss_strided_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-            CU(ctx, cudaFuncSetAttribute(ss_bulk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-            CU(ctx, cudaFuncSetAttribute(ss_wide_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            // (bit per kernel, measurements.  Not the wide kernel: its few blocks are the batch's longest warps, and with a
+            // configuration of their own they land on SMs they share with little else -- one eighth of config 3: 25.4 us
+            // against 27.2 with it included.  Leaving out any OTHER kernel is what must not happen: 39.6-41.6 us.)
+            const int which = getenv("SYMRELAY_CARVEOUT_SET") ? atoi(getenv("SYMRELAY_CARVEOUT_SET")) : 31;
+            if (which & 1) CU(ctx, cudaFuncSetAttribute(ss_packed_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            if (which & 2) CU(ctx, cudaFuncSetAttribute(ss_packed_only_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            if (which & 4) CU(ctx, cudaFuncSetAttribute(ss_thread_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            if (which & 8) CU(ctx, cudaFuncSetAttribute(ss_strided_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            if (which & 16) CU(ctx, cudaFuncSetAttribute(ss_bulk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            if (which & 32) CU(ctx, cudaFuncSetAttribute(ss_wide_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
         }
     }
     sh.init_cap = 4096;
