@@ -19,6 +19,14 @@ int main(){ const uint32_t n=131072; std::vector<symrelay_desc> d(n), s(n); std:
  // validate: tiles cover every sorted descriptor exactly once, block sums <= 32, perm is a permutation
  std::vector<int> seen(n,0), pseen(n,0); uint64_t lanes=0; bool ok=true;
  for(int64_t k=0;k<r;k++){ uint32_t f=t[k].first, cnt=t[k].n_kind&0xffff, kind=t[k].n_kind>>16; const bool wide=(kind&4u)!=0; if(wide) kind&=~4u; uint32_t sum=0; for(uint32_t j=0;j<cnt;j++){ seen[f+j]++; uint32_t c=2+(((s[f+j].len_flags&0xffffff)+63)>>6); sum+=c; if(kind==2 && c!=2+(((s[f].len_flags&0xffffff)+63)>>6)) ok=false; if(kind==1 && c<=32) ok=false; if(wide && (kind!=1 || c<128)) ok=false; if(kind!=1 && c>32) ok=false;} if(kind==0 && sum>32) ok=false; if(kind==2 && cnt!=32) ok=false; lanes+=sum; }
+ // longest first: along the small-tile list the frames' block counts never grow, thread tiles and packed tiles alike
+ // (what starts last in a batch that needs two rounds of warps must be the short tiles), and the same holds inside the
+ // strided part and inside the big-frame part of the bulk class
+ { uint32_t prev_small=0xffffffffu, prev_str=0xffffffffu, prev_big_class=0xffffffffu;
+   for(int64_t k=0;k<r;k++){ const uint32_t kind=(t[k].n_kind>>16)&3u, lanes_per=(t[k].n_kind>>24)&63u, c=2+(((s[t[k].first].len_flags&0xffffff)+63)>>6);
+     if(kind!=1){ if(c>prev_small) ok=false; prev_small=c; }
+     else if(lanes_per){ if(c>prev_str) ok=false; prev_str=c; }
+     else { const uint32_t cls=31-__builtin_clz(c); if(cls>prev_big_class) ok=false; prev_big_class=cls; } } }
  for(uint32_t i=0;i<n;i++){ if(seen[i]!=1) ok=false; pseen[perm[i]]++; if(memcmp(&s[i],&d[perm[i]],16)) ok=false; }
  for(uint32_t i=0;i<n;i++) if(pseen[i]!=1) ok=false;
  uint32_t nb2; int64_t r2=symrelay_plan_inline(d.data(),n,t.data(),n,&nb2,&chk);
