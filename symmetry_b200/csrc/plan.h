@@ -243,6 +243,73 @@ static inline int64_t symrelay_plan_inline(const symrelay_desc *desc, uint32_t n
     return (int64_t)n_tiles;
 }
 
+// A four-way fork-join for the planner of very large batches (BASELINE config 3 is 131,072 descriptors per batch and its
+// host path was bound by ~1 ms of single-threaded planning per batch against ~60 us of kernels).  Three workers are
+// started with the first large batch and sleep on a condition variable between batches; the caller runs share 0 itself.
+// If the pool is busy (another GPU's batch is being planned), cannot start, or the process has forked since, the caller
+// simply runs all four shares one after the other: the result is the same either way.
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <string.h>
+#include <unistd.h>
+#ifndef SYMRELAY_PLAN_PAR_MIN
+#define SYMRELAY_PLAN_PAR_MIN 32768u   /* descriptors; below this the wake-ups cost more than they save */
+#endif
+class SymrelayPlanPool {
+public:
+    // Never destroyed: the workers sleep until the process ends (a destructor would have to join them from whatever
+    // thread runs exit handlers -- and in a forked child, where they do not exist, there is nothing to join).
+    static SymrelayPlanPool &get() { static SymrelayPlanPool *p = new SymrelayPlanPool; return *p; }
+    template <class F> void run(F &&f) {
+        std::unique_lock<std::mutex> busy(busy_, std::defer_lock);
+        if (!usable() || !busy.try_lock()) { for (int k = 0; k < 4; k++) f(k); return; }
+        job_ = [&f](int k) { f(k); };
+        { std::lock_guard<std::mutex> g(m_); pending_ = 3; gen_++; }
+        cv_go_.notify_all();
+        f(0);
+        std::unique_lock<std::mutex> g(m_);
+        cv_done_.wait(g, [this] { return pending_ == 0; });
+    }
+private:
+    SymrelayPlanPool() {
+        if (getenv("SYMRELAY_PLAN_THREADS") && atoi(getenv("SYMRELAY_PLAN_THREADS")) == 0) return;   // kill switch
+        pid_ = getpid();
+        try {
+            for (int k = 0; k < 3; k++) th_[k] = std::thread([this, k] { worker(k + 1); });
+            ok_ = true;
+        } catch (...) {   // no threads to be had: whatever did start is told to leave, and the caller plans alone
+            { std::lock_guard<std::mutex> g(m_); quit_ = true; gen_++; }
+            cv_go_.notify_all();
+            for (auto &t : th_) if (t.joinable()) t.join();
+        }
+    }
+    SymrelayPlanPool(const SymrelayPlanPool &) = delete;
+    bool usable() const { return ok_ && pid_ == getpid(); }
+    void worker(int k) {
+        unsigned long long seen = 0;
+        for (;;) {
+            std::unique_lock<std::mutex> g(m_);
+            cv_go_.wait(g, [&] { return gen_ != seen; });
+            seen = gen_;
+            if (quit_) return;
+            g.unlock();
+            job_(k);
+            g.lock();
+            if (--pending_ == 0) cv_done_.notify_one();
+        }
+    }
+    std::thread th_[3];
+    std::mutex m_, busy_;
+    std::condition_variable cv_go_, cv_done_;
+    std::function<void(int)> job_;
+    unsigned long long gen_ = 0;
+    int pending_ = 0;
+    bool quit_ = false, ok_ = false;
+    pid_t pid_ = 0;
+};
+
 // Bucketed planning for large host batches.  Frames that arrive in any order pack badly (BASELINE config 3:
 // 19,441 tiles in arrival order against 9,068 when grouped by size, no thread tiles) and the greedy cut above
 // mispredicts on every tile boundary (1.5 ms for 131,072 descriptors).  A batch holds at most one frame per
@@ -257,25 +324,57 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
                                              uint32_t *perm) {
     static thread_local std::vector<uint32_t> ncv;
     if (ncv.size() < 3u * (size_t)n) ncv.resize(3u * (size_t)n);
-    uint32_t *nc = ncv.data();
+    uint32_t *nc = ncv.data(), *row_lo = nc + n, *row_hi = nc + 2u * (size_t)n;
     const uint64_t cap = 0xffffffffull;
-    uint32_t scan[6];
-    symrelay_plan_scan(desc, n, nc, nc + n, nc + 2u * (size_t)n, (uint32_t)(chk && chk->in_bytes < cap ? chk->in_bytes : cap),
-                       (uint32_t)(chk && chk->out_bytes < cap ? chk->out_bytes : cap), chk ? chk->max_streams : 0xffffffffu, scan);
-    if (chk) { chk->out_of_bounds = scan[1]; chk->any_flags = scan[2]; chk->out_overlap = scan[5]; }
-    if (scan[0]) return SYMRELAY_EINVAL;
-    if (scan[2] & SYMRELAY_F_RUN) return -2;
+    const uint32_t in_cap = (uint32_t)(chk && chk->in_bytes < cap ? chk->in_bytes : cap),
+                   out_cap = (uint32_t)(chk && chk->out_bytes < cap ? chk->out_bytes : cap),
+                   max_streams = chk ? chk->max_streams : 0xffffffffu;
+    // The batch is cut into four consecutive quarters; every pass below works quarter by quarter -- on four threads when
+    // the batch is large (SymrelayPlanPool), one after the other otherwise -- and a quarter's frames of a bucket are
+    // placed behind the earlier quarters' frames of that bucket, so the sorted order is the one a single walk gives.
+    constexpr uint32_t PQ = 4;
+    const uint32_t quarter = (((n + PQ - 1u) / PQ) + 7u) & ~7u;
+    const bool parallel = n >= SYMRELAY_PLAN_PAR_MIN;
+    auto run4 = [parallel](auto &&f) {   // (the pool and its threads come into being with the first large batch)
+        if (parallel) SymrelayPlanPool::get().run(f);
+        else for (int k = 0; k < 4; k++) f(k);
+    };
     // bucket 0..30: 2..32 blocks; bucket 31: bulk.  Inside the bulk bucket the frames are ordered by size class
     // (power-of-two ranges of the block count), LARGEST FIRST: a 16 KiB frame keeps its warp nine times as long as a
     // 2 KiB one, so the long ones must start first or they finish last.
-    uint32_t count[32] = {0}, bulk_class[20] = {0};
-    uint64_t batch_blocks = 0;
-    for (uint32_t i = 0; i < n; i++) {
-        const uint32_t c = nc[i];
-        batch_blocks += c;
-        count[(c > 32u ? 33u : c) - 2u]++;
-        if (c > 32u) bulk_class[31 - __builtin_clz(c)]++;   // c in [33, 2^18 + 2]: classes 5..18
+    uint32_t qscan[PQ][6], qcount[PQ][32], qclass[PQ][20];
+    uint64_t qblocks[PQ];
+    run4([&](int k) {
+        const uint32_t lo = (uint32_t)k * quarter < n ? (uint32_t)k * quarter : n, hi = lo + quarter < n ? lo + quarter : n;
+        memset(qcount[k], 0, sizeof(qcount[k]));
+        memset(qclass[k], 0, sizeof(qclass[k]));
+        symrelay_plan_scan(desc + lo, hi - lo, nc + lo, row_lo + lo, row_hi + lo, in_cap, out_cap, max_streams, qscan[k]);
+        uint64_t blocks = 0;
+        for (uint32_t i = lo; i < hi; i++) {
+            const uint32_t c = nc[i];
+            blocks += c;
+            qcount[k][(c > 32u ? 33u : c) - 2u]++;
+            if (c > 32u) qclass[k][31 - __builtin_clz(c)]++;   // c in [33, 2^18 + 2]: classes 5..18
+        }
+        qblocks[k] = blocks;
+    });
+    uint32_t scan[6] = {0, 0, 0, 0xffffffffu, 0, 0};
+    for (uint32_t k = 0; k < PQ; k++) {
+        const uint32_t lo = k * quarter;
+        if (lo >= n) break;
+        scan[0] |= qscan[k][0]; scan[1] |= qscan[k][1]; scan[2] |= qscan[k][2]; scan[5] |= qscan[k][5];
+        scan[3] = qscan[k][3] < scan[3] ? qscan[k][3] : scan[3];
+        scan[4] = qscan[k][4] > scan[4] ? qscan[k][4] : scan[4];
+        if (k) scan[5] |= (uint32_t)(row_lo[lo] < row_hi[lo - 1u]);   // the output rows across the cut
     }
+    if (chk) { chk->out_of_bounds = scan[1]; chk->any_flags = scan[2]; chk->out_overlap = scan[5]; }
+    if (scan[0]) return SYMRELAY_EINVAL;
+    if (scan[2] & SYMRELAY_F_RUN) return -2;
+    uint32_t count[32], bulk_class[20];
+    uint64_t batch_blocks = 0;
+    for (uint32_t b = 0; b < 32u; b++) count[b] = qcount[0][b] + qcount[1][b] + qcount[2][b] + qcount[3][b];
+    for (uint32_t b = 0; b < 20u; b++) bulk_class[b] = qclass[0][b] + qclass[1][b] + qclass[2][b] + qclass[3][b];
+    for (uint32_t k = 0; k < PQ; k++) batch_blocks += qblocks[k];
     const bool thread_ok = n >= SYMRELAY_THREAD_TILE_MIN_FRAMES;
     uint32_t base[32], at = 0;
     uint64_t n_tiles = 0;
@@ -329,15 +428,20 @@ static inline int64_t symrelay_plan_bucketed(const symrelay_desc *desc, uint32_t
     }
     if (n_bulk_out) *n_bulk_out = count[31] + n_strided;
     if (tiles && sorted && perm) {
-        uint32_t next[32], bnext[20];
-        for (uint32_t b = 0; b < 32u; b++) next[b] = base[b];
-        for (uint32_t k = 20u, at2 = base[31]; k-- > 0u;) { bnext[k] = at2; at2 += bulk_class[k]; }   // largest class first
-        for (uint32_t i = 0; i < n; i++) {
-            const uint32_t c = nc[i];
-            const uint32_t pos = c > 32u ? bnext[31 - __builtin_clz(c)]++ : next[c - 2u]++;
-            sorted[pos] = desc[i];
-            perm[pos] = i;
-        }
+        uint32_t next[PQ][32], bnext[PQ][20];
+        for (uint32_t b = 0; b < 32u; b++)
+            for (uint32_t k = 0, at2 = base[b]; k < PQ; k++) { next[k][b] = at2; at2 += qcount[k][b]; }
+        for (uint32_t c = 20u, at2 = base[31]; c-- > 0u;)   // largest class first
+            for (uint32_t k = 0; k < PQ; k++) { bnext[k][c] = at2; at2 += qclass[k][c]; }
+        run4([&](int k) {
+            const uint32_t lo = (uint32_t)k * quarter < n ? (uint32_t)k * quarter : n, hi = lo + quarter < n ? lo + quarter : n;
+            for (uint32_t i = lo; i < hi; i++) {
+                const uint32_t c = nc[i];
+                const uint32_t pos = c > 32u ? bnext[k][31 - __builtin_clz(c)]++ : next[k][c - 2u]++;
+                sorted[pos] = desc[i];
+                perm[pos] = i;
+            }
+        });
     }
     return (int64_t)n_tiles;
 }

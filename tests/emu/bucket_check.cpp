@@ -30,4 +30,11 @@ int main(){ const uint32_t n=131072; std::vector<symrelay_desc> d(n), s(n); std:
  for(uint32_t i=0;i<n;i++){ if(seen[i]!=1) ok=false; pseen[perm[i]]++; if(memcmp(&s[i],&d[perm[i]],16)) ok=false; }
  for(uint32_t i=0;i<n;i++) if(pseen[i]!=1) ok=false;
  uint32_t nb2; int64_t r2=symrelay_plan_inline(d.data(),n,t.data(),n,&nb2,&chk);
- printf("bucketed: %lld tiles (%u bulk) in %.0f us, valid=%d; greedy in arrival order: %lld tiles\n",(long long)r,nb,best,(int)ok,(long long)r2); return ok?0:1; }
+ // the plan as one number (the test runs this program with and without the planner's worker threads: same plan), and the
+ // same call many more times, to give a race between the caller and the workers a chance to show
+ auto fnv=[&](){ uint64_t h=1469598103934665603ull; auto mix=[&](const void*p,size_t nbytes){ const uint8_t*b=(const uint8_t*)p; for(size_t i=0;i<nbytes;i++){ h^=b[i]; h*=1099511628211ull; } };
+   mix(t.data(),(size_t)r*sizeof(symrelay_tile)); mix(s.data(),(size_t)n*16); mix(perm.data(),(size_t)n*4); return h; };
+ r=symrelay_plan_bucketed(d.data(),n,t.data(),n,&nb,&chk,s.data(),perm.data());
+ const uint64_t h0=fnv();
+ for(int k=0;k<300;k++){ std::fill(perm.begin(),perm.end(),0u); int64_t rr=symrelay_plan_bucketed(d.data(),n,t.data(),n,&nb,&chk,s.data(),perm.data()); if(rr!=r||fnv()!=h0){ ok=false; break; } }
+ printf("bucketed: %lld tiles (%u bulk) in %.0f us, valid=%d, plan=%016llx; greedy in arrival order: %lld tiles\n",(long long)r,nb,best,(int)ok,(unsigned long long)h0,(long long)r2); return ok?0:1; }

@@ -139,10 +139,53 @@ def test_bucketed_planner_covers_every_descriptor_once(tmp_path):
     import subprocess
 
     exe = str(tmp_path / "bucket_check")
-    subprocess.run(["g++", "-O2", "-std=c++17", "-o", exe, os.path.join(ROOT, "tests", "emu", "bucket_check.cpp"),
+    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", "-o", exe, os.path.join(ROOT, "tests", "emu", "bucket_check.cpp"),
                     os.path.join(ROOT, "symmetry_b200", "csrc", "plan_scan_avx2.cpp")], check=True)
     res = subprocess.run([exe], capture_output=True, text=True)
     assert res.returncode == 0 and "valid=1" in res.stdout, res.stdout + res.stderr
+    # batches this large are planned on four threads (the caller and three workers); without them -- kill switch, a busy
+    # pool, a forked child -- the caller runs the four shares itself and must arrive at the very same plan
+    env = dict(os.environ, SYMRELAY_PLAN_THREADS="0")
+    res1 = subprocess.run([exe], capture_output=True, text=True, env=env)
+    assert res1.returncode == 0 and "valid=1" in res1.stdout, res1.stdout + res1.stderr
+    plan = re.search(r"plan=([0-9a-f]{16})", res.stdout).group(1)
+    assert plan == re.search(r"plan=([0-9a-f]{16})", res1.stdout).group(1), (res.stdout, res1.stdout)
+
+
+def test_planner_threads_survive_fork_and_exit():
+    """The library's planner starts three worker threads with its first large batch.  The process must still exit
+    cleanly, and a forked child (which has no such threads) must plan by itself instead of waiting for them."""
+    import subprocess
+    import sys
+
+    code = r'''
+import os, sys, ctypes as C
+import numpy as np
+sys.path.insert(0, os.path.join(%r, "tests"))
+sys.path.insert(0, %r)
+import batch_util as bu
+from symmetry_b200 import _lib
+L = _lib.load()
+n = 70000
+lens = [64 + (i * 37) %% 900 for i in range(n)]
+p, _ = bu.plain_layout(lens); w, _ = bu.wire_layout(lens)
+d = bu.make_descs(np.arange(n), lens, p, w)
+def plan():
+    tiles = np.zeros((n, 2), dtype=np.uint32); sd = np.zeros_like(d); perm = np.zeros(n, dtype=np.uint32); nb = C.c_uint32(0)
+    nt = L.symrelay_plan_sorted(d.ctypes.data, n, tiles.ctypes.data, n, C.byref(nb), sd.ctypes.data, perm.ctypes.data)
+    assert nt > 0 and sorted(perm.tolist()) == list(range(n))
+    return tiles[:nt].tobytes() + sd.tobytes() + perm.tobytes()
+a = plan()
+pid = os.fork()
+if pid == 0:
+    sys.exit(0 if plan() == a else 3)      # an ordinary exit: the child runs the library's exit handlers too
+_, st = os.waitpid(pid, 0)
+assert os.WEXITSTATUS(st) == 0, st
+assert plan() == a
+print("ok")
+''' % (ROOT, ROOT)
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0 and "ok" in res.stdout, res.stdout + res.stderr
 
 
 def test_napi_shim_is_valid_c_against_the_header():
